@@ -1,0 +1,159 @@
+"""ctypes binding of libb2seg.so (C ABI declared in include/b2seg.h).
+
+There is deliberately no fallback: if the shared library is missing or a call
+fails, a B2SegError is raised.  Nothing under ``oracle/`` is ever imported here.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+ABI_VERSION = 1
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb2seg.so")
+
+
+class B2SegError(RuntimeError):
+    pass
+
+
+# ---------------------------------------------------------------- structs ----
+class LossSpec(C.Structure):
+    _fields_ = [
+        ("w_dice", C.c_float), ("w_logcosh_dice", C.c_float), ("dice_smooth", C.c_float),
+        ("w_tversky", C.c_float), ("tv_alpha", C.c_float), ("tv_beta", C.c_float),
+        ("tv_smooth", C.c_float), ("tv_gamma", C.c_float),
+        ("w_sens_spec", C.c_float), ("ss_w", C.c_float), ("ss_eps", C.c_float),
+        ("w_bce", C.c_float), ("bce_mode", C.c_int32), ("bce_beta", C.c_float),
+        ("w_focal", C.c_float), ("focal_alpha", C.c_float), ("focal_gamma", C.c_float),
+    ]
+
+
+STATS_LEN = 16
+COEF_LEN = 8
+S_P, S_T, S_PT, S_BCE, S_BCE_T, S_FOCAL, S_PB, S_PB_T, S_N, S_LOSS, S_TP, S_FP, S_FN, S_TN = range(14)
+
+AUG_HFLIP, AUG_VFLIP, AUG_ROT90, AUG_TRANSPOSE = 0, 1, 2, 3
+INTERP_NEAREST, INTERP_LINEAR = 0, 1
+BORDER_CONSTANT, BORDER_REFLECT, BORDER_REFLECT101 = 0, 1, 2
+
+MAX_TAPS = 9
+MAX_SUB = 4
+
+
+class Tensor4(C.Structure):
+    _fields_ = [("ptr", C.c_void_p), ("n", C.c_int32), ("h", C.c_int32), ("w", C.c_int32),
+                ("c", C.c_int32), ("sn", C.c_int64), ("sh", C.c_int64), ("sw", C.c_int64)]
+
+
+class Tap(C.Structure):
+    _fields_ = [("src", C.c_int8), ("dh", C.c_int8), ("dw", C.c_int8), ("wtap", C.c_int8)]
+
+
+class TapSub(C.Structure):
+    _fields_ = [("ntaps", C.c_int32), ("taps", Tap * MAX_TAPS), ("out_offset", C.c_int64)]
+
+
+class TapGemmDesc(C.Structure):
+    _fields_ = [
+        ("src", Tensor4 * 4), ("nsrc", C.c_int32), ("nsub", C.c_int32),
+        ("sub", TapSub * MAX_SUB),
+        ("weights", C.c_void_p), ("wtaps", C.c_int32), ("ngemm", C.c_int32), ("cin", C.c_int32),
+        ("on", C.c_int32), ("oh", C.c_int32), ("ow", C.c_int32),
+        ("out", C.c_void_p), ("osn", C.c_int64), ("osh", C.c_int64), ("osw", C.c_int64),
+        ("cq", C.c_int32), ("oqh", C.c_int64), ("oqw", C.c_int64),
+        ("bias", C.c_void_p), ("stats", C.c_void_p), ("accumulate", C.c_int32),
+    ]
+
+
+class WgradTap(C.Structure):
+    _fields_ = [("src", C.c_int8), ("dh", C.c_int8), ("dw", C.c_int8), ("pad", C.c_int8),
+                ("out_base", C.c_int64)]
+
+
+class WgradDesc(C.Structure):
+    _fields_ = [
+        ("a_src", Tensor4 * 4), ("na_src", C.c_int32), ("b_src", Tensor4),
+        ("ntaps", C.c_int32), ("taps", WgradTap * MAX_TAPS),
+        ("pn", C.c_int32), ("ph", C.c_int32), ("pw", C.c_int32),
+        ("grad", C.c_void_p), ("row_stride", C.c_int64), ("col_stride", C.c_int64),
+        ("accumulate", C.c_int32), ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
+    ]
+
+
+# ------------------------------------------------------------- signatures ----
+_vp, _i, _i64, _sz = C.c_void_p, C.c_int, C.c_int64, C.c_size_t
+_SIGS = {
+    "b2seg_abi_version": (C.c_int, []),
+    "b2seg_last_error": (C.c_char_p, []),
+    "b2seg_device_info": (C.c_int, [C.c_char_p, _i, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "b2seg_seg_reduce_workspace_bytes": (_sz, []),
+    "b2seg_seg_loss_fwd": (C.c_int, [_vp, _vp, _vp, _i64, C.POINTER(LossSpec), _vp, _vp, _vp, _vp, _vp]),
+    "b2seg_seg_loss_bwd": (C.c_int, [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp]),
+    "b2seg_seg_metrics_from_probs": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _vp]),
+    "b2seg_aug_permute_u8": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "b2seg_aug_warp_affine_u8": (C.c_int, [_vp, _vp, _i, _i, _i, C.POINTER(C.c_double), _i, _i, _i, _vp]),
+    "b2seg_aug_remap_u8": (C.c_int, [_vp, _vp, _i, _i, _i, _vp, _vp, _i, _i, _i, _vp]),
+    "b2seg_op_run": (C.c_int, [_vp, _vp]),
+    "b2seg_op_destroy": (C.c_int, [_vp]),
+    "b2seg_op_launches": (C.c_int, [_vp]),
+    "b2seg_seq_create": (C.c_int, [C.POINTER(_vp)]),
+    "b2seg_seq_append": (C.c_int, [_vp, _vp]),
+    "b2seg_seq_run": (C.c_int, [_vp, _vp]),
+    "b2seg_seq_launches": (C.c_int, [_vp]),
+    "b2seg_seq_destroy": (C.c_int, [_vp]),
+    "b2seg_tapgemm_create": (C.c_int, [C.POINTER(TapGemmDesc), C.POINTER(_vp)]),
+    "b2seg_tapgemm_stat_rows": (C.c_int, [_i, _i, _i]),
+    "b2seg_wgrad_workspace_bytes": (_sz, [_i, _i, _i, _i, _i, _i]),
+    "b2seg_wgrad_create": (C.c_int, [C.POINTER(WgradDesc), C.POINTER(_vp)]),
+}
+
+_lib = None
+
+
+def exported_symbols():
+    """Names include/b2seg.h declares (used by the CPU-side ABI test)."""
+    return sorted(_SIGS)
+
+
+def register(name, restype, argtypes):
+    _SIGS[name] = (restype, argtypes)
+    if _lib is not None:
+        fn = getattr(_lib, name)
+        fn.restype, fn.argtypes = restype, argtypes
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise B2SegError(
+                f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; "
+                "g.build()'` (nvcc, sm_100a).  b2seg has no CPU or PyTorch fallback.")
+        handle = C.CDLL(LIB_PATH)
+        for name, (restype, argtypes) in _SIGS.items():
+            fn = getattr(handle, name)  # AttributeError here = ABI mismatch, fail loudly
+            fn.restype, fn.argtypes = restype, argtypes
+        ver = handle.b2seg_abi_version()
+        if ver != ABI_VERSION:
+            raise B2SegError(f"libb2seg ABI {ver} != expected {ABI_VERSION}")
+        _lib = handle
+    return _lib
+
+
+def check(rc: int):
+    if rc != 0:
+        msg = lib().b2seg_last_error().decode("utf-8", "replace")
+        raise B2SegError(f"libb2seg error {rc}: {msg}")
+
+
+def stream_ptr():
+    import torch
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def require_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise B2SegError("b2seg kernels run on a Blackwell GPU only; got a CPU tensor "
+                             "(there is no CPU fallback)")

@@ -1,0 +1,31 @@
+// Planned-op objects behind the C ABI: an op is created once for fixed device
+// pointers/shapes (TMA descriptors encoded at creation) and then enqueued any
+// number of times on a stream; a sequence replays a list of ops with one call.
+#pragma once
+#include <vector>
+
+#include "common.cuh"
+
+struct b2seg_op {
+  virtual ~b2seg_op() {}
+  virtual int run(cudaStream_t st) = 0;
+  virtual const char* name() const = 0;
+  // number of kernel launches one run() enqueues (for bench accounting)
+  virtual int launches() const { return 1; }
+};
+
+struct b2seg_seq {
+  std::vector<b2seg_op*> ops;
+};
+
+// NHWC bf16 view -> rank-4 TMA descriptor with box (64ch, wt, ht, nt), 128B swizzle.
+int b2_view_tmap(CUtensorMap* out, const b2seg_tensor4* v, int wt, int ht, int nt);
+
+// pixel-tile shape (wt*ht*nt == 128) for an (n,h,w) iteration grid
+static inline void b2_pick_pixel_tile(int n, int h, int w, int* wt, int* ht, int* nt) {
+  auto p2 = [](int x) { int p = 1; while (p < x) p <<= 1; return p; };
+  int a = p2(w); if (a > 16) a = 16;
+  int b = p2(h); if (b > 128 / a) b = 128 / a;
+  *wt = a; *ht = b; *nt = 128 / (a * b);
+  (void)n;
+}

@@ -1,0 +1,498 @@
+// Fused per-pixel segmentation losses + metrics (HBM-bound, single pass).
+//
+// Every closed-form loss of the reference (losses.py:13-171, 322-342) is a
+// function of six batch-global sums; calculate_metrics (utils.py:120-151) adds
+// two thresholded counts.  The forward kernel reads logits and targets exactly
+// once (8 B/px), reduces 8 accumulators warp -> block -> grid (last block done
+// finishes in fixed order, so results are run-to-run deterministic), evaluates
+// the weighted loss and leaves the gradient coefficients on the device.  The
+// backward kernel is a second streaming pass (12 B/px).
+#include "common.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kAcc = 8;
+constexpr int kMaxBlocks = 148 * 8;
+
+struct LossSpecDev {
+  b2seg_loss_spec s;
+};
+
+// ---- per-element math ------------------------------------------------------
+struct PixelTerms {
+  float p, bce, one_m_pt;
+};
+
+// softplus(-|x|) = log1p(exp(-|x|)) without the 1+e rounding loss for small e.
+__device__ __forceinline__ float log1p_exp_neg(float e) {
+  // e in (0, 1].  Series below 2^-6: error < e^4/4 relative 6e-8.
+  float series = e * (1.0f - e * (0.5f - e * (1.0f / 3.0f)));
+  return e < 0.015625f ? series : __logf(1.0f + e);
+}
+
+template <bool NEED_FOCAL>
+__device__ __forceinline__ PixelTerms pixel_terms(float x, float t) {
+  PixelTerms r;
+  const float e = __expf(-fabsf(x));
+  const float inv = __frcp_rn(1.0f + e);
+  r.p = x >= 0.0f ? inv : e * inv;
+  r.bce = fmaxf(x, 0.0f) - x * t + log1p_exp_neg(e);
+  r.one_m_pt = NEED_FOCAL ? 1.0f - __expf(-r.bce) : 0.0f;
+  return r;
+}
+
+__device__ __forceinline__ float pow_pos(float base, float g) {
+  // base in [0,1]; g > 0.  lg2(0) = -inf -> ex2(-inf) = 0.
+  return exp2f(g * __log2f(base));
+}
+
+template <bool NEED_FOCAL, bool HAS_WMAP>
+__device__ __forceinline__ void accumulate(float (&acc)[kAcc], float x, float t, float w,
+                                           float gamma, bool gamma_is_two) {
+  const PixelTerms q = pixel_terms<NEED_FOCAL>(x, t);
+  const float bce_w = HAS_WMAP ? q.bce * w : q.bce;
+  acc[0] += q.p;
+  acc[1] += t;
+  acc[2] = fmaf(q.p, t, acc[2]);
+  acc[3] += bce_w;
+  acc[4] = fmaf(q.bce, t, acc[4]);
+  if (NEED_FOCAL) {
+    const float m = gamma_is_two ? q.one_m_pt * q.one_m_pt : pow_pos(q.one_m_pt, gamma);
+    acc[5] = fmaf(m, q.bce, acc[5]);
+  }
+  const float pb = q.p > 0.5f ? 1.0f : 0.0f;
+  acc[6] += pb;
+  acc[7] = fmaf(pb, t, acc[7]);
+}
+
+// ---- reduction tail shared by loss-forward and metrics kernels --------------
+struct ReduceWs {
+  unsigned int ticket;
+  unsigned int pad[3];
+  double partial[kMaxBlocks][kAcc];
+};
+
+// Returns true (to every thread of exactly one block) once all blocks have
+// published their partials; that block then holds the grid totals in tot[].
+__device__ __forceinline__ bool grid_reduce(float (&acc)[kAcc], ReduceWs* ws, double (&tot)[kAcc],
+                                            double* s_tot /* smem [kAcc] */) {
+  __shared__ float s_part[kThreads / 32][kAcc];
+  __shared__ bool s_last;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int i = 0; i < kAcc; ++i) acc[i] = warp_sum(acc[i]);
+  if (lane == 0) {
+#pragma unroll
+    for (int i = 0; i < kAcc; ++i) s_part[warp][i] = acc[i];
+  }
+  __syncthreads();
+  if (threadIdx.x < kAcc) {
+    double s = 0.0;
+#pragma unroll
+    for (int w = 0; w < kThreads / 32; ++w) s += (double)s_part[w][threadIdx.x];
+    ws->partial[blockIdx.x][threadIdx.x] = s;
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int tk = atomicAdd(&ws->ticket, 1u);
+    s_last = (tk == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!s_last) return false;
+  __threadfence();
+  // One warp per accumulator, fixed block order -> deterministic.
+  if (warp < kAcc) {
+    double s = 0.0;
+    for (int b = lane; b < (int)gridDim.x; b += 32) s += ws->partial[b][warp];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) s_tot[warp] = s;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < kAcc; ++i) tot[i] = s_tot[i];
+  if (threadIdx.x == 0) ws->ticket = 0;  // leave the workspace reusable
+  return true;
+}
+
+__device__ void write_confusion(double* stats, double n) {
+  const double pb = stats[B2SEG_S_PB], tp = stats[B2SEG_S_PB_T], st = stats[B2SEG_S_T];
+  stats[B2SEG_S_N] = n;
+  stats[B2SEG_S_TP] = tp;
+  stats[B2SEG_S_FP] = pb - tp;
+  stats[B2SEG_S_FN] = st - tp;
+  stats[B2SEG_S_TN] = n - pb - st + tp;
+}
+
+// Loss value + gradient coefficients from the six sums.
+//   dL/dx_i = (A t_i + B) p_i (1-p_i) + (W0 + W1 t_i [+ Wm w_i]) (p_i - t_i)
+//             + F ((1-pt)^g + g (1-pt)^(g-1) pt bce_i) (p_i - t_i)
+__device__ void finish_loss(const b2seg_loss_spec& s, const double* tot, double n, double* stats,
+                            float* loss_out, float* coef) {
+  const double Sp = tot[0], St = tot[1], Spt = tot[2], Sbce = tot[3], Sbce_t = tot[4],
+               Sfoc = tot[5];
+  double loss = 0.0, A = 0.0, B = 0.0, W0 = 0.0, W1 = 0.0, Wm = 0.0, F = 0.0;
+
+  if (s.w_dice != 0.0f || s.w_logcosh_dice != 0.0f) {
+    const double sm = s.dice_smooth, U = Sp + St;
+    const double dice = (2.0 * Spt + sm) / (U + sm);
+    const double Ld = 1.0 - dice;
+    const double a = -2.0 / (U + sm), b = (2.0 * Spt + sm) / ((U + sm) * (U + sm));
+    loss += s.w_dice * Ld;
+    A += s.w_dice * a;
+    B += s.w_dice * b;
+    if (s.w_logcosh_dice != 0.0f) {
+      const double th = tanh(Ld);
+      loss += s.w_logcosh_dice * log(cosh(Ld));
+      A += s.w_logcosh_dice * th * a;
+      B += s.w_logcosh_dice * th * b;
+    }
+  }
+  if (s.w_tversky != 0.0f) {
+    const double al = s.tv_alpha, be = s.tv_beta, sm = s.tv_smooth, g = s.tv_gamma;
+    const double TP = Spt, FP = Sp - Spt, FN = St - Spt;
+    const double D = TP + al * FP + be * FN + sm;
+    const double Lt = 1.0 - (TP + sm) / D;
+    double val = Lt, fac = 1.0;
+    if (g != 1.0) {
+      val = pow(Lt, g);
+      fac = g * pow(Lt, g - 1.0);
+    }
+    loss += s.w_tversky * val;
+    A += s.w_tversky * fac * (-(D - (TP + sm) * (1.0 - al - be)) / (D * D));
+    B += s.w_tversky * fac * ((TP + sm) * al / (D * D));
+  }
+  if (s.w_sens_spec != 0.0f) {
+    const double w = s.ss_w, eps = s.ss_eps;
+    const double TP = Spt, FN = St - Spt, FP = Sp - Spt, TN = n - Sp - St + Spt;
+    const double sens = TP / (TP + FN + eps), spec = TN / (TN + FP + eps);
+    loss += s.w_sens_spec * (1.0 - (w * sens + (1.0 - w) * spec));
+    const double ds = 1.0 / (St + eps), dn = 1.0 / (n - St + eps);
+    A += s.w_sens_spec * (-w * ds - (1.0 - w) * dn);
+    B += s.w_sens_spec * ((1.0 - w) * dn);
+  }
+  if (s.w_bce != 0.0f) {
+    double w0 = 1.0, w1 = 0.0;
+    if (s.bce_mode == 1) {
+      w1 = (double)s.bce_beta - 1.0;
+    } else if (s.bce_mode == 2) {
+      const double beta = 1.0 - St / n;
+      w0 = 1.0 - beta;
+      w1 = 2.0 * beta - 1.0;
+    }
+    if (s.bce_mode == 3) {  // Sbce already carries the per-pixel weight map
+      loss += s.w_bce * Sbce / n;
+      Wm += s.w_bce / n;
+    } else {
+      loss += s.w_bce * (w0 * Sbce + w1 * Sbce_t) / n;
+      W0 += s.w_bce * w0 / n;
+      W1 += s.w_bce * w1 / n;
+    }
+  }
+  if (s.w_focal != 0.0f) {
+    loss += s.w_focal * s.focal_alpha * Sfoc / n;
+    F += s.w_focal * s.focal_alpha / n;
+  }
+  for (int i = 0; i < kAcc; ++i) stats[i] = tot[i];
+  write_confusion(stats, n);
+  stats[B2SEG_S_LOSS] = loss;
+  *loss_out = (float)loss;
+  coef[0] = (float)A;
+  coef[1] = (float)B;
+  coef[2] = (float)W0;
+  coef[3] = (float)W1;
+  coef[4] = (float)F;
+  coef[5] = s.focal_gamma;
+  coef[6] = (float)Wm;
+  coef[7] = 0.0f;
+}
+
+// ---- forward kernel -----------------------------------------------------------
+template <bool NEED_FOCAL, bool HAS_WMAP, bool VEC4>
+__global__ void __launch_bounds__(kThreads)
+    seg_loss_fwd_kernel(const float* __restrict__ x, const float* __restrict__ t,
+                        const float* __restrict__ wm, long long n, LossSpecDev spec, ReduceWs* ws,
+                        double* stats, float* loss_out, float* coef) {
+  float acc[kAcc];
+#pragma unroll
+  for (int i = 0; i < kAcc; ++i) acc[i] = 0.0f;
+  const float gamma = spec.s.focal_gamma;
+  const bool g2 = gamma == 2.0f;
+  const long long tid = (long long)blockIdx.x * kThreads + threadIdx.x;
+  const long long nthreads = (long long)gridDim.x * kThreads;
+
+  if (VEC4) {
+    const long long n4 = n >> 2;
+    const float4* x4 = reinterpret_cast<const float4*>(x);
+    const float4* t4 = reinterpret_cast<const float4*>(t);
+    const float4* w4 = reinterpret_cast<const float4*>(wm);
+    long long i = tid;
+    // two independent 128-bit loads per stream in flight per iteration
+    for (; i + nthreads < n4; i += 2 * nthreads) {
+      const float4 xa = ldg_stream_f4(x4 + i), xb = ldg_stream_f4(x4 + i + nthreads);
+      const float4 ta = ldg_stream_f4(t4 + i), tb = ldg_stream_f4(t4 + i + nthreads);
+      float4 wa = make_float4(1.f, 1.f, 1.f, 1.f), wb = wa;
+      if (HAS_WMAP) {
+        wa = ldg_stream_f4(w4 + i);
+        wb = ldg_stream_f4(w4 + i + nthreads);
+      }
+      accumulate<NEED_FOCAL, HAS_WMAP>(acc, xa.x, ta.x, wa.x, gamma, g2);
+      accumulate<NEED_FOCAL, HAS_WMAP>(acc, xa.y, ta.y, wa.y, gamma, g2);
+      accumulate<NEED_FOCAL, HAS_WMAP>(acc, xa.z, ta.z, wa.z, gamma, g2);
+      accumulate<NEED_FOCAL, HAS_WMAP>(acc, xa.w, ta.w, wa.w, gamma, g2);
+      accumulate<NEED_FOCAL, HAS_WMAP>(acc, xb.x, tb.x, wb.x, gamma, g2);
+      accumulate<NEED_FOCAL, HAS_WMAP>(acc, xb.y, tb.y, wb.y, gamma, g2);
+      accumulate<NEED_FOCAL, HAS_WMAP>(acc, xb.z, tb.z, wb.z, gamma, g2);
+      accumulate<NEED_FOCAL, HAS_WMAP>(acc, xb.w, tb.w, wb.w, gamma, g2);
+    }
+    for (; i < n4; i += nthreads) {
+      const float4 xa = ldg_stream_f4(x4 + i);
+      const float4 ta = ldg_stream_f4(t4 + i);
+      float4 wa = make_float4(1.f, 1.f, 1.f, 1.f);
+      if (HAS_WMAP) wa = ldg_stream_f4(w4 + i);
+      accumulate<NEED_FOCAL, HAS_WMAP>(acc, xa.x, ta.x, wa.x, gamma, g2);
+      accumulate<NEED_FOCAL, HAS_WMAP>(acc, xa.y, ta.y, wa.y, gamma, g2);
+      accumulate<NEED_FOCAL, HAS_WMAP>(acc, xa.z, ta.z, wa.z, gamma, g2);
+      accumulate<NEED_FOCAL, HAS_WMAP>(acc, xa.w, ta.w, wa.w, gamma, g2);
+    }
+    for (long long j = (n4 << 2) + tid; j < n; j += nthreads)
+      accumulate<NEED_FOCAL, HAS_WMAP>(acc, x[j], t[j], HAS_WMAP ? wm[j] : 1.0f, gamma, g2);
+  } else {
+    for (long long j = tid; j < n; j += nthreads)
+      accumulate<NEED_FOCAL, HAS_WMAP>(acc, x[j], t[j], HAS_WMAP ? wm[j] : 1.0f, gamma, g2);
+  }
+
+  __shared__ double s_tot[kAcc];
+  double tot[kAcc];
+  if (grid_reduce(acc, ws, tot, s_tot) && threadIdx.x == 0)
+    finish_loss(spec.s, tot, (double)n, stats, loss_out, coef);
+}
+
+// ---- backward kernel ----------------------------------------------------------
+template <bool NEED_FOCAL, bool HAS_WMAP>
+__device__ __forceinline__ float pixel_grad(float x, float t, float w, float A, float B, float W0,
+                                            float W1, float F, float Wm, float gamma,
+                                            bool gamma_is_two, float go) {
+  const PixelTerms q = pixel_terms<NEED_FOCAL>(x, t);
+  const float d = q.p - t;
+  float g = (fmaf(A, t, B)) * q.p * (1.0f - q.p);
+  float wl = fmaf(W1, t, W0);
+  if (HAS_WMAP) wl = fmaf(Wm, w, wl);
+  if (NEED_FOCAL) {
+    const float m = q.one_m_pt, pt = 1.0f - q.one_m_pt;
+    float mg, mg1;  // m^g, g*m^(g-1)
+    if (gamma_is_two) {
+      mg = m * m;
+      mg1 = 2.0f * m;
+    } else {
+      mg1 = gamma * pow_pos(m, gamma - 1.0f);
+      mg = pow_pos(m, gamma);
+      if (gamma == 1.0f) mg1 = 1.0f;
+    }
+    wl = fmaf(F, fmaf(mg1 * pt, q.bce, mg), wl);
+  }
+  g = fmaf(wl, d, g);
+  return g * go;
+}
+
+template <bool NEED_FOCAL, bool HAS_WMAP, bool VEC4>
+__global__ void __launch_bounds__(kThreads)
+    seg_loss_bwd_kernel(const float* __restrict__ x, const float* __restrict__ t,
+                        const float* __restrict__ wm, long long n,
+                        const float* __restrict__ coef, const float* __restrict__ grad_out,
+                        float* __restrict__ gx) {
+  const float A = coef[0], B = coef[1], W0 = coef[2], W1 = coef[3], F = coef[4], gamma = coef[5],
+              Wm = coef[6];
+  const float go = grad_out ? *grad_out : 1.0f;
+  const bool g2 = gamma == 2.0f;
+  const long long tid = (long long)blockIdx.x * kThreads + threadIdx.x;
+  const long long nthreads = (long long)gridDim.x * kThreads;
+#define B2_PG(xx, tt, ww) \
+  pixel_grad<NEED_FOCAL, HAS_WMAP>(xx, tt, ww, A, B, W0, W1, F, Wm, gamma, g2, go)
+  if (VEC4) {
+    const long long n4 = n >> 2;
+    const float4* x4 = reinterpret_cast<const float4*>(x);
+    const float4* t4 = reinterpret_cast<const float4*>(t);
+    const float4* w4 = reinterpret_cast<const float4*>(wm);
+    float4* g4 = reinterpret_cast<float4*>(gx);
+    long long i = tid;
+    for (; i + nthreads < n4; i += 2 * nthreads) {
+      const float4 xa = ldg_stream_f4(x4 + i), xb = ldg_stream_f4(x4 + i + nthreads);
+      const float4 ta = ldg_stream_f4(t4 + i), tb = ldg_stream_f4(t4 + i + nthreads);
+      float4 wa = make_float4(1.f, 1.f, 1.f, 1.f), wb = wa;
+      if (HAS_WMAP) {
+        wa = ldg_stream_f4(w4 + i);
+        wb = ldg_stream_f4(w4 + i + nthreads);
+      }
+      float4 ga, gb;
+      ga.x = B2_PG(xa.x, ta.x, wa.x);
+      ga.y = B2_PG(xa.y, ta.y, wa.y);
+      ga.z = B2_PG(xa.z, ta.z, wa.z);
+      ga.w = B2_PG(xa.w, ta.w, wa.w);
+      gb.x = B2_PG(xb.x, tb.x, wb.x);
+      gb.y = B2_PG(xb.y, tb.y, wb.y);
+      gb.z = B2_PG(xb.z, tb.z, wb.z);
+      gb.w = B2_PG(xb.w, tb.w, wb.w);
+      stg_stream_f4(g4 + i, ga);
+      stg_stream_f4(g4 + i + nthreads, gb);
+    }
+    for (; i < n4; i += nthreads) {
+      const float4 xa = ldg_stream_f4(x4 + i);
+      const float4 ta = ldg_stream_f4(t4 + i);
+      float4 wa = make_float4(1.f, 1.f, 1.f, 1.f);
+      if (HAS_WMAP) wa = ldg_stream_f4(w4 + i);
+      float4 ga;
+      ga.x = B2_PG(xa.x, ta.x, wa.x);
+      ga.y = B2_PG(xa.y, ta.y, wa.y);
+      ga.z = B2_PG(xa.z, ta.z, wa.z);
+      ga.w = B2_PG(xa.w, ta.w, wa.w);
+      stg_stream_f4(g4 + i, ga);
+    }
+    for (long long j = (n4 << 2) + tid; j < n; j += nthreads)
+      gx[j] = B2_PG(x[j], t[j], HAS_WMAP ? wm[j] : 1.0f);
+  } else {
+    for (long long j = tid; j < n; j += nthreads)
+      gx[j] = B2_PG(x[j], t[j], HAS_WMAP ? wm[j] : 1.0f);
+  }
+#undef B2_PG
+}
+
+// ---- metrics from probabilities (utils.py:120-151) --------------------------------
+template <bool VEC4>
+__global__ void __launch_bounds__(kThreads)
+    seg_metrics_probs_kernel(const float* __restrict__ p, const float* __restrict__ t,
+                             long long n, ReduceWs* ws, double* stats) {
+  float acc[kAcc];
+#pragma unroll
+  for (int i = 0; i < kAcc; ++i) acc[i] = 0.0f;
+  const long long tid = (long long)blockIdx.x * kThreads + threadIdx.x;
+  const long long nthreads = (long long)gridDim.x * kThreads;
+#define B2_ACC(pp, tt)                         \
+  {                                            \
+    const float pb = (pp) > 0.5f ? 1.f : 0.f;  \
+    acc[0] += (pp);                            \
+    acc[1] += (tt);                            \
+    acc[2] = fmaf((pp), (tt), acc[2]);         \
+    acc[6] += pb;                              \
+    acc[7] = fmaf(pb, (tt), acc[7]);           \
+  }
+  if (VEC4) {
+    const long long n4 = n >> 2;
+    const float4* p4 = reinterpret_cast<const float4*>(p);
+    const float4* t4 = reinterpret_cast<const float4*>(t);
+    long long i = tid;
+    for (; i + nthreads < n4; i += 2 * nthreads) {
+      const float4 pa = ldg_stream_f4(p4 + i), pb2 = ldg_stream_f4(p4 + i + nthreads);
+      const float4 ta = ldg_stream_f4(t4 + i), tb = ldg_stream_f4(t4 + i + nthreads);
+      B2_ACC(pa.x, ta.x) B2_ACC(pa.y, ta.y) B2_ACC(pa.z, ta.z) B2_ACC(pa.w, ta.w)
+      B2_ACC(pb2.x, tb.x) B2_ACC(pb2.y, tb.y) B2_ACC(pb2.z, tb.z) B2_ACC(pb2.w, tb.w)
+    }
+    for (; i < n4; i += nthreads) {
+      const float4 pa = ldg_stream_f4(p4 + i);
+      const float4 ta = ldg_stream_f4(t4 + i);
+      B2_ACC(pa.x, ta.x) B2_ACC(pa.y, ta.y) B2_ACC(pa.z, ta.z) B2_ACC(pa.w, ta.w)
+    }
+    for (long long j = (n4 << 2) + tid; j < n; j += nthreads) B2_ACC(p[j], t[j])
+  } else {
+    for (long long j = tid; j < n; j += nthreads) B2_ACC(p[j], t[j])
+  }
+#undef B2_ACC
+  __shared__ double s_tot[kAcc];
+  double tot[kAcc];
+  if (grid_reduce(acc, ws, tot, s_tot) && threadIdx.x == 0) {
+    for (int i = 0; i < kAcc; ++i) stats[i] = tot[i];
+    write_confusion(stats, (double)n);
+    stats[B2SEG_S_LOSS] = 0.0;
+  }
+}
+
+int pick_blocks(long long n, int per_thread) {
+  long long b = (n + (long long)kThreads * per_thread - 1) / ((long long)kThreads * per_thread);
+  const long long cap = (long long)b2_num_sms() * 8;
+  if (b > cap) b = cap;
+  if (b > kMaxBlocks) b = kMaxBlocks;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+}  // namespace
+
+extern "C" size_t b2seg_seg_reduce_workspace_bytes(void) { return sizeof(ReduceWs); }
+
+extern "C" int b2seg_seg_loss_fwd(const float* logits, const float* target,
+                                  const float* weight_map, int64_t n,
+                                  const b2seg_loss_spec* spec, void* workspace, double* stats,
+                                  float* loss_out, float* coef, void* stream) {
+  B2_REQUIRE(logits && target && spec && workspace && stats && loss_out && coef,
+             "seg_loss_fwd: null argument");
+  B2_REQUIRE(n > 0, "seg_loss_fwd: n must be positive (got %lld)", (long long)n);
+  B2_REQUIRE(spec->bce_mode >= 0 && spec->bce_mode <= 3, "seg_loss_fwd: bad bce_mode %d",
+             spec->bce_mode);
+  const bool wmap = spec->bce_mode == 3 && spec->w_bce != 0.0f;
+  B2_REQUIRE(!wmap || weight_map, "seg_loss_fwd: bce_mode 3 needs a weight map");
+  B2_REQUIRE(spec->w_focal == 0.0f || spec->focal_gamma > 0.0f,
+             "seg_loss_fwd: focal_gamma must be > 0");
+  const bool focal = spec->w_focal != 0.0f;
+  const bool vec = aligned16(logits) && aligned16(target) && (!wmap || aligned16(weight_map));
+  LossSpecDev sd;
+  sd.s = *spec;
+  const int blocks = pick_blocks(n, 16);
+  cudaStream_t st = (cudaStream_t)stream;
+  ReduceWs* ws = (ReduceWs*)workspace;
+#define LAUNCH(F, W, V)                                                                      \
+  seg_loss_fwd_kernel<F, W, V><<<blocks, kThreads, 0, st>>>(logits, target, weight_map, n, sd, \
+                                                            ws, stats, loss_out, coef)
+  if (focal) {
+    if (wmap) { if (vec) LAUNCH(true, true, true); else LAUNCH(true, true, false); }
+    else      { if (vec) LAUNCH(true, false, true); else LAUNCH(true, false, false); }
+  } else {
+    if (wmap) { if (vec) LAUNCH(false, true, true); else LAUNCH(false, true, false); }
+    else      { if (vec) LAUNCH(false, false, true); else LAUNCH(false, false, false); }
+  }
+#undef LAUNCH
+  B2_CHECK_CUDA(cudaGetLastError());
+  return B2SEG_OK;
+}
+
+extern "C" int b2seg_seg_loss_bwd(const float* logits, const float* target,
+                                  const float* weight_map, int64_t n, const float* coef,
+                                  const float* grad_out, float* grad_logits, void* stream) {
+  B2_REQUIRE(logits && target && coef && grad_logits, "seg_loss_bwd: null argument");
+  B2_REQUIRE(n > 0, "seg_loss_bwd: n must be positive (got %lld)", (long long)n);
+  const bool wmap = weight_map != nullptr;
+  const bool vec = aligned16(logits) && aligned16(target) && aligned16(grad_logits) &&
+                   (!wmap || aligned16(weight_map));
+  const int blocks = pick_blocks(n, 8);
+  cudaStream_t st = (cudaStream_t)stream;
+  // The focal branch is selected on the host from nothing but pointers, so the
+  // general kernel is always used: F == 0 makes the focal term vanish and costs
+  // only ALU in an HBM-bound pass.
+#define LAUNCH(W, V)                                                                        \
+  seg_loss_bwd_kernel<true, W, V><<<blocks, kThreads, 0, st>>>(logits, target, weight_map, n, \
+                                                               coef, grad_out, grad_logits)
+  if (wmap) { if (vec) LAUNCH(true, true); else LAUNCH(true, false); }
+  else      { if (vec) LAUNCH(false, true); else LAUNCH(false, false); }
+#undef LAUNCH
+  B2_CHECK_CUDA(cudaGetLastError());
+  return B2SEG_OK;
+}
+
+extern "C" int b2seg_seg_metrics_from_probs(const float* probs, const float* target, int64_t n,
+                                            void* workspace, double* stats, void* stream) {
+  B2_REQUIRE(probs && target && workspace && stats, "seg_metrics: null argument");
+  B2_REQUIRE(n > 0, "seg_metrics: n must be positive (got %lld)", (long long)n);
+  const bool vec = aligned16(probs) && aligned16(target);
+  const int blocks = pick_blocks(n, 16);
+  cudaStream_t st = (cudaStream_t)stream;
+  ReduceWs* ws = (ReduceWs*)workspace;
+  if (vec)
+    seg_metrics_probs_kernel<true><<<blocks, kThreads, 0, st>>>(probs, target, n, ws, stats);
+  else
+    seg_metrics_probs_kernel<false><<<blocks, kThreads, 0, st>>>(probs, target, n, ws, stats);
+  B2_CHECK_CUDA(cudaGetLastError());
+  return B2SEG_OK;
+}

@@ -1,0 +1,389 @@
+// Tap-gather implicit GEMM for convolutions on tcgen05 tensor cores.
+//
+//   out[pix, col] = sum_{tap} sum_{c} src_tap[pix + off_tap, c] * W[tap][col][c]
+//
+// M = 128 output pixels (a wt x ht x nt brick of the NHWC pixel grid),
+// N = BLOCK_N output columns, K = taps x channels in chunks of 64.
+// The A operand never exists as an im2col matrix: for every (tap, channel
+// chunk) one rank-4 TMA box load with a shifted coordinate lands a 128 x 64
+// bf16 K-major tile in shared memory (128B swizzle); out-of-bounds pixels are
+// zero-filled by TMA, which is exactly the conv zero padding.  Weights arrive
+// as [tap][col][c] boxes.  One elected thread issues tcgen05.mma with the fp32
+// accumulator in TMEM; four epilogue warps read it back with tcgen05.ld, add
+// bias, emit per-channel BatchNorm partial sums (sum, sum of squares) and store
+// bf16 through a strided / pixel-shuffle address map.
+//
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM alloc + MMA
+// issuer, warps 2..5 = epilogue (TMEM lane quadrant = warp_id % 4).
+#include <new>
+#include <string.h>
+
+#include "ops.cuh"
+
+namespace {
+
+struct TapSub {
+  int ntaps;
+  int8_t src[B2SEG_MAX_TAPS], dh[B2SEG_MAX_TAPS], dw[B2SEG_MAX_TAPS], wt[B2SEG_MAX_TAPS];
+  long long out_off;
+};
+
+struct alignas(64) TapGemmParams {
+  CUtensorMap tmA[4];
+  CUtensorMap tmB;
+  TapSub sub[B2SEG_MAX_SUB];
+  int kchunks;
+  int wt, ht, nt, tilesW, tilesH, mtiles;
+  int on, oh, ow;
+  bf16* out;
+  long long osn, osh, osw, oqh, oqw;
+  int cq_shift;  // 30 = no pixel-shuffle groups
+  int ngemm;
+  const float* bias;
+  float* stats;
+  int accumulate;
+};
+
+constexpr int kThreadsTG = 192;
+constexpr int A_BYTES = 128 * 128;  // 128 pixels x 64 bf16
+
+template <int BLOCK_N, int NSTAGES>
+struct TGSmem {
+  static constexpr int B_BYTES = BLOCK_N * 128;
+  static constexpr int STAGE = A_BYTES + B_BYTES;
+  static constexpr int BAR_OFF = NSTAGES * STAGE;
+  static constexpr int TOTAL = BAR_OFF + (2 * NSTAGES + 1) * 8 + 16 + 1024 /*align slack*/;
+};
+
+template <int BLOCK_N, int NSTAGES>
+__global__ void __launch_bounds__(kThreadsTG)
+    tapgemm_kernel(const __grid_constant__ TapGemmParams p) {
+  using L = TGSmem<BLOCK_N, NSTAGES>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~(uintptr_t)1023);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::BAR_OFF);
+  uint64_t* empty_bar = full_bar + NSTAGES;
+  uint64_t* tmem_full = empty_bar + NSTAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const TapSub& sub = p.sub[blockIdx.z];
+  const int mtile = blockIdx.x;
+  const int tw = mtile % p.tilesW, th = (mtile / p.tilesW) % p.tilesH,
+            tn = mtile / (p.tilesW * p.tilesH);
+  const int w0 = tw * p.wt, h0 = th * p.ht, n0 = tn * p.nt;
+  const int col0 = blockIdx.y * BLOCK_N;
+  const int total_iters = sub.ntaps * p.kchunks;
+
+  if (warp == 0 && lane == 0) {
+    for (int i = 0; i < NSTAGES; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    mbar_init(tmem_full, 1);
+    fence_barrier_init();
+    tma_prefetch_desc(&p.tmB);
+    tma_prefetch_desc(&p.tmA[sub.src[0]]);
+  }
+  if (warp == 1) tmem_alloc<BLOCK_N>(tmem_slot);
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int it = 0;
+      for (int t = 0; t < sub.ntaps; ++t) {
+        const CUtensorMap* tmA = &p.tmA[sub.src[t]];
+        const int cw = w0 + sub.dw[t], ch = h0 + sub.dh[t], wtap = sub.wt[t];
+        for (int kc = 0; kc < p.kchunks; ++kc, ++it) {
+          const int s = it % NSTAGES;
+          const uint32_t ph = (uint32_t)(it / NSTAGES) & 1u;
+          mbar_wait(&empty_bar[s], ph ^ 1u);
+          mbar_expect_tx(&full_bar[s], L::STAGE);
+          uint8_t* sa = smem + s * L::STAGE;
+          tma_load_4d(sa, tmA, &full_bar[s], kc * 64, cw, ch, n0);
+          tma_load_3d(sa + A_BYTES, &p.tmB, &full_bar[s], kc * 64, col0, wtap);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(128, BLOCK_N, 0, 0);
+      for (int it = 0; it < total_iters; ++it) {
+        const int s = it % NSTAGES;
+        const uint32_t ph = (uint32_t)(it / NSTAGES) & 1u;
+        mbar_wait(&full_bar[s], ph);
+        tcgen05_fence_after();
+        const uint32_t sa = smem_u32(smem + s * L::STAGE);
+        const uint64_t adesc = umma_smem_desc(sa, 16, 1024);
+        const uint64_t bdesc = umma_smem_desc(sa + A_BYTES, 16, 1024);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)  // 4 x (K = 16 bf16 = 32 B) per 64-channel chunk
+          umma_bf16_ss(tmem_base, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
+                       (it | k) != 0 ? 1u : 0u);
+        tcgen05_commit(&empty_bar[s]);  // smem slot free once these MMAs retire
+      }
+      tcgen05_commit(tmem_full);
+    }
+  } else {
+    // ===================== epilogue =====================
+    const int wq = warp & 3;  // TMEM lane quadrant this warp may access
+    const int r = wq * 32 + lane;
+    const int hw = p.ht * p.wt;
+    const int ln = r / hw, lh = (r % hw) / p.wt, lw = r % p.wt;
+    const int pn = n0 + ln, phh = h0 + lh, pw = w0 + lw;
+    const bool row_ok = pn < p.on && phh < p.oh && pw < p.ow;
+    const long long row_off =
+        sub.out_off + (long long)pn * p.osn + (long long)phh * p.osh + (long long)pw * p.osw;
+    const int cq_mask = (1 << p.cq_shift) - 1;
+    float* stat_row = nullptr;
+    if (p.stats)
+      stat_row = p.stats + (size_t)(((size_t)blockIdx.z * p.mtiles + mtile) * 4 + wq) * 2 * p.ngemm;
+
+    mbar_wait(tmem_full, 0);
+    tcgen05_fence_after();
+#pragma unroll 1
+    for (int c = 0; c < BLOCK_N / 32; ++c) {
+      float v[32];
+      tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(c * 32), v);
+      const int colc = col0 + c * 32;
+      if (p.bias) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + ((colc + j) & cq_mask));
+      }
+      if (row_ok) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const int col = colc + g * 8;
+          const int q = col >> p.cq_shift;
+          bf16* dst = p.out + row_off + (long long)(q >> 1) * p.oqh + (long long)(q & 1) * p.oqw +
+                      (col & cq_mask);
+          float o[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] = v[g * 8 + j];
+          if (p.accumulate) {
+            const uint4 old = *reinterpret_cast<const uint4*>(dst);
+            const float2 a0 = bf2_to_f2(old.x), a1 = bf2_to_f2(old.y), a2 = bf2_to_f2(old.z),
+                         a3 = bf2_to_f2(old.w);
+            o[0] += a0.x; o[1] += a0.y; o[2] += a1.x; o[3] += a1.y;
+            o[4] += a2.x; o[5] += a2.y; o[6] += a3.x; o[7] += a3.y;
+          }
+          uint4 pk;
+          pk.x = f2_to_bf2(o[0], o[1]);
+          pk.y = f2_to_bf2(o[2], o[3]);
+          pk.z = f2_to_bf2(o[4], o[5]);
+          pk.w = f2_to_bf2(o[6], o[7]);
+          *reinterpret_cast<uint4*>(dst) = pk;
+        }
+      }
+      if (stat_row) {
+        float s1[32], s2[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const float x = row_ok ? v[j] : 0.0f;
+          s1[j] = x;
+          s2[j] = x * x;
+        }
+        const float a = warp_transpose_sum32(s1, lane);
+        const float b = warp_transpose_sum32(s2, lane);
+        stat_row[colc + lane] = a;
+        stat_row[p.ngemm + colc + lane] = b;
+      }
+    }
+    tcgen05_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    tmem_dealloc<BLOCK_N>(tmem_base);
+  }
+}
+
+struct TapGemmOp : b2seg_op {
+  TapGemmParams p;
+  dim3 grid;
+  int block_n, stages;
+  size_t smem;
+  const char* name() const override { return "tapgemm"; }
+  int run(cudaStream_t st) override {
+#define TG_LAUNCH(BN, NS)                                                            \
+  tapgemm_kernel<BN, NS><<<grid, kThreadsTG, TGSmem<BN, NS>::TOTAL, st>>>(p)
+    if (block_n == 128) TG_LAUNCH(128, 3);
+    else if (block_n == 64) TG_LAUNCH(64, 4);
+    else TG_LAUNCH(32, 4);
+#undef TG_LAUNCH
+    B2_CHECK_CUDA(cudaGetLastError());
+    return B2SEG_OK;
+  }
+};
+
+template <int BN, int NS>
+int set_smem_attr() {
+  static bool done = false;
+  if (!done) {
+    B2_CHECK_CUDA(cudaFuncSetAttribute(tapgemm_kernel<BN, NS>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       TGSmem<BN, NS>::TOTAL));
+    done = true;
+  }
+  return B2SEG_OK;
+}
+
+int ilog2_exact(int x) {
+  int s = 0;
+  while ((1 << s) < x) ++s;
+  return (1 << s) == x ? s : -1;
+}
+
+}  // namespace
+
+int b2_view_tmap(CUtensorMap* out, const b2seg_tensor4* v, int wt, int ht, int nt) {
+  const uint64_t dims[4] = {(uint64_t)v->c, (uint64_t)v->w, (uint64_t)v->h, (uint64_t)v->n};
+  const uint64_t strides[3] = {(uint64_t)v->sw * 2, (uint64_t)v->sh * 2, (uint64_t)v->sn * 2};
+  const uint32_t box[4] = {64, (uint32_t)wt, (uint32_t)ht, (uint32_t)nt};
+  return b2_encode_tmap_bf16(out, v->ptr, 4, dims, strides, box, 1);
+}
+
+extern "C" int b2seg_tapgemm_stat_rows(int on, int oh, int ow) {
+  int wt, ht, nt;
+  b2_pick_pixel_tile(on, oh, ow, &wt, &ht, &nt);
+  const int tiles = ((ow + wt - 1) / wt) * ((oh + ht - 1) / ht) * ((on + nt - 1) / nt);
+  return tiles * 4;
+}
+
+extern "C" int b2seg_tapgemm_create(const b2seg_tapgemm_desc* d, b2seg_op** out) {
+  B2_REQUIRE(d && out, "tapgemm_create: null argument");
+  B2_REQUIRE(d->nsrc >= 1 && d->nsrc <= 4, "tapgemm_create: nsrc %d", d->nsrc);
+  B2_REQUIRE(d->nsub >= 1 && d->nsub <= B2SEG_MAX_SUB, "tapgemm_create: nsub %d", d->nsub);
+  B2_REQUIRE(d->weights && d->out, "tapgemm_create: null weights/out");
+  B2_REQUIRE(d->cin >= 8 && d->cin % 8 == 0, "tapgemm_create: cin %d must be a multiple of 8",
+             d->cin);
+  B2_REQUIRE(d->ngemm >= 32 && d->ngemm % 32 == 0,
+             "tapgemm_create: ngemm %d must be a multiple of 32", d->ngemm);
+  B2_REQUIRE(d->on > 0 && d->oh > 0 && d->ow > 0, "tapgemm_create: empty pixel grid");
+  B2_REQUIRE(d->stats == nullptr || d->nsub == 1, "tapgemm_create: stats need nsub == 1");
+  int cq_shift = 30;
+  if (d->cq > 0) {
+    cq_shift = ilog2_exact(d->cq);
+    B2_REQUIRE(cq_shift >= 3, "tapgemm_create: cq %d must be a power of two >= 8", d->cq);
+  }
+  auto* op = new (std::nothrow) TapGemmOp();
+  B2_REQUIRE(op, "tapgemm_create: out of host memory");
+  TapGemmParams& p = op->p;
+  memset(&p, 0, sizeof(p));
+  b2_pick_pixel_tile(d->on, d->oh, d->ow, &p.wt, &p.ht, &p.nt);
+  p.tilesW = (d->ow + p.wt - 1) / p.wt;
+  p.tilesH = (d->oh + p.ht - 1) / p.ht;
+  const int tilesN = (d->on + p.nt - 1) / p.nt;
+  p.mtiles = p.tilesW * p.tilesH * tilesN;
+  for (int i = 0; i < d->nsrc; ++i) {
+    const b2seg_tensor4& v = d->src[i];
+    if (v.c != d->cin || !v.ptr) {
+      b2seg_set_error("tapgemm_create: src[%d] has %d channels, expected %d", i, v.c, d->cin);
+      delete op;
+      return B2SEG_EINVAL;
+    }
+    int rc = b2_view_tmap(&p.tmA[i], &v, p.wt, p.ht, p.nt);
+    if (rc != B2SEG_OK) { delete op; return rc; }
+  }
+  for (int i = d->nsrc; i < 4; ++i) p.tmA[i] = p.tmA[0];
+
+  const int nm = d->ngemm;
+  int bn;
+  if (nm % 128 == 0 && (long long)p.mtiles * (nm / 128) >= b2_num_sms()) bn = 128;
+  else if (nm % 64 == 0) bn = 64;
+  else bn = 32;
+  op->block_n = bn;
+  {
+    const uint64_t dims[3] = {(uint64_t)d->cin, (uint64_t)d->ngemm, (uint64_t)d->wtaps};
+    const uint64_t strides[2] = {(uint64_t)d->cin * 2, (uint64_t)d->cin * d->ngemm * 2};
+    const uint32_t box[3] = {64, (uint32_t)bn, 1};
+    int rc = b2_encode_tmap_bf16(&p.tmB, d->weights, 3, dims, strides, box, 1);
+    if (rc != B2SEG_OK) { delete op; return rc; }
+  }
+  for (int s = 0; s < d->nsub; ++s) {
+    const auto& ds = d->sub[s];
+    if (ds.ntaps < 1 || ds.ntaps > B2SEG_MAX_TAPS) {
+      b2seg_set_error("tapgemm_create: sub %d ntaps %d", s, ds.ntaps);
+      delete op;
+      return B2SEG_EINVAL;
+    }
+    p.sub[s].ntaps = ds.ntaps;
+    p.sub[s].out_off = ds.out_offset;
+    for (int t = 0; t < ds.ntaps; ++t) {
+      if (ds.taps[t].src < 0 || ds.taps[t].src >= d->nsrc || ds.taps[t].wtap < 0 ||
+          ds.taps[t].wtap >= d->wtaps) {
+        b2seg_set_error("tapgemm_create: sub %d tap %d out of range", s, t);
+        delete op;
+        return B2SEG_EINVAL;
+      }
+      p.sub[s].src[t] = ds.taps[t].src;
+      p.sub[s].dh[t] = ds.taps[t].dh;
+      p.sub[s].dw[t] = ds.taps[t].dw;
+      p.sub[s].wt[t] = ds.taps[t].wtap;
+    }
+  }
+  p.kchunks = (d->cin + 63) / 64;
+  p.on = d->on; p.oh = d->oh; p.ow = d->ow;
+  p.out = (bf16*)d->out;
+  p.osn = d->osn; p.osh = d->osh; p.osw = d->osw;
+  p.oqh = d->oqh; p.oqw = d->oqw;
+  p.cq_shift = cq_shift;
+  p.ngemm = d->ngemm;
+  p.bias = d->bias;
+  p.stats = d->stats;
+  p.accumulate = d->accumulate;
+  op->grid = dim3(p.mtiles, d->ngemm / bn, d->nsub);
+  int rc;
+  if (bn == 128) rc = set_smem_attr<128, 3>();
+  else if (bn == 64) rc = set_smem_attr<64, 4>();
+  else rc = set_smem_attr<32, 4>();
+  if (rc != B2SEG_OK) { delete op; return rc; }
+  *out = op;
+  return B2SEG_OK;
+}
+
+// ---- generic op / sequence plumbing ----------------------------------------------
+extern "C" int b2seg_op_run(b2seg_op* op, void* stream) {
+  B2_REQUIRE(op, "op_run: null op");
+  return op->run((cudaStream_t)stream);
+}
+extern "C" int b2seg_op_destroy(b2seg_op* op) {
+  delete op;
+  return B2SEG_OK;
+}
+extern "C" int b2seg_op_launches(const b2seg_op* op) { return op ? op->launches() : 0; }
+extern "C" int b2seg_seq_create(b2seg_seq** out) {
+  B2_REQUIRE(out, "seq_create: null");
+  *out = new (std::nothrow) b2seg_seq();
+  B2_REQUIRE(*out, "seq_create: out of host memory");
+  return B2SEG_OK;
+}
+extern "C" int b2seg_seq_append(b2seg_seq* seq, b2seg_op* op) {
+  B2_REQUIRE(seq && op, "seq_append: null");
+  seq->ops.push_back(op);
+  return B2SEG_OK;
+}
+extern "C" int b2seg_seq_run(b2seg_seq* seq, void* stream) {
+  B2_REQUIRE(seq, "seq_run: null");
+  for (b2seg_op* op : seq->ops) {
+    int rc = op->run((cudaStream_t)stream);
+    if (rc != B2SEG_OK) return rc;
+  }
+  return B2SEG_OK;
+}
+extern "C" int b2seg_seq_launches(const b2seg_seq* seq) {
+  int n = 0;
+  if (seq)
+    for (const b2seg_op* op : seq->ops) n += op->launches();
+  return n;
+}
+extern "C" int b2seg_seq_destroy(b2seg_seq* seq) {
+  delete seq;
+  return B2SEG_OK;
+}

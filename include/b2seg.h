@@ -1,0 +1,249 @@
+/*
+ * b2seg.h — C ABI of libb2seg.so, the sm_100a (B200) kernels behind the
+ * segmentation training step of SwagMag1213/image-segmentation-project.
+ *
+ * The reference has no FFI of its own: its hot path sits behind a Python module
+ * API.  Each entry point below names the reference call site(s) it replaces
+ * (file:line under the reference checkout).  The Python host layer
+ * (image-segmentation-project_b200/b2seg/) binds these with ctypes; the stub a
+ * reference maintainer would add is shown in INTEGRATION.md.
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes; no torch / C++ types.
+ *   - every function returns 0 (B2SEG_OK) or a negative B2SEG_E* code; the
+ *     message is available from b2seg_last_error() (thread-local).
+ *   - tensor arguments are raw DEVICE pointers into caller-owned memory unless
+ *     a parameter is documented as host memory.  The library never allocates
+ *     tensors, never synchronises the device implicitly and never takes
+ *     ownership.  Scratch comes from caller-provided workspaces.
+ *   - `stream` is a cudaStream_t passed as void*; all work is enqueued there,
+ *     so whole steps are CUDA-graph capturable.
+ *   - there is no CPU fallback: without a Blackwell GPU every compute entry
+ *     point fails with B2SEG_ECUDA.
+ */
+#ifndef B2SEG_H_
+#define B2SEG_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2SEG_ABI_VERSION 1
+
+#define B2SEG_OK 0
+#define B2SEG_EINVAL (-1)  /* bad argument / unsupported shape            */
+#define B2SEG_ECUDA (-2)   /* CUDA runtime or driver error                 */
+#define B2SEG_ENOMEM (-3)  /* workspace too small                          */
+
+int b2seg_abi_version(void);
+const char* b2seg_last_error(void);
+/* Fills name[len] with the device name, *sms with the SM count, *cc with
+ * major*10+minor.  Fails with B2SEG_ECUDA when no CUDA device is usable. */
+int b2seg_device_info(char* name, int len, int* sms, int* cc);
+
+/* ======================================================================== *
+ *  1. Per-pixel segmentation losses + metrics                               *
+ *     replaces losses.py:13-171, 322-342 (Dice, BCE, WeightedBCE,          *
+ *     BalancedBCE, Focal, Tversky, FocalTversky, SensitivitySpecificity,   *
+ *     LogCoshDice, Combo, TripleCombo), utils.py:26-56 (dice_loss,         *
+ *     combo_loss) and utils.py:120-151 (calculate_metrics).                *
+ * ======================================================================== */
+
+/* Every closed-form loss of the reference is a weighted sum of these terms;
+ * a term with weight 0 costs nothing.  Field meanings follow the reference
+ * constructors (losses.py:345-403 for the factory defaults). */
+typedef struct b2seg_loss_spec {
+  float w_dice;          /* DiceLoss weight;            losses.py:19-28   */
+  float w_logcosh_dice;  /* log(cosh(dice_loss)) weight; losses.py:156-158 */
+  float dice_smooth;
+  float w_tversky;       /* (1 - Tversky)^tv_gamma;     losses.py:97-122  */
+  float tv_alpha, tv_beta, tv_smooth, tv_gamma;
+  float w_sens_spec;     /* losses.py:132-147 */
+  float ss_w, ss_eps;
+  float w_bce;           /* losses.py:36-65 */
+  int32_t bce_mode;      /* 0 plain mean, 1 weighted (beta), 2 balanced, 3 per-pixel weight map */
+  float bce_beta;
+  float w_focal;         /* losses.py:76-86 (reduction='mean') */
+  float focal_alpha, focal_gamma;
+} b2seg_loss_spec;
+
+/* Layout of the device-side result block written by the forward kernels
+ * (double[B2SEG_STATS_LEN]).  Sums are over all n pixels of the batch. */
+enum {
+  B2SEG_S_P = 0,       /* sum sigmoid(x)                          */
+  B2SEG_S_T = 1,       /* sum t                                   */
+  B2SEG_S_PT = 2,      /* sum sigmoid(x)*t                        */
+  B2SEG_S_BCE = 3,     /* sum bce_i (times weight map in mode 3)  */
+  B2SEG_S_BCE_T = 4,   /* sum bce_i*t                             */
+  B2SEG_S_FOCAL = 5,   /* sum (1-pt)^gamma * bce_i                */
+  B2SEG_S_PB = 6,      /* sum [sigmoid(x) > 0.5]                  */
+  B2SEG_S_PB_T = 7,    /* sum [sigmoid(x) > 0.5]*t                */
+  B2SEG_S_N = 8,       /* n                                       */
+  B2SEG_S_LOSS = 9,    /* loss value                              */
+  B2SEG_S_TP = 10, B2SEG_S_FP = 11, B2SEG_S_FN = 12, B2SEG_S_TN = 13,
+  B2SEG_STATS_LEN = 16
+};
+#define B2SEG_LOSS_COEF_LEN 8
+
+/* Scratch for the two-level reduction (must be zero-filled ONCE by the caller
+ * before first use; the kernels leave it zeroed). */
+size_t b2seg_seg_reduce_workspace_bytes(void);
+
+/* Forward: one pass over logits+targets (8 B/px algorithmic).  Writes
+ * stats[16] (double), loss_out[1] (float) and coef[8] (float; consumed by
+ * b2seg_seg_loss_bwd without a host round trip).  weight_map may be NULL
+ * unless spec->bce_mode == 3. */
+int b2seg_seg_loss_fwd(const float* logits, const float* target, const float* weight_map,
+                       int64_t n, const b2seg_loss_spec* spec /*host*/, void* workspace,
+                       double* stats, float* loss_out, float* coef, void* stream);
+
+/* Backward: grad_logits[i] = grad_out * dL/dlogits[i] (12 B/px algorithmic).
+ * grad_out is a DEVICE scalar (NULL means 1). */
+int b2seg_seg_loss_bwd(const float* logits, const float* target, const float* weight_map,
+                       int64_t n, const float* coef, const float* grad_out, float* grad_logits,
+                       void* stream);
+
+/* calculate_metrics(pred, target) of utils.py:120-151: `probs` are
+ * probabilities; fills stats[S_PB, S_PB_T, S_T, S_N, S_TP..S_TN]. */
+int b2seg_seg_metrics_from_probs(const float* probs, const float* target, int64_t n,
+                                 void* workspace, double* stats, void* stream);
+
+/* ======================================================================== *
+ *  2. Geometric augmentation gather                                         *
+ *     replaces the cv2 calls albumentations bottoms out in at               *
+ *     dataset.py:148-154,184 and forward_selection_integration.py:73-105.   *
+ * ======================================================================== */
+enum {
+  B2SEG_AUG_HFLIP = 0,     /* cv2.flip(img, 1)            */
+  B2SEG_AUG_VFLIP = 1,     /* cv2.flip(img, 0)            */
+  B2SEG_AUG_ROT90 = 2,     /* np.rot90(img, k), k in arg  */
+  B2SEG_AUG_TRANSPOSE = 3, /* img.T                       */
+};
+enum { B2SEG_INTERP_NEAREST = 0, B2SEG_INTERP_LINEAR = 1 };
+enum { B2SEG_BORDER_CONSTANT = 0, B2SEG_BORDER_REFLECT = 1, B2SEG_BORDER_REFLECT101 = 2 };
+
+/* Exact index permutation of `planes` uint8 planes of size h x w (image and
+ * mask stacked).  Output plane size is (w x h) for odd rot90 k and transpose. */
+int b2seg_aug_permute_u8(const uint8_t* src, uint8_t* dst, int planes, int h, int w, int mode,
+                         int k, void* stream);
+
+/* cv2.warpAffine(src, M, (w,h), flags=interp|WARP_INVERSE_MAP-free form):
+ * `minv` (host, 6 doubles) is the already-inverted 2x3 matrix mapping
+ * destination (x,y) to source coordinates, exactly what cv2 computes from M.
+ * Bilinear uses cv2's fixed-point scheme (5-bit coordinate fractions, 15-bit
+ * weights) so uint8 results match cv2 bit-for-bit away from rounding ties. */
+int b2seg_aug_warp_affine_u8(const uint8_t* src, uint8_t* dst, int planes, int h, int w,
+                             const double* minv /*host[6]*/, int interp, int border,
+                             int border_value, void* stream);
+
+/* cv2.remap(src, map_x, map_y, interp, border): float32 absolute maps (device). */
+int b2seg_aug_remap_u8(const uint8_t* src, uint8_t* dst, int planes, int h, int w,
+                       const float* map_x, const float* map_y, int interp, int border,
+                       int border_value, void* stream);
+
+/* ======================================================================== *
+ *  3. Planned ops: created once per (pointers, shapes), replayed per step.  *
+ *     TMA descriptors are encoded at creation, so run() is launch-only and  *
+ *     CUDA-graph capturable.                                                 *
+ * ======================================================================== */
+typedef struct b2seg_op b2seg_op;   /* opaque */
+typedef struct b2seg_seq b2seg_seq; /* opaque ordered list of ops */
+
+int b2seg_op_run(b2seg_op* op, void* stream);
+int b2seg_op_destroy(b2seg_op* op);
+int b2seg_op_launches(const b2seg_op* op);
+int b2seg_seq_create(b2seg_seq** out);
+int b2seg_seq_append(b2seg_seq* seq, b2seg_op* op); /* does not take ownership */
+int b2seg_seq_run(b2seg_seq* seq, void* stream);
+int b2seg_seq_launches(const b2seg_seq* seq);
+int b2seg_seq_destroy(b2seg_seq* seq);
+
+/* NHWC bf16 activation view; strides in ELEMENTS, channel stride is 1.  A
+ * channel slice of a wider buffer (fused skip-concat) or a stride-2 phase of a
+ * feature map is just another view. */
+typedef struct b2seg_tensor4 {
+  void* ptr;
+  int32_t n, h, w, c;
+  int64_t sn, sh, sw;
+} b2seg_tensor4;
+
+/* One filter tap of a tap-gather GEMM: which source view it reads, the pixel
+ * offset applied to the output pixel coordinate, and which weight slab. */
+typedef struct b2seg_tap {
+  int8_t src, dh, dw, wtap;
+} b2seg_tap;
+
+#define B2SEG_MAX_TAPS 9
+#define B2SEG_MAX_SUB 4
+
+/* Tap-gather implicit GEMM on tcgen05/TMEM, fed by TMA:
+ *   out[pix, col] (+)= sum_taps sum_c src[tap.src][pix + (tap.dh,tap.dw), c] * W[tap.wtap][col][c]
+ * replaces torch conv2d / conv_transpose2d and their data gradients:
+ *   advanced_models.py:76,90-100,158-160,199,202 (Conv2d 3x3/1x1, ConvTranspose2d 2x2 s2),
+ *   torchvision resnet BasicBlock/Bottleneck convs (advanced_models.py:81-87,111-117),
+ *   AttentionGate 1x1 convs (advanced_models.py:11,16) and, with repacked weights,
+ *   the dgrad half of convolution_backward triggered at train.py:48.
+ * Stride-2 convs read four phase views; ConvTranspose writes through the
+ * pixel-shuffle addressing (cq, oqh, oqw) straight into a channel slice of the
+ * decoder's concat buffer (advanced_models.py:288-333 torch.cat fused away). */
+typedef struct b2seg_tapgemm_desc {
+  b2seg_tensor4 src[4];
+  int32_t nsrc;
+  int32_t nsub;                 /* independent sub-problems (e.g. 4 dgrad phases) */
+  struct {
+    int32_t ntaps;
+    b2seg_tap taps[B2SEG_MAX_TAPS];
+    int64_t out_offset;         /* elements added to `out` for this sub-problem */
+  } sub[B2SEG_MAX_SUB];
+  const void* weights;          /* bf16 [wtaps][ngemm][cin] */
+  int32_t wtaps, ngemm, cin;
+  int32_t on, oh, ow;           /* iteration (output pixel) grid */
+  void* out;                    /* bf16 */
+  int64_t osn, osh, osw;        /* output strides, elements */
+  int32_t cq;                   /* columns per pixel-shuffle group (power of 2); 0 = none */
+  int64_t oqh, oqw;             /* extra offset for group q: (q>>1)*oqh + (q&1)*oqw */
+  const float* bias;            /* fp32 [cq ? cq : ngemm] or NULL */
+  float* stats;                 /* fp32 [stat_rows][2][ngemm] partial (sum, sumsq) or NULL */
+  int32_t accumulate;           /* out += result instead of out = result */
+} b2seg_tapgemm_desc;
+
+int b2seg_tapgemm_create(const b2seg_tapgemm_desc* desc /*host*/, b2seg_op** out);
+/* number of partial-statistics rows a tapgemm op with this iteration grid writes */
+int b2seg_tapgemm_stat_rows(int on, int oh, int ow);
+
+/* Weight-gradient GEMM on tcgen05 (both operands MN-major straight from the
+ * NHWC tiles TMA lands), split-K over pixel tiles with a deterministic
+ * two-phase reduction:
+ *   G[tap][i][j] = sum_pix a_src[tap.src][pix + (tap.dh,tap.dw), i] * b_src[pix, j]
+ *   grad[tap.out_base + i*row_stride + j*col_stride] (+)= G[tap][i][j]   (fp32)
+ * replaces the wgrad half of convolution_backward for Conv2d (a = layer input,
+ * b = dY) and ConvTranspose2d (a = dY phases, b = layer input) reached from
+ * loss.backward() at train.py:48. */
+typedef struct b2seg_wgrad_desc {
+  b2seg_tensor4 a_src[4];
+  int32_t na_src;
+  b2seg_tensor4 b_src;
+  int32_t ntaps;
+  struct {
+    int8_t src, dh, dw, pad;
+    int64_t out_base;           /* fp32 elements into `grad` */
+  } taps[B2SEG_MAX_TAPS];
+  int32_t pn, ph, pw;           /* pixel grid reduced over (K dimension) */
+  float* grad;                  /* fp32 destination (e.g. an OIHW parameter gradient) */
+  int64_t row_stride, col_stride;
+  int32_t accumulate;           /* grad += instead of grad = */
+  void* workspace;              /* fp32 split-K partials, >= b2seg_wgrad_workspace_bytes() */
+  size_t workspace_bytes;
+} b2seg_wgrad_desc;
+
+size_t b2seg_wgrad_workspace_bytes(int a_channels, int b_channels, int ntaps, int pn, int ph,
+                                   int pw);
+int b2seg_wgrad_create(const b2seg_wgrad_desc* desc /*host*/, b2seg_op** out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2SEG_H_ */

@@ -1,0 +1,151 @@
+"""tcgen05 convolution kernels (tap-gather GEMM + weight-gradient GEMM) vs a torch-CPU fp32
+oracle evaluated on the same bf16-rounded operands.
+
+Tolerance: products of bf16 values are exact in fp32 and both sides accumulate in fp32, so the
+only differences are summation order and the final bf16 rounding of the output:
+|err| <= 2^-8 * |ref| + 1e-3 * sqrt(K)-scaled absolute slack.
+"""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _nhwc(t):  # NCHW fp32 cpu -> NHWC bf16
+    return t.permute(0, 2, 3, 1).contiguous().to(torch.bfloat16)
+
+
+def _nchw(t):  # NHWC (any) -> NCHW fp32 cpu
+    return t.float().cpu().permute(0, 3, 1, 2).contiguous()
+
+
+def _rb(t):  # round to bf16, keep fp32
+    return t.to(torch.bfloat16).float()
+
+
+def _close(got, ref, k):
+    tol = 2.0 ** -7 * ref.abs() + 2e-3 * ref.abs().max().clamp(min=1e-3)
+    bad = (got - ref).abs() > tol
+    assert not bad.any(), (int(bad.sum()), float((got - ref).abs().max()), float(ref.abs().max()), k)
+
+
+CASES = [
+    # n, h, w, cin, cout, k, stride
+    (2, 16, 16, 64, 64, 3, 1),
+    (4, 8, 8, 128, 256, 3, 1),
+    (1, 32, 48, 96, 32, 3, 1),     # decoder1: cin not a multiple of 64, narrow N
+    (2, 12, 20, 32, 32, 3, 1),     # ragged tiles, cin < 64
+    (3, 3, 3, 512, 512, 3, 1),     # 96-px input at enc4: tiny odd grid
+    (2, 16, 16, 64, 128, 3, 2),
+    (2, 32, 32, 64, 128, 1, 2),    # downsample 1x1 s2
+    (2, 16, 16, 256, 128, 1, 1),   # attention W_g
+    (8, 64, 64, 64, 64, 3, 1),     # many tiles -> BLOCK_N path with >= SM-count CTAs
+    (4, 32, 32, 128, 128, 3, 1),
+]
+
+
+@pytest.mark.parametrize("n,h,w,cin,cout,k,stride", CASES)
+def test_conv_fprop_dgrad_wgrad(cuda, n, h, w, cin, cout, k, stride):
+    from b2seg import convops as co
+    g = torch.Generator().manual_seed(n * 1000 + h * 10 + cin + cout + k + stride)
+    x = _rb(torch.randn(n, cin, h, w, generator=g))
+    wt = _rb(torch.randn(cout, cin, k, k, generator=g) / (cin * k * k) ** 0.5)
+    bias = torch.randn(cout, generator=g)
+    pad = k // 2
+    ho, wo = h // stride, w // stride
+
+    # ---------------- fprop (+bias, + BatchNorm partial statistics) ----------------
+    y_ref = F.conv2d(x, wt, bias, stride, pad)
+    xd = _nhwc(x).to(cuda)
+    yd = torch.zeros(n, ho, wo, cout, dtype=torch.bfloat16, device=cuda)
+    rows = co.stat_rows(n, ho, wo)
+    stats = torch.zeros(rows, 2, cout, dtype=torch.float32, device=cuda)
+    wp = co.pack_conv_fprop(wt.to(cuda))
+    op = co.conv_fprop(co.View(xd), wp, k, stride, co.View(yd), bias=bias.to(cuda), stats=stats)
+    op.run()
+    torch.cuda.synchronize()
+    _close(_nchw(yd), y_ref, "fprop")
+    s = stats.double().sum(0).cpu()
+    np.testing.assert_allclose(s[0].numpy(), y_ref.double().sum((0, 2, 3)).numpy(), rtol=1e-3,
+                               atol=1e-2 * float(y_ref.abs().max()) * (n * ho * wo) ** 0.5)
+    np.testing.assert_allclose(s[1].numpy(), (y_ref.double() ** 2).sum((0, 2, 3)).numpy(), rtol=2e-3)
+
+    # ---------------- dgrad ----------------
+    dy = _rb(torch.randn(n, cout, ho, wo, generator=g))
+    dx_ref = F.conv_transpose2d(dy, wt, None, stride, pad, output_padding=stride - 1)
+    dyd = _nhwc(dy).to(cuda)
+    dxd = torch.zeros(n, h, w, cin, dtype=torch.bfloat16, device=cuda)
+    wd = co.pack_conv_dgrad(wt.to(cuda))
+    co.conv_dgrad(co.View(dyd), wd, k, stride, co.View(dxd)).run()
+    torch.cuda.synchronize()
+    _close(_nchw(dxd), dx_ref, "dgrad")
+    # accumulate mode: running it again on top doubles the result
+    co.conv_dgrad(co.View(dyd), wd, k, stride, co.View(dxd), accumulate=True).run()
+    torch.cuda.synchronize()
+    got2 = _nchw(dxd)
+    ref2 = _rb(dx_ref) * 2
+    assert (got2 - ref2).abs().max() <= 2.0 ** -6 * ref2.abs().max() + 1e-3
+
+    # ---------------- wgrad ----------------
+    gw_ref = torch.nn.grad.conv2d_weight(x, wt.shape, dy, stride, pad)
+    gw = torch.full((cout, cin, k, k), 7.0, dtype=torch.float32, device=cuda)
+    ws = torch.empty(co.wgrad_workspace_bytes(cin, cout, k * k, n, ho, wo) // 4 + 4, dtype=torch.float32,
+                     device=cuda)
+    co.conv_wgrad(co.View(xd), co.View(dyd), k, stride, gw, ws).run()
+    torch.cuda.synchronize()
+    scale = float(gw_ref.abs().max())
+    np.testing.assert_allclose(gw.cpu().numpy(), gw_ref.numpy(), rtol=2e-3, atol=2e-4 * scale)
+
+
+@pytest.mark.parametrize("n,h,w,cin,cout,skip", [(2, 8, 8, 128, 64, 64), (1, 16, 24, 32, 16, 0),
+                                                  (4, 4, 4, 512, 256, 256), (2, 64, 64, 64, 32, 64)])
+def test_conv_transpose_into_concat_slice(cuda, n, h, w, cin, cout, skip):
+    """ConvTranspose2d(k2,s2) written straight into channels [skip, skip+cout) of the concat
+    buffer (advanced_models.py:284-333: torch.cat((skip, up), 1) fused away), + its gradients."""
+    from b2seg import convops as co
+    g = torch.Generator().manual_seed(cin + cout + h)
+    x = _rb(torch.randn(n, cin, h, w, generator=g))
+    wt = _rb(torch.randn(cin, cout, 2, 2, generator=g) / cin ** 0.5)
+    bias = torch.randn(cout, generator=g)
+    y_ref = F.conv_transpose2d(x, wt, bias, 2)
+    xd = _nhwc(x).to(cuda)
+    cat = torch.full((n, 2 * h, 2 * w, skip + cout), 3.0, dtype=torch.bfloat16, device=cuda)
+    co.convT_fprop(co.View(xd), co.pack_convT_fprop(wt.to(cuda)), co.View(cat, skip, cout),
+                   bias=bias.to(cuda)).run()
+    torch.cuda.synchronize()
+    _close(_nchw(cat[..., skip:]), y_ref, "convT")
+    if skip:
+        assert bool((cat[..., :skip] == 3.0).all())   # the skip slice is untouched
+
+    dcat = _rb(torch.randn(n, skip + cout, 2 * h, 2 * w, generator=g))
+    dy = dcat[:, skip:]
+    xr = x.clone().requires_grad_(True)
+    wr = wt.clone().requires_grad_(True)
+    F.conv_transpose2d(xr, wr, bias, 2).backward(dy)
+    dcd = _nhwc(dcat).to(cuda)
+    dxd = torch.zeros(n, h, w, cin, dtype=torch.bfloat16, device=cuda)
+    co.convT_dgrad(co.View(dcd, skip, cout), co.pack_convT_dgrad(wt.to(cuda)), co.View(dxd)).run()
+    gw = torch.zeros(cin, cout, 2, 2, dtype=torch.float32, device=cuda)
+    ws = torch.empty(co.wgrad_workspace_bytes(cout, cin, 4, n, h, w) // 4 + 4, dtype=torch.float32, device=cuda)
+    co.convT_wgrad(co.View(xd), co.View(dcd, skip, cout), gw, ws).run()
+    torch.cuda.synchronize()
+    _close(_nchw(dxd), xr.grad, "convT_dgrad")
+    np.testing.assert_allclose(gw.cpu().numpy(), wr.grad.numpy(), rtol=2e-3,
+                               atol=2e-4 * float(wr.grad.abs().max()))
+
+
+def test_seq_replays_ops(cuda):
+    from b2seg import convops as co
+    x = torch.randn(2, 16, 16, 64, device=cuda).to(torch.bfloat16)
+    w1 = co.pack_conv_fprop(torch.randn(64, 64, 3, 3, device=cuda) / 24)
+    y1 = torch.zeros_like(x)
+    y2 = torch.zeros_like(x)
+    seq = co.Seq([co.conv_fprop(co.View(x), w1, 3, 1, co.View(y1)), co.conv_fprop(co.View(y1), w1, 3, 1, co.View(y2))])
+    assert seq.launches == 2
+    seq.run()
+    torch.cuda.synchronize()
+    ref = F.conv2d(F.conv2d(x.float().permute(0, 3, 1, 2), w1.float().reshape(3, 3, 64, 64).permute(2, 3, 0, 1), None, 1, 1)
+                   .to(torch.bfloat16).float(), w1.float().reshape(3, 3, 64, 64).permute(2, 3, 0, 1), None, 1, 1)
+    _close(y2.float().permute(0, 3, 1, 2).cpu(), ref.cpu(), "seq")
