@@ -81,6 +81,23 @@ class WgradDesc(C.Structure):
     ]
 
 
+class EwDesc(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("p", C.c_void_p * 10), ("i", C.c_int64 * 10), ("f", C.c_float * 4)]
+
+
+class PackJob(C.Structure):
+    _fields_ = [("inp", C.c_void_p), ("out", C.c_void_p), ("T", C.c_int32), ("A", C.c_int32),
+                ("B", C.c_int32), ("pad", C.c_int32), ("sa", C.c_int64), ("sb", C.c_int64),
+                ("st", C.c_int64), ("start", C.c_int64)]
+
+
+EW_MAX_PARTIAL_ROWS = 592
+(EW_BN_FINALIZE, EW_BN_APPLY, EW_BN_BWD_REDUCE, EW_BN_BWD_FINALIZE, EW_BN_BWD_APPLY, EW_MAXPOOL_FWD,
+ EW_MAXPOOL_BWD, EW_STEM_FWD, EW_STEM_WGRAD, EW_DOT1_FWD, EW_DOT1_BWD, EW_COLSUM_FINALIZE, EW_COLSUM,
+ EW_PACK, EW_GATE_APPLY, EW_GATE_BWD, EW_SE_POOL, EW_SE_MLP, EW_SE_SCALE, EW_SE_BWD_REDUCE,
+ EW_SE_MLP_BWD, EW_SE_BWD_APPLY, EW_FILL) = range(1, 24)
+
+
 # ------------------------------------------------------------- signatures ----
 _vp, _i, _i64, _sz = C.c_void_p, C.c_int, C.c_int64, C.c_size_t
 _SIGS = {
@@ -106,6 +123,10 @@ _SIGS = {
     "b2seg_tapgemm_stat_rows": (C.c_int, [_i, _i, _i]),
     "b2seg_wgrad_workspace_bytes": (_sz, [_i, _i, _i, _i, _i, _i]),
     "b2seg_wgrad_create": (C.c_int, [C.POINTER(WgradDesc), C.POINTER(_vp)]),
+    "b2seg_ew_create": (C.c_int, [C.POINTER(EwDesc), C.POINTER(_vp)]),
+    "b2seg_ew_partial_rows": (C.c_int, [_i, _i64, _i]),
+    "b2seg_stem_stat_rows": (C.c_int, [_i, _i, _i]),
+    "b2seg_stem_wgrad_rows": (C.c_int, [_i, _i, _i]),
 }
 
 _lib = None

@@ -1,0 +1,445 @@
+// BatchNorm2d forward/backward, per-channel column sums, weight packing, fill.
+//
+// Replaces torch native_batch_norm / native_batch_norm_backward / threshold_backward reached
+// from every nn.BatchNorm2d + ReLU of the reference model (advanced_models.py:12,17,22,200-204
+// and the torchvision BasicBlock/Bottleneck the encoder is built from, :81-87,111-117).
+// All kernels are HBM-bound: 128-bit accesses, 8 channels per thread, no atomics.
+#include "ew.cuh"
+
+namespace {
+
+// ------------------------------------------------------------------ BN_FINALIZE ----
+// block = (32 channels, 32 row lanes); fp64 accumulation of the fp32 block partials.
+__global__ void __launch_bounds__(1024) bn_finalize_kernel(const EwArgs a) {
+  const float* partial = (const float*)a.p[0];
+  const float* gamma = (const float*)a.p[1];
+  const float* beta = (const float*)a.p[2];
+  float* rmean = (float*)a.p[3];
+  float* rvar = (float*)a.p[4];
+  long long* nbt = (long long*)a.p[5];
+  float* bnp = (float*)a.p[6];
+  const int rows = (int)a.i[0], C = (int)a.i[1];
+  const double count = (double)a.i[2];
+  const bool training = a.i[3] != 0;
+  const float eps = a.f[0], mom = a.f[1];
+  const size_t rstep = (size_t)(a.i[4] > 0 ? a.i[4] : 1) * 2 * C;  // floats between consecutive rows
+  __shared__ double sh[2][32][33];
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  const int c = blockIdx.x * 32 + tx;
+  double s = 0.0, q = 0.0;
+  if (training && c < C) {
+    for (int r = ty; r < rows; r += 32) {
+      s += (double)partial[(size_t)r * rstep + c];
+      q += (double)partial[(size_t)r * rstep + C + c];
+    }
+  }
+  sh[0][ty][tx] = s;
+  sh[1][ty][tx] = q;
+  __syncthreads();
+  if (ty == 0 && c < C) {
+    float mean, invstd;
+    if (training) {
+      s = 0.0; q = 0.0;
+      for (int l = 0; l < 32; ++l) { s += sh[0][l][tx]; q += sh[1][l][tx]; }
+      const double m = s / count;
+      double var = q / count - m * m;
+      if (var < 0.0) var = 0.0;
+      mean = (float)m;
+      invstd = (float)(1.0 / sqrt(var + (double)eps));
+      if (rmean) {
+        const double unb = count > 1.0 ? var * count / (count - 1.0) : var;
+        rmean[c] = (1.0f - mom) * rmean[c] + mom * mean;
+        rvar[c] = (1.0f - mom) * rvar[c] + mom * (float)unb;
+      }
+    } else {
+      mean = rmean[c];
+      invstd = 1.0f / sqrtf(rvar[c] + eps);
+    }
+    const float g = gamma ? gamma[c] : 1.0f, b = beta ? beta[c] : 0.0f;
+    const float scale = g * invstd;
+    bnp[c] = scale;
+    bnp[C + c] = b - mean * scale;
+    bnp[2 * C + c] = mean;
+    bnp[3 * C + c] = invstd;
+  }
+  if (training && nbt && blockIdx.x == 0 && tx == 0 && ty == 0) *nbt += 1;
+}
+
+// Folds `chunk` consecutive partial rows into the first row of each chunk (in place), so the
+// finalize kernel above never walks more than a few thousand rows with its C/32 blocks.
+__global__ void __launch_bounds__(1024) rows_fold_kernel(float* partial, int rows, int width, int chunk) {
+  __shared__ double sh[32][33];
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  const int col = blockIdx.x * 32 + tx;
+  const int r0 = blockIdx.y * chunk, r1 = min(rows, r0 + chunk);
+  double s = 0.0;
+  if (col < width)
+    for (int r = r0 + ty; r < r1; r += 32) s += (double)partial[(size_t)r * width + col];
+  sh[ty][tx] = s;
+  __syncthreads();
+  if (ty == 0 && col < width && r0 < rows) {
+    s = 0.0;
+    for (int l = 0; l < 32; ++l) s += sh[l][tx];
+    partial[(size_t)r0 * width + col] = (float)s;
+  }
+}
+
+// -------------------------------------------------------------------- BN_APPLY ----
+__global__ void __launch_bounds__(kEwThreads) bn_apply_kernel(const EwArgs a) {
+  const bf16* y = (const bf16*)a.p[0];
+  const float* bnp = (const float*)a.p[1];
+  bf16* out = (bf16*)a.p[2];
+  const bf16* res = (const bf16*)a.p[3];
+  const float* rbnp = (const float*)a.p[4];
+  const long long P = a.i[0];
+  const int C = (int)a.i[1];
+  const long long ldy = a.i[2], ldo = a.i[3], ldr = a.i[4];
+  const bool relu = a.i[5] != 0;
+  const int cv = C >> 3;
+  const long long total = P * cv;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const long long p = idx / cv;
+    const int c0 = (int)(idx % cv) * 8;
+    F8 v = ld_bf8(y + p * ldy + c0);
+    const F8 sc = ld_f8(bnp + c0), sf = ld_f8(bnp + C + c0);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v.v[j] = fmaf(v.v[j], sc.v[j], sf.v[j]);
+    if (res) {
+      F8 r = ld_bf8(res + p * ldr + c0);
+      if (rbnp) {
+        const F8 rs = ld_f8(rbnp + c0), rf = ld_f8(rbnp + C + c0);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) r.v[j] = fmaf(r.v[j], rs.v[j], rf.v[j]);
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v.v[j] += r.v[j];
+    }
+    if (relu) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v.v[j] = fmaxf(v.v[j], 0.0f);
+    }
+    st_bf8(out + p * ldo + c0, v);
+  }
+}
+
+// ------------------------------------------------------------------ BN backward ----
+struct BnBwdIn {
+  const bf16 *da1, *da2, *act, *y;
+  const float* bnp;
+  long long ld1, ld2, lda, ldy;
+  int C;
+};
+__device__ __forceinline__ BnBwdIn bn_bwd_in(const EwArgs& a) {
+  BnBwdIn s;
+  s.da1 = (const bf16*)a.p[0]; s.da2 = (const bf16*)a.p[1];
+  s.act = (const bf16*)a.p[2]; s.y = (const bf16*)a.p[3];
+  s.bnp = (const float*)a.p[4];
+  s.C = (int)a.i[1];
+  s.ld1 = a.i[2]; s.ld2 = a.i[3]; s.lda = a.i[4]; s.ldy = a.i[5];
+  return s;
+}
+// dz = (da1 [+ da2]) * [act > 0];  yhat = (y - mean) * invstd
+__device__ __forceinline__ void bn_bwd_load(const BnBwdIn& s, long long p, int c0, F8& dz, F8& yh) {
+  dz = ld_bf8(s.da1 + p * s.ld1 + c0);
+  if (s.da2) {
+    const F8 d2 = ld_bf8(s.da2 + p * s.ld2 + c0);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dz.v[j] += d2.v[j];
+  }
+  if (s.act) {
+    const F8 m = ld_bf8(s.act + p * s.lda + c0);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dz.v[j] = m.v[j] > 0.0f ? dz.v[j] : 0.0f;
+  }
+  yh = ld_bf8(s.y + p * s.ldy + c0);
+  const F8 mean = ld_f8(s.bnp + 2 * s.C + c0), inv = ld_f8(s.bnp + 3 * s.C + c0);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) yh.v[j] = (yh.v[j] - mean.v[j]) * inv.v[j];
+}
+
+__global__ void __launch_bounds__(kEwThreads) bn_bwd_reduce_kernel(const EwArgs a) {
+  extern __shared__ float red[];
+  const BnBwdIn s = bn_bwd_in(a);
+  ew_channel_reduce<2>(0, a.i[0], s.C, (float*)a.p[5], red,
+                       [&](long long p, int c0, float (&acc)[2][8]) {
+                         F8 dz, yh;
+                         bn_bwd_load(s, p, c0, dz, yh);
+#pragma unroll
+                         for (int j = 0; j < 8; ++j) {
+                           acc[0][j] += dz.v[j];
+                           acc[1][j] = fmaf(dz.v[j], yh.v[j], acc[1][j]);
+                         }
+                       });
+}
+
+__global__ void __launch_bounds__(1024) bn_bwd_finalize_kernel(const EwArgs a) {
+  const float* partial = (const float*)a.p[0];
+  const float* gamma = (const float*)a.p[1];
+  const float* bnp = (const float*)a.p[2];
+  float* dgamma = (float*)a.p[3];
+  float* dbeta = (float*)a.p[4];
+  float* coef = (float*)a.p[5];
+  float* dbias = (float*)a.p[6];
+  const int rows = (int)a.i[0], C = (int)a.i[1];
+  const double count = (double)a.i[2];
+  const bool accumulate = a.i[3] != 0, training = a.i[4] != 0;
+  __shared__ double sh[2][32][33];
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  const int c = blockIdx.x * 32 + tx;
+  double s = 0.0, q = 0.0;
+  if (c < C) {
+    for (int r = ty; r < rows; r += 32) {
+      s += (double)partial[((size_t)r * 2) * C + c];
+      q += (double)partial[((size_t)r * 2 + 1) * C + c];
+    }
+  }
+  sh[0][ty][tx] = s;
+  sh[1][ty][tx] = q;
+  __syncthreads();
+  if (ty == 0 && c < C) {
+    s = 0.0; q = 0.0;
+    for (int l = 0; l < 32; ++l) { s += sh[0][l][tx]; q += sh[1][l][tx]; }
+    const float g = gamma ? gamma[c] : 1.0f;
+    const float c1 = g * bnp[3 * C + c];
+    if (dgamma) dgamma[c] = accumulate ? dgamma[c] + (float)q : (float)q;
+    if (dbeta) dbeta[c] = accumulate ? dbeta[c] + (float)s : (float)s;
+    coef[c] = c1;
+    coef[C + c] = training ? (float)(s / count) : 0.0f;
+    coef[2 * C + c] = training ? (float)(q / count) : 0.0f;
+    if (dbias) {  // gradient of a conv bias feeding this BN: sum of dy (0 with batch statistics)
+      const float v = training ? 0.0f : c1 * (float)s;
+      dbias[c] = accumulate ? dbias[c] + v : v;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kEwThreads) bn_bwd_apply_kernel(const EwArgs a) {
+  const BnBwdIn s = bn_bwd_in(a);
+  const float* coef = (const float*)a.p[5];
+  bf16* dy = (bf16*)a.p[6];
+  bf16* dzo = (bf16*)a.p[7];
+  const long long P = a.i[0], lddy = a.i[6], lddz = a.i[7];
+  const int dz_mode = (int)a.i[8];  // 1 = store, 2 = accumulate
+  const int C = s.C, cv = C >> 3;
+  const long long total = P * cv;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const long long p = idx / cv;
+    const int c0 = (int)(idx % cv) * 8;
+    F8 dz, yh;
+    bn_bwd_load(s, p, c0, dz, yh);
+    const F8 c1 = ld_f8(coef + c0), c2 = ld_f8(coef + C + c0), c3 = ld_f8(coef + 2 * C + c0);
+    F8 o;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o.v[j] = c1.v[j] * (dz.v[j] - c2.v[j] - yh.v[j] * c3.v[j]);
+    st_bf8(dy + p * lddy + c0, o);
+    if (dzo) {
+      if (dz_mode == 2) {
+        const F8 old = ld_bf8(dzo + p * lddz + c0);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) dz.v[j] += old.v[j];
+      }
+      st_bf8(dzo + p * lddz + c0, dz);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------- COLSUM ----
+__global__ void __launch_bounds__(kEwThreads) colsum_kernel(const EwArgs a) {
+  extern __shared__ float red[];
+  const bf16* x = (const bf16*)a.p[0];
+  const long long ld = a.i[2];
+  ew_channel_reduce<1>(0, a.i[0], (int)a.i[1], (float*)a.p[1], red,
+                       [&](long long p, int c0, float (&acc)[1][8]) {
+                         const F8 v = ld_bf8(x + p * ld + c0);
+#pragma unroll
+                         for (int j = 0; j < 8; ++j) acc[0][j] += v.v[j];
+                       });
+}
+
+// out[k] (+)= sum_r partial[r*stride + k]; block = (32 k, 32 row lanes)
+__global__ void __launch_bounds__(1024) colsum_finalize_kernel(const EwArgs a) {
+  const float* partial = (const float*)a.p[0];
+  float* out = (float*)a.p[1];
+  const int rows = (int)a.i[0], K = (int)a.i[1];
+  const bool accumulate = a.i[2] != 0;
+  const long long stride = a.i[3];
+  __shared__ double sh[32][33];
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  const int k = blockIdx.x * 32 + tx;
+  double s = 0.0;
+  if (k < K)
+    for (int r = ty; r < rows; r += 32) s += (double)partial[(size_t)r * stride + k];
+  sh[ty][tx] = s;
+  __syncthreads();
+  if (ty == 0 && k < K) {
+    s = 0.0;
+    for (int l = 0; l < 32; ++l) s += sh[l][tx];
+    out[k] = accumulate ? out[k] + (float)s : (float)s;
+  }
+}
+
+// ------------------------------------------------------------------------ PACK ----
+// One launch repacks every fp32 parameter into its bf16 GEMM operand layouts.
+__global__ void __launch_bounds__(kEwThreads) pack_kernel(const EwArgs a) {
+  const b2seg_pack_job* jobs = (const b2seg_pack_job*)a.p[0];
+  const int njobs = (int)a.i[0];
+  const long long total = a.i[1];
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+       e += (long long)gridDim.x * blockDim.x) {
+    int lo = 0, hi = njobs - 1;
+    while (lo < hi) {  // last job with start <= e
+      const int mid = (lo + hi + 1) >> 1;
+      if (jobs[mid].start <= e) lo = mid; else hi = mid - 1;
+    }
+    const b2seg_pack_job j = jobs[lo];
+    const long long r = e - j.start;
+    const long long ab = (long long)j.A * j.B;
+    const int t = (int)(r / ab);
+    const long long r2 = r % ab;
+    const int ia = (int)(r2 / j.B), ib = (int)(r2 % j.B);
+    const float v = j.in[(long long)ia * j.sa + (long long)ib * j.sb + (long long)t * j.st];
+    ((bf16*)j.out)[r] = __float2bfloat16_rn(v);
+  }
+}
+
+__global__ void __launch_bounds__(kEwThreads) fill_kernel(const EwArgs a) {
+  uint32_t* dst = (uint32_t*)a.p[0];
+  const long long n = a.i[0] / 4;
+  const uint32_t pat = (uint32_t)a.i[1];
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x)
+    dst[i] = pat;
+}
+
+#define EW_LAUNCHER(name, kernel)                                                         \
+  int name(const EwArgs& a, dim3 grid, dim3 block, size_t smem, cudaStream_t st) {        \
+    kernel<<<grid, block, smem, st>>>(a);                                                 \
+    B2_CHECK_CUDA(cudaGetLastError());                                                    \
+    return B2SEG_OK;                                                                      \
+  }
+int launch_bn_finalize(const EwArgs& a, dim3 grid, dim3 block, size_t smem, cudaStream_t st) {
+  EwArgs b = a;
+  const int rows = (int)a.i[0], C = (int)a.i[1];
+  if (a.i[3] && rows > 2048) {  // training with many conv tiles: two-level row reduction
+    const int chunk = (rows + 255) / 256, slices = (rows + chunk - 1) / chunk;
+    rows_fold_kernel<<<dim3((2 * C + 31) / 32, slices), dim3(32, 32), 0, st>>>((float*)a.p[0], rows,
+                                                                               2 * C, chunk);
+    B2_CHECK_CUDA(cudaGetLastError());
+    b.i[0] = slices;
+    b.i[4] = chunk;
+  } else {
+    b.i[4] = 1;
+  }
+  bn_finalize_kernel<<<grid, block, smem, st>>>(b);
+  B2_CHECK_CUDA(cudaGetLastError());
+  return B2SEG_OK;
+}
+EW_LAUNCHER(launch_bn_apply, bn_apply_kernel)
+EW_LAUNCHER(launch_bn_bwd_reduce, bn_bwd_reduce_kernel)
+EW_LAUNCHER(launch_bn_bwd_finalize, bn_bwd_finalize_kernel)
+EW_LAUNCHER(launch_bn_bwd_apply, bn_bwd_apply_kernel)
+EW_LAUNCHER(launch_colsum, colsum_kernel)
+EW_LAUNCHER(launch_colsum_finalize, colsum_finalize_kernel)
+EW_LAUNCHER(launch_pack, pack_kernel)
+EW_LAUNCHER(launch_fill, fill_kernel)
+
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+}  // namespace
+
+#define EW_REQ_VEC(C, ...)                                                                \
+  B2_REQUIRE((C) >= 8 && (C) % 8 == 0 && (C) <= 2048, "ew: C=%d must be a multiple of 8 in [8,2048]", (int)(C))
+
+int ew_plan_bn(const b2seg_ew_desc* d, EwPlan* pl) {
+  const int64_t* i = d->i;
+  void* const* p = d->p;
+  pl->smem = 0;
+  pl->launches = 1;
+  switch (d->kind) {
+    case B2SEG_EW_BN_FINALIZE: {
+      B2_REQUIRE(p[6] && i[1] >= 1 && i[2] >= 1, "bn_finalize: bad arguments");
+      B2_REQUIRE(!i[3] || (p[0] && i[0] >= 1), "bn_finalize: training needs partial sums");
+      B2_REQUIRE(i[3] || (p[3] && p[4]), "bn_finalize: eval needs running statistics");
+      pl->fn = launch_bn_finalize;
+      pl->grid = dim3((unsigned)((i[1] + 31) / 32));
+      pl->block = dim3(32, 32);
+      pl->launches = (i[3] && i[0] > 2048) ? 2 : 1;
+      return B2SEG_OK;
+    }
+    case B2SEG_EW_BN_APPLY: {
+      EW_REQ_VEC(i[1]);
+      B2_REQUIRE(p[0] && p[1] && p[2] && i[0] >= 1, "bn_apply: null argument");
+      B2_REQUIRE(i[2] % 8 == 0 && i[3] % 8 == 0 && i[4] % 8 == 0 && aligned16(p[0]) &&
+                     aligned16(p[2]) && aligned16(p[3]),
+                 "bn_apply: leading dimensions / pointers must be 16-byte aligned");
+      pl->fn = launch_bn_apply;
+      pl->grid = dim3(ew_blocks(i[0] * (i[1] / 8)));
+      pl->block = dim3(kEwThreads);
+      return B2SEG_OK;
+    }
+    case B2SEG_EW_BN_BWD_REDUCE:
+    case B2SEG_EW_BN_BWD_APPLY: {
+      EW_REQ_VEC(i[1]);
+      B2_REQUIRE(p[0] && p[3] && p[4] && p[5] && i[0] >= 1, "bn_bwd: null argument");
+      B2_REQUIRE(i[2] % 8 == 0 && i[3] % 8 == 0 && i[4] % 8 == 0 && i[5] % 8 == 0 &&
+                     aligned16(p[0]) && aligned16(p[1]) && aligned16(p[2]) && aligned16(p[3]),
+                 "bn_bwd: leading dimensions / pointers must be 16-byte aligned");
+      if (d->kind == B2SEG_EW_BN_BWD_REDUCE) {
+        pl->fn = launch_bn_bwd_reduce;
+        pl->grid = dim3(ew_rows(i[0], (int)i[1]));
+        pl->block = dim3(kEwThreads);
+        pl->smem = (size_t)2 * ew_pl((int)i[1]) * i[1] * sizeof(float);
+      } else {
+        B2_REQUIRE(p[6] && i[6] % 8 == 0 && i[7] % 8 == 0 && aligned16(p[6]) && aligned16(p[7]),
+                   "bn_bwd_apply: dy/dz must be 16-byte aligned");
+        B2_REQUIRE(!p[7] || i[8] == 1 || i[8] == 2, "bn_bwd_apply: dz mode must be 1 or 2");
+        pl->fn = launch_bn_bwd_apply;
+        pl->grid = dim3(ew_blocks(i[0] * (i[1] / 8)));
+        pl->block = dim3(kEwThreads);
+      }
+      return B2SEG_OK;
+    }
+    case B2SEG_EW_BN_BWD_FINALIZE: {
+      B2_REQUIRE(p[0] && p[2] && p[5] && i[0] >= 1 && i[1] >= 1 && i[2] >= 1,
+                 "bn_bwd_finalize: bad arguments");
+      pl->fn = launch_bn_bwd_finalize;
+      pl->grid = dim3((unsigned)((i[1] + 31) / 32));
+      pl->block = dim3(32, 32);
+      return B2SEG_OK;
+    }
+    case B2SEG_EW_COLSUM: {
+      EW_REQ_VEC(i[1]);
+      B2_REQUIRE(p[0] && p[1] && i[0] >= 1 && i[2] % 8 == 0 && aligned16(p[0]), "colsum: bad arguments");
+      pl->fn = launch_colsum;
+      pl->grid = dim3(ew_rows(i[0], (int)i[1]));
+      pl->block = dim3(kEwThreads);
+      pl->smem = (size_t)ew_pl((int)i[1]) * i[1] * sizeof(float);
+      return B2SEG_OK;
+    }
+    case B2SEG_EW_COLSUM_FINALIZE: {
+      B2_REQUIRE(p[0] && p[1] && i[0] >= 1 && i[1] >= 1 && i[3] >= i[1], "colsum_finalize: bad arguments");
+      pl->fn = launch_colsum_finalize;
+      pl->grid = dim3((unsigned)((i[1] + 31) / 32));
+      pl->block = dim3(32, 32);
+      return B2SEG_OK;
+    }
+    case B2SEG_EW_PACK: {
+      B2_REQUIRE(p[0] && i[0] >= 1 && i[1] >= 1, "pack: bad arguments");
+      pl->fn = launch_pack;
+      pl->grid = dim3(ew_blocks(i[1]));
+      pl->block = dim3(kEwThreads);
+      return B2SEG_OK;
+    }
+    case B2SEG_EW_FILL: {
+      B2_REQUIRE(p[0] && i[0] >= 4 && i[0] % 4 == 0, "fill: bytes must be a positive multiple of 4");
+      pl->fn = launch_fill;
+      pl->grid = dim3(ew_blocks(i[0] / 4));
+      pl->block = dim3(kEwThreads);
+      return B2SEG_OK;
+    }
+  }
+  b2seg_set_error("ew_plan_bn: kind %d not handled here", d->kind);
+  return B2SEG_EINVAL;
+}

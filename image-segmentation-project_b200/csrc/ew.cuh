@@ -1,0 +1,121 @@
+// Shared plumbing of the HBM-bound layer kernels (section 4 of include/b2seg.h).
+//
+// Activations are NHWC bf16 seen as [P pixels][C channels] with a leading
+// dimension ld; every thread moves 8 channels (one 128-bit word).  Per-channel
+// reductions are two-phase: each block writes one row of fp32 partials, a
+// finalize kernel sums the rows in fixed order (fp64) -> bit-reproducible.
+#pragma once
+#include "ops.cuh"
+
+struct EwArgs {
+  void* p[10];
+  long long i[10];
+  float f[4];
+};
+
+typedef int (*EwLaunch)(const EwArgs& a, dim3 grid, dim3 block, size_t smem, cudaStream_t st);
+
+struct EwPlan {
+  EwLaunch fn;
+  dim3 grid, block;
+  size_t smem;
+  int launches;
+};
+
+// planners, one per source file; each fills `plan` for desc->kind or returns an error
+int ew_plan_bn(const b2seg_ew_desc* d, EwPlan* plan);
+int ew_plan_stem(const b2seg_ew_desc* d, EwPlan* plan);
+int ew_plan_attn(const b2seg_ew_desc* d, EwPlan* plan);
+int ew_plan_se(const b2seg_ew_desc* d, EwPlan* plan);
+
+constexpr int kEwThreads = 256;
+
+static inline int ew_pl(int C) {  // pixel lanes of a 256-thread block whose threads own 8 channels
+  const int cv = C / 8;
+  const int pl = kEwThreads / (cv > 0 ? cv : 1);
+  return pl < 1 ? 1 : pl;
+}
+static inline int ew_rows(long long P, int C) {
+  const long long per = (long long)ew_pl(C) * 8;
+  long long r = (P + per - 1) / per;
+  if (r < 1) r = 1;
+  if (r > B2SEG_EW_MAX_PARTIAL_ROWS) r = B2SEG_EW_MAX_PARTIAL_ROWS;
+  return (int)r;
+}
+static inline int ew_blocks(long long work_items) {  // elementwise grid: 256 threads, grid-stride
+  long long b = (work_items + kEwThreads - 1) / kEwThreads;
+  const long long cap = (long long)b2_num_sms() * 16;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+// sub-warp group size (power of two <= 32) for kernels that reduce over the channels of a pixel
+static inline int ew_group(int C) {
+  const int cv = C / 8;
+  int g = 1;
+  while (g < cv && g < 32) g <<= 1;
+  return g;
+}
+
+#ifdef __CUDACC__
+struct F8 {
+  float v[8];
+};
+__device__ __forceinline__ F8 ld_bf8(const bf16* p) {
+  const uint4 u = *reinterpret_cast<const uint4*>(p);
+  F8 r;
+  float2 t;
+  t = bf2_to_f2(u.x); r.v[0] = t.x; r.v[1] = t.y;
+  t = bf2_to_f2(u.y); r.v[2] = t.x; r.v[3] = t.y;
+  t = bf2_to_f2(u.z); r.v[4] = t.x; r.v[5] = t.y;
+  t = bf2_to_f2(u.w); r.v[6] = t.x; r.v[7] = t.y;
+  return r;
+}
+__device__ __forceinline__ void st_bf8(bf16* p, const F8& r) {
+  uint4 u;
+  u.x = f2_to_bf2(r.v[0], r.v[1]);
+  u.y = f2_to_bf2(r.v[2], r.v[3]);
+  u.z = f2_to_bf2(r.v[4], r.v[5]);
+  u.w = f2_to_bf2(r.v[6], r.v[7]);
+  *reinterpret_cast<uint4*>(p) = u;
+}
+__device__ __forceinline__ F8 ld_f8(const float* p) {
+  const float4 a = *reinterpret_cast<const float4*>(p);
+  const float4 b = *reinterpret_cast<const float4*>(p + 4);
+  F8 r;
+  r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w;
+  r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+  return r;
+}
+
+// Block-level per-channel reduction.  Thread t owns channel vector t % cv and pixel lane
+// t / cv; `body(p, c0, acc)` adds pixel p's contribution for channels [c0, c0+8) into
+// acc[NACC][8].  Row `blockIdx.x` of `partial` ([gridDim.x][NACC][C]) receives the block sums.
+template <int NACC, class Body>
+__device__ __forceinline__ void ew_channel_reduce(long long P0, long long P1, int C, float* partial,
+                                                  float* red /* smem NACC*pl*C */, Body body) {
+  const int cv = C >> 3;
+  const int pl = blockDim.x / cv > 0 ? blockDim.x / cv : 1;
+  const int lc = threadIdx.x % cv, lp = threadIdx.x / cv;
+  float acc[NACC][8];
+#pragma unroll
+  for (int k = 0; k < NACC; ++k)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[k][j] = 0.0f;
+  if (lp < pl) {
+    for (long long p = P0 + (long long)blockIdx.x * pl + lp; p < P1; p += (long long)gridDim.x * pl)
+      body(p, lc * 8, acc);
+#pragma unroll
+    for (int k = 0; k < NACC; ++k)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) red[((size_t)k * pl + lp) * C + lc * 8 + j] = acc[k][j];
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < NACC * C; idx += blockDim.x) {
+    const int k = idx / C, c = idx % C;
+    float s = 0.0f;
+    for (int l = 0; l < pl; ++l) s += red[((size_t)k * pl + l) * C + c];
+    partial[((size_t)blockIdx.x * NACC + k) * C + c] = s;
+  }
+}
+#endif

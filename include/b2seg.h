@@ -243,6 +243,131 @@ size_t b2seg_wgrad_workspace_bytes(int a_channels, int b_channels, int ntaps, in
                                    int pw);
 int b2seg_wgrad_create(const b2seg_wgrad_desc* desc /*host*/, b2seg_op** out);
 
+/* ======================================================================== *
+ *  4. HBM-bound layer kernels (BatchNorm, ReLU, pooling, stem, 1-channel    *
+ *     convs, attention gate, squeeze-excite, weight packing) as planned ops.*
+ *     Activations are NHWC bf16 seen as [P pixels][C] with a leading         *
+ *     dimension `ld` in elements (channel slices of the concat buffers work  *
+ *     in place).  One generic descriptor: `kind` selects the kernel; slot    *
+ *     meanings are listed per kind (p = device pointers, i = integers,       *
+ *     f = floats).  Per-channel reductions are two-phase (block partials ->  *
+ *     fixed-order fp64 finalize), never atomics: runs are bit-reproducible.  *
+ *     C must be a multiple of 8 (<= 2048); ld multiples of 8; 16-B pointers. *
+ * ======================================================================== */
+#define B2SEG_EW_MAX_PARTIAL_ROWS 592 /* 148 SMs x 4: most rows any block-partial buffer has */
+
+enum {
+  /* BatchNorm2d statistics -> per-channel affine (torch native_batch_norm; every
+   * nn.BatchNorm2d: advanced_models.py:12,17,22,200,203 + torchvision blocks).
+   * p0 partial f32 [rows][2][C] (sum, sumsq; may be folded in place; unused in eval)
+   * p1 gamma|NULL  p2 beta|NULL  p3 running_mean  p4 running_var  p5 num_batches_tracked (int64)|NULL
+   * p6 out bnp f32 [4][C] = scale, shift, mean, invstd
+   * i0 rows  i1 C  i2 count (N*H*W)  i3 training    f0 eps  f1 momentum */
+  B2SEG_EW_BN_FINALIZE = 1,
+  /* out = act(y*scale+shift (+ res*rscale+rshift | + res)), act = ReLU if i5.
+   * p0 y bf16  p1 bnp  p2 out bf16  p3 res bf16|NULL  p4 res bnp|NULL
+   * i0 P  i1 C  i2 ld_y  i3 ld_out  i4 ld_res  i5 relu */
+  B2SEG_EW_BN_APPLY = 2,
+  /* BatchNorm backward phase 1: dz = (da1 [+ da2]) * [a > 0]; block partials of (dz, dz*yhat).
+   * p0 da1 bf16  p1 da2 bf16|NULL  p2 a bf16|NULL (ReLU mask source)  p3 y bf16 (pre-BN)  p4 bnp
+   * p5 out partial f32 [rows][2][C], rows = b2seg_ew_partial_rows(kind, P, C)
+   * i0 P  i1 C  i2 ld_da1  i3 ld_da2  i4 ld_a  i5 ld_y */
+  B2SEG_EW_BN_BWD_REDUCE = 3,
+  /* p0 partial  p1 gamma|NULL  p2 bnp  p3 dgamma f32|NULL  p4 dbeta f32|NULL  p5 out coef f32 [3][C]
+   * p6 dbias f32|NULL (gradient of a conv bias feeding this BN: 0 with batch statistics)
+   * i0 rows  i1 C  i2 count  i3 accumulate into dgamma/dbeta/dbias  i4 training */
+  B2SEG_EW_BN_BWD_FINALIZE = 4,
+  /* phase 2: dy = c1*(dz - c2 - yhat*c3) -> bf16; optionally also emits dz (residual branch).
+   * p0..p4 as BN_BWD_REDUCE  p5 coef  p6 dy bf16  p7 dz bf16|NULL
+   * i0..i5 as BN_BWD_REDUCE  i6 ld_dy  i7 ld_dz  i8 dz mode (1 store, 2 accumulate) */
+  B2SEG_EW_BN_BWD_APPLY = 5,
+  /* MaxPool2d(3, stride 2, pad 1) (advanced_models.py:83,272) + argmax byte (kh*3+kw) per element.
+   * p0 x bf16 [N,H,W,C]  p1 out bf16 [N,H/2,W/2,C]  p2 idx u8 [N,H/2,W/2,C]
+   * i0 N i1 H i2 W i3 C i4 ld_x i5 ld_out */
+  B2SEG_EW_MAXPOOL_FWD = 6,
+  /* p0 dout bf16  p1 idx u8  p2 dx bf16 [N,H,W,C]   i0 N i1 H i2 W i3 C i4 ld_dout i5 ld_dx i6 accumulate */
+  B2SEG_EW_MAXPOOL_BWD = 7,
+  /* input_conv 7x7 s2 p3, 1 -> 64 channels (advanced_models.py:76,268) + BatchNorm block partials.
+   * p0 x f32 [N,H,W]  p1 w f32 [64][49]  p2 y bf16 [N,H/2,W/2,64]  p3 partial f32 [rows][2][64]|NULL
+   * i0 N i1 H i2 W ; rows = b2seg_stem_stat_rows(N,H,W) */
+  B2SEG_EW_STEM_FWD = 8,
+  /* p0 x f32  p1 dy bf16 [N,H/2,W/2,64]  p2 out partial f32 [rows][3136] (rows =
+   * b2seg_stem_wgrad_rows; reduce with COLSUM_FINALIZE into dW [64][49])   i0 N i1 H i2 W */
+  B2SEG_EW_STEM_WGRAD = 9,
+  /* 1-output-channel 1x1 conv (conv_final advanced_models.py:160,350; AttentionGate.psi :21):
+   * out[p] = sum_c v[p,c]*w[c] + b (f32), optional block partials (sum, sumsq) for BatchNorm2d(1).
+   * p0 v bf16  p1 w f32 [C]  p2 b f32 [1]|NULL  p3 out f32 [P]  p4 partial f32 [rows][2]|NULL
+   * i0 P  i1 C  i2 ld_v */
+  B2SEG_EW_DOT1_FWD = 10,
+  /* backward of DOT1: ds[p] = dscalar[p], or BatchNorm2d(1)-backward of it when p5 is given
+   * (coef p5, pre-BN values p6, bnp p7);  dv[p,c] = ds*w[c];  partial [rows][C+1] = (dW[C], db).
+   * p0 dscalar f32  p1 v bf16  p2 w f32  p3 dv bf16  p4 partial  p5 coef|NULL  p6 ypre f32|NULL
+   * p7 bnp|NULL     i0 P  i1 C  i2 ld_v  i3 ld_dv */
+  B2SEG_EW_DOT1_BWD = 11,
+  /* out[k] (+)= sum_r partial[r*stride + k].  p0 partial  p1 out f32  i0 rows i1 K i2 accumulate
+   * i3 row stride (elements) */
+  B2SEG_EW_COLSUM_FINALIZE = 12,
+  /* per-channel sum over pixels (ConvTranspose2d bias gradient).
+   * p0 x bf16  p1 partial f32 [rows][C]   i0 P i1 C i2 ld */
+  B2SEG_EW_COLSUM = 13,
+  /* every fp32 parameter -> its bf16 GEMM operand layouts, one launch.
+   * p0 device table of b2seg_pack_job  i0 number of jobs  i1 total elements */
+  B2SEG_EW_PACK = 14,
+  /* AttentionGate tail (advanced_models.py:34-40): psi = sigmoid(BN1(psi_pre)); out[p,c] = x[p,c]*psi[p].
+   * p0 psi_pre f32 [P]  p1 bnp (1 channel)  p2 x bf16  p3 out bf16  p4 psi f32 [P] (saved)
+   * i0 P i1 C i2 ld_x i3 ld_out */
+  B2SEG_EW_GATE_APPLY = 15,
+  /* gate backward: dpsi[p] = sum_c dout[p,c]*x[p,c]; dz = dpsi*psi*(1-psi) (f32 out);
+   * dx[p,c] (+)= dout[p,c]*psi[p]; partial [rows][2] = (sum dz, sum dz*yhat) for BatchNorm2d(1).
+   * p0 dout bf16  p1 x bf16  p2 psi f32  p3 psi_pre f32  p4 bnp (1 channel)  p5 dz f32  p6 dx bf16
+   * p7 partial    i0 P i1 C i2 ld_dout i3 ld_x i4 ld_dx i5 accumulate into dx */
+  B2SEG_EW_GATE_BWD = 16,
+  /* ChannelAttention (advanced_models.py:43-61) squeeze: per (n,c) sum, max, first argmax over H*W.
+   * p0 x bf16  p1 part f32 [N][rows][3][C]   i0 N i1 HW i2 C i3 ld ;
+   * rows = b2seg_ew_partial_rows(kind, HW, C) */
+  B2SEG_EW_SE_POOL = 17,
+  /* excite: finish pooling, shared MLP C->Ch->C (no bias), sigmoid.
+   * p0 part  p1 w1 f32 [Ch][C]  p2 w2 f32 [C][Ch]  p3 saved f32 [N][4][C] (avg, max, gate, argmax bits)
+   * p4 hidden f32 [N][2][Ch]   i0 N i1 HW i2 C i3 Ch i4 rows */
+  B2SEG_EW_SE_MLP = 18,
+  /* out[p,c] = x[p,c]*gate[n,c].  p0 x bf16  p1 saved  p2 out bf16  i0 N i1 HW i2 C i3 ld_x i4 ld_out */
+  B2SEG_EW_SE_SCALE = 19,
+  /* backward 1: part[n][row][c] = sum_p dout*x.  p0 dout bf16  p1 x bf16  p2 part f32 [N][rows][C]
+   * i0 N i1 HW i2 C i3 ld_dout i4 ld_x */
+  B2SEG_EW_SE_BWD_REDUCE = 20,
+  /* backward 2 (tiny, one block): MLP backward -> dW1, dW2, dpool = (davg, dmax).
+   * p0 part  p1 w1  p2 w2  p3 saved  p4 hidden  p5 dW1 f32  p6 dW2 f32  p7 dpool f32 [N][2][C]
+   * i0 N i1 HW i2 C i3 Ch i4 rows i5 accumulate into dW1/dW2 */
+  B2SEG_EW_SE_MLP_BWD = 21,
+  /* backward 3: dx = dout*gate + davg/HW + dmax*[p == argmax].
+   * p0 dout bf16  p1 saved  p2 dpool  p3 dx bf16   i0 N i1 HW i2 C i3 ld_dout i4 ld_dx */
+  B2SEG_EW_SE_BWD_APPLY = 22,
+  /* p0 dst, i0 bytes (multiple of 4), i1 32-bit pattern */
+  B2SEG_EW_FILL = 23,
+};
+
+/* out[t][a][b] = bf16(in[a*sa + b*sb + t*st]); `start` = elements of all earlier jobs. */
+typedef struct b2seg_pack_job {
+  const float* in;
+  void* out;
+  int32_t T, A, B, pad;
+  int64_t sa, sb, st;
+  int64_t start;
+} b2seg_pack_job;
+
+typedef struct b2seg_ew_desc {
+  int32_t kind;
+  void* p[10];
+  int64_t i[10];
+  float f[4];
+} b2seg_ew_desc;
+
+int b2seg_ew_create(const b2seg_ew_desc* desc /*host*/, b2seg_op** out);
+/* rows of the block-partial buffer an op of `kind` writes for P pixels x C channels */
+int b2seg_ew_partial_rows(int kind, int64_t P, int C);
+int b2seg_stem_stat_rows(int n, int h, int w);
+int b2seg_stem_wgrad_rows(int n, int h, int w);
+
 #ifdef __cplusplus
 }
 #endif
