@@ -63,8 +63,7 @@ class _UNetStep(torch.autograd.Function):
     flat-buffer views to autograd as parameter gradients."""
 
     @staticmethod
-    def forward(ctx, model, x, *params):
-        need_grad = torch.is_grad_enabled() and any(p.requires_grad for p in params)
+    def forward(ctx, model, need_grad, x, *params):
         plan = model._plan_for(x, need_grad)
         logits = plan.run_forward(x)
         ctx.plan, ctx.generation, ctx.model = plan, plan.generation, model
@@ -97,7 +96,7 @@ class _UNetStep(torch.autograd.Function):
                 grads.append(plan.gview(name) - carry[plan.goff[name]:plan.goff[name] + p.numel()].view(p.shape))
             else:
                 grads.append(plan.gview(name))
-        return (None, None, *grads)
+        return (None, None, None, *grads)
 
 
 class UNetWithBackbone(nn.Module):
@@ -189,4 +188,6 @@ class UNetWithBackbone(nn.Module):
                                "model and the batch to CUDA")
         if x.device != p0.device:
             raise L.B2SegError(f"input on {x.device}, parameters on {p0.device}")
-        return _UNetStep.apply(self, x, *self.parameters())
+        params = list(self.parameters())
+        need_grad = torch.is_grad_enabled() and any(p.requires_grad for p in params)
+        return _UNetStep.apply(self, need_grad, x, *params)

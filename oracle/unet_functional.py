@@ -60,12 +60,29 @@ class _BN:
                             sd[p + ".weight"], sd[p + ".bias"], self.training, 0.1, 1e-5)
 
 
+_STORE = [None]
+
+
+def _store(t):
+    return _STORE[0](t) if _STORE[0] is not None else t
+
+
+def bf16_round(t):
+    """Round to the nearest bf16 value, keep fp32 storage (straight-through for autograd)."""
+    return t + (t.detach().to(torch.bfloat16).float() - t.detach())
+
+
 def unet_forward(sd, x, backbone="resnet34", use_attention=True, training=True, new_stats=None,
-                 taps=None):
+                 taps=None, storage_round=None):
     """logits = UNetWithBackbone.forward(x) (advanced_models.py:264-357) from state dict `sd`.
 
-    `taps` (optional dict) receives named intermediate activations for layer-level parity."""
+    `taps` (optional dict) receives named intermediate activations for layer-level parity.
+    `storage_round` (e.g. bf16_round) is applied to every conv weight, every conv output and every
+    stored activation: the "same arithmetic, bf16 storage" comparator for the B200 path, which
+    keeps activations in bf16 between kernels (all sums still accumulate in fp32)."""
     kind, depths = RESNET_LAYERS[backbone]
+    if storage_round is not None:
+        return _unet_forward_rounded(sd, x, backbone, use_attention, training, new_stats, taps, storage_round)
 
     def bn(prefix):
         return _BN(sd, prefix, training, new_stats)
@@ -105,7 +122,7 @@ def unet_forward(sd, x, backbone="resnet34", use_attention=True, training=True, 
         s1 = bn(a + ".W_x.1")(F.conv2d(s, sd[a + ".W_x.0.weight"], sd[a + ".W_x.0.bias"]))
         psi = F.relu(g1 + s1)
         psi = torch.sigmoid(bn(a + ".psi.1")(F.conv2d(psi, sd[a + ".psi.0.weight"], sd[a + ".psi.0.bias"])))
-        return s * psi
+        return _store(s * psi)
 
     def squeeze_excite(k, d):  # ChannelAttention.forward (:57-61); fc shared by both pools
         c = f"ch_attention{k}"
@@ -114,7 +131,7 @@ def unet_forward(sd, x, backbone="resnet34", use_attention=True, training=True, 
             return F.conv2d(F.relu(F.conv2d(v, sd[c + ".fc.0.weight"])), sd[c + ".fc.2.weight"])
 
         w = fc(F.adaptive_avg_pool2d(d, 1)) + fc(F.adaptive_max_pool2d(d, 1))
-        return d * torch.sigmoid(w)
+        return _store(d * torch.sigmoid(w))
 
     def dec_block(k, d):  # _decoder_block (:197-205)
         p = f"decoder{k}"
@@ -139,6 +156,33 @@ def unet_forward(sd, x, backbone="resnet34", use_attention=True, training=True, 
         if dh > 0 or dw > 0:
             d0 = d0[:, :, dh // 2:dh // 2 + x.shape[2], dw // 2:dw // 2 + x.shape[3]]
     return F.conv2d(d0, sd["conv_final.weight"], sd["conv_final.bias"])  # (:350)
+
+
+def _unet_forward_rounded(sd, x, backbone, use_attention, training, new_stats, taps, q):
+    """Same network with `q` applied at every point where the B200 path stores bf16."""
+    import contextlib
+    orig = dict(conv2d=F.conv2d, conv_transpose2d=F.conv_transpose2d, relu=F.relu, batch_norm=F.batch_norm)
+
+    def conv2d(inp, w, b=None, *a, **k):
+        if w.shape[1] == 1 and w.shape[2] == 7:      # stem: fp32 weights and input, bf16 output
+            return q(orig["conv2d"](inp, w, b, *a, **k))
+        if w.shape[0] == 1 or inp.shape[2] * inp.shape[3] == 1:   # 1-channel convs / SE MLP: fp32
+            return orig["conv2d"](inp, w, b, *a, **k)
+        return q(orig["conv2d"](inp, q(w), b, *a, **k))
+
+    def conv_transpose2d(inp, w, b=None, *a, **k):
+        return q(orig["conv_transpose2d"](inp, q(w), b, *a, **k))
+
+    def relu(t, *a, **k):
+        return q(orig["relu"](t, *a, **k))
+
+    F.conv2d, F.conv_transpose2d, F.relu = conv2d, conv_transpose2d, relu
+    _STORE[0] = q
+    try:
+        return unet_forward(sd, x, backbone, use_attention, training, new_stats, taps, None)
+    finally:
+        _STORE[0] = None
+        F.conv2d, F.conv_transpose2d, F.relu = orig["conv2d"], orig["conv_transpose2d"], orig["relu"]
 
 
 def forward_backward(sd, x, target, loss_fn, **kw):

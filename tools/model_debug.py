@@ -28,6 +28,9 @@ def rel(a, b):
 taps = {}
 new_stats = {}
 ref_logits = uf.unet_forward(sd, x, backbone=backbone, use_attention=attn, training=True, new_stats=new_stats, taps=taps)
+taps_q = {}
+with torch.no_grad():
+    ref_logits_q = uf.unet_forward(sd, x, backbone=backbone, use_attention=attn, training=True, taps=taps_q, storage_round=uf.bf16_round)
 crit_ref = lambda lo, ta: seg_losses.torch_loss("combo", lo, ta) if hasattr(seg_losses, "torch_loss") else None
 logits = model(x.to(dev))
 torch.cuda.synchronize()
@@ -35,8 +38,8 @@ plan = next(iter(model._plans.values()))
 print(f"plan: {len(plan.fwd_ops)} fwd ops / {plan.launches_fwd} launches, {len(plan.bwd_ops)} bwd ops / {plan.launches_bwd} launches, {plan.nbytes/2**20:.1f} MiB")
 for name, act in plan.named.items():
     got = act.v.torch().float().cpu().permute(0, 3, 1, 2)
-    print(f"  {name:4s} rel err {rel(got, taps[name]):.3e}  max|ref| {float(taps[name].abs().max()):.3f}")
-print(f"  logits rel err {rel(logits.cpu(), ref_logits):.3e}")
+    print(f"  {name:4s} rel err vs fp32 {rel(got, taps[name]):.3e}  vs bf16-storage oracle {rel(got, taps_q[name]):.3e}  (oracle bf16 vs fp32 {rel(taps_q[name], taps[name]):.3e})")
+print(f"  logits rel err vs fp32 {rel(logits.cpu(), ref_logits):.3e} vs bf16-storage {rel(logits.cpu(), ref_logits_q):.3e} (oracle bf16 vs fp32 {rel(ref_logits_q, ref_logits):.3e})")
 for k in ("bn1.running_mean", "bn1.running_var", "enc4.2.bn2.running_var"):
     print(f"  {k} rel err {rel(model.state_dict()[k].cpu(), new_stats[k]):.3e}")
 # backward with the combo loss on both sides
@@ -50,6 +53,7 @@ def combo(lo, ta):
     dice = 1 - (2 * (p * tt).sum() + 1) / (p.sum() + tt.sum() + 1)
     return 0.5 * F.binary_cross_entropy_with_logits(lo, ta) + 0.5 * dice
 _, ref_loss, ref_grads = uf.forward_backward(sd, x, t, combo, backbone=backbone, use_attention=attn, training=True)
+_, ref_loss_q, ref_grads_q = uf.forward_backward(sd, x, t, combo, backbone=backbone, use_attention=attn, training=True, storage_round=uf.bf16_round)
 print(f"loss {float(loss):.6f} ref {ref_loss:.6f}")
 worst = []
 for n, p in model.named_parameters():
@@ -57,8 +61,9 @@ for n, p in model.named_parameters():
     if rg is None:
         continue
     e = rel(p.grad.cpu(), rg)
-    worst.append((e, n, float(rg.norm())))
+    worst.append((e, n, float(rg.norm()), rel(p.grad.cpu(), ref_grads_q[n]), rel(ref_grads_q[n], rg)))
 worst.sort(reverse=True)
-for e, n, nr in worst[:25]:
-    print(f"  grad {n:40s} rel err {e:.3e}  |ref| {nr:.3e}")
+for e, n, nr, eq, qq in worst[:25]:
+    print(f"  grad {n:36s} vs fp32 {e:.3e} vs bf16-storage {eq:.3e} (oracle bf16 vs fp32 {qq:.3e}) |ref| {nr:.3e}")
+print("median vs bf16-storage", sorted(w[3] for w in worst)[len(worst) // 2], "max", max(w[3] for w in worst))
 print("median grad rel err", sorted(w[0] for w in worst)[len(worst) // 2])
