@@ -61,6 +61,8 @@ class UNetPlan:
         self.backbone = model.backbone_name
         self.attn = bool(model.use_attention)
         self.fwd_ops, self.bwd_ops, self.tape = [], [], []
+        self.stored_g = {}  # name -> View of the gradient w.r.t. that activation (after backward)
+        self.stored = {}  # name -> View / fp32 tensor of every activation kept in HBM (parity tests)
         self.keep = []
         self.generation = 0
         self.nbytes = 0
@@ -241,6 +243,7 @@ class UNetPlan:
         self.F(eo.ew(L.EW_STEM_FWD, p=[self.x_in, P["input_conv.weight"], y0, st0], i=[N, H, W]))
         bnp0 = self.bn_finalize("bn1", 64, rows0, N * h1 * w1, st0)
         self.bn_apply(y0, bnp0, x1.v, True)
+        self.stored.update({"stem.y": y0, "x1": x1.v})
         h0 = self.act(N, h1 // 2, w1 // 2, 64)
         idx = self._alloc((N, h1 // 2, w1 // 2, 64), torch.uint8)
         self.F(eo.ew(L.EW_MAXPOOL_FWD, p=[x1.v, h0.v, idx], i=[N, h1, w1, 64, x1.v.sw, h0.v.sw]))
@@ -248,6 +251,7 @@ class UNetPlan:
         def bwd_stem():
             dy0 = View(self._alloc((N, h1, w1, 64), BF16))
             self.bn_backward("bn1", x1.g, x1.v, y0, bnp0, dy0)
+            self.stored_g.update({"stem.y": dy0, "x1": x1.g})
             rows = eo.stem_wgrad_rows(N, H, W)
             wsS = self._alloc((rows, 3136), F32)
             self.B(eo.ew(L.EW_STEM_WGRAD, p=[self.x_in, dy0, wsS], i=[N, H, W]))
@@ -293,6 +297,7 @@ class UNetPlan:
         self.F(eo.ew(L.EW_DOT1_FWD, p=[d0.v, P["conv_final.weight"], P["conv_final.bias"], self.logits, None],
                      i=[NP, 16, 16]))
         d1 = d
+        self.stored.update({"d0": d0.v, "logits": self.logits})
 
         def bwd_up0():
             self.upconv_backward("upconv0", d1, d0.g)
@@ -304,6 +309,7 @@ class UNetPlan:
             self.B(eo.ew(L.EW_COLSUM_FINALIZE, p=[self.part, self.gview("conv_final.weight")], i=[rows, 16, 0, 17]))
             self.B(eo.ew(L.EW_COLSUM_FINALIZE, p=[self.part[16:], self.gview("conv_final.bias")], i=[rows, 1, 0, 17]))
             d0.gw = True
+            self.stored_g.update({"d0": d0.g, "logits": self.dlogits})
 
         self.tape += [bwd_up0, bwd_final]
         if ng:
@@ -353,6 +359,9 @@ class UNetPlan:
             self.bn_apply(y2, b2, out.v, True, res=yd, rbnp=bd)
         else:
             self.bn_apply(y2, b2, out.v, True, res=hin.v)
+        self.stored.update({pre + ".y1": y1, pre + ".a1": a1.v, pre + ".y2": y2, pre + ".out": out.v})
+        if ds:
+            self.stored[pre + ".yd"] = yd
 
         def bwd():
             dy2 = self._like(y2)
@@ -369,6 +378,8 @@ class UNetPlan:
                 dyd = self._like(yd)
                 self.bn_backward(pre + ".downsample.1", dzb, None, yd, bd, dyd)
                 self.conv_backward(hin, dyd, pre + ".downsample.0.weight", 1, stride)
+                self.stored_g[pre + ".yd"] = dyd
+            self.stored_g.update({pre + ".y1": dy1, pre + ".a1": a1.g, pre + ".y2": dy2, pre + ".out": out.g})
 
         self.tape.append(bwd)
         return out
@@ -390,6 +401,10 @@ class UNetPlan:
             self.bn_apply(y3, b3, out.v, True, res=yd, rbnp=bd)
         else:
             self.bn_apply(y3, b3, out.v, True, res=hin.v)
+        self.stored.update({pre + ".y1": y1, pre + ".a1": a1.v, pre + ".y2": y2, pre + ".a2": a2.v,
+                            pre + ".y3": y3, pre + ".out": out.v})
+        if ds:
+            self.stored[pre + ".yd"] = yd
 
         def bwd():
             dy3 = self._like(y3)
@@ -409,6 +424,9 @@ class UNetPlan:
                 dyd = self._like(yd)
                 self.bn_backward(pre + ".downsample.1", dzb, None, yd, bd, dyd)
                 self.conv_backward(hin, dyd, pre + ".downsample.0.weight", 1, stride)
+                self.stored_g[pre + ".yd"] = dyd
+            self.stored_g.update({pre + ".y1": dy1, pre + ".a1": a1.g, pre + ".y2": dy2, pre + ".a2": a2.g,
+                                  pre + ".y3": dy3, pre + ".out": out.g})
 
         self.tape.append(bwd)
         return out
@@ -436,6 +454,7 @@ class UNetPlan:
         yb, bb = self.conv_bn(a.v, p + ".3.weight", p + ".4", 3, 1, Cu, biasname=p + ".3.bias")
         b = self.act(N, h, w, Cu)
         self.bn_apply(yb, bb, b.v, True)
+        self.stored.update({f"up{k}": up.v, f"dec{k}.ya": ya, f"dec{k}.a": a.v, f"dec{k}.yb": yb, f"dec{k}.b": b.v})
 
         def bwd_dec():
             dyb = self._like(yb)
@@ -447,12 +466,15 @@ class UNetPlan:
             up.gw = True
             if not self.attn:
                 skip.gw = True  # skip.g IS the skip slice of dcat
+            self.stored_g.update({f"up{k}": up.g, f"dec{k}.ya": dya, f"dec{k}.a": a.g, f"dec{k}.yb": dyb,
+                                  f"dec{k}.b": b.g})
 
         self.tape.append(bwd_dec)
         if not self.attn:
             return b
         out = self.act(N, h, w, Cu)
         self.channel_attention(k, b, out)
+        self.stored[f"se{k}.out"] = out.v
         return out
 
     def gate(self, k, up: Act, skip: Act, outS: View, doutS: View | None):
@@ -473,6 +495,8 @@ class UNetPlan:
                                        self.part if self.training else None], i=[NP, fint, pin.v.sw]))
         bp = self.bn_finalize(a + ".psi.1", 1, rows, NP, self.part)
         self.F(eo.ew(L.EW_GATE_APPLY, p=[pre, bp, skip.v, outS, psi], i=[NP, skip.v.c, skip.v.sw, outS.sw]))
+        self.stored.update({f"att{k}.yg": yg, f"att{k}.ys": ys, f"att{k}.pin": pin.v,
+                            f"att{k}.pre": pre.view(N, 1, hh, ww), f"att{k}.out": outS})
 
         def bwd():
             dz = self._alloc((NP,), F32)
@@ -495,6 +519,7 @@ class UNetPlan:
             self.bn_backward(a + ".W_x.1", pin.g, pin.v, ys, bs, dys, dbias=self.gview(a + ".W_x.0.bias"))
             self.conv_backward(up, dyg, a + ".W_g.0.weight", 1, 1)
             self.conv_backward(skip, dys, a + ".W_x.0.weight", 1, 1)
+            self.stored_g.update({f"att{k}.yg": dyg, f"att{k}.ys": dys, f"att{k}.pin": pin.g, f"att{k}.out": doutS})
 
         self.tape.append(bwd)
 
@@ -519,8 +544,21 @@ class UNetPlan:
                                              self.gview(n2), dpool], i=[N, hw, C_, ch, rows, 0]))
             self.B(eo.ew(L.EW_SE_BWD_APPLY, p=[out.g, saved, dpool, b.g], i=[N, hw, C_, out.g.sw, b.g.sw]))
             b.gw = True
+            self.stored_g[f"se{k}.out"] = out.g
 
         self.tape.append(bwd)
+
+    def stored_nchw(self, grads=False):
+        """Host copies (NCHW fp32) of every stored activation (or, with grads=True, of the
+        gradient w.r.t. it after a backward pass), keyed like oracle.unet_functional's storage
+        points."""
+        out = {}
+        for name, v in (self.stored_g if grads else self.stored).items():
+            if torch.is_tensor(v):
+                out[name] = v.detach().float().cpu().clone()
+            else:
+                out[name] = v.torch().float().cpu().permute(0, 3, 1, 2).contiguous()
+        return out
 
     # ---------------------------------------------------------------- execution ----
     def params_moved(self) -> bool:

@@ -60,41 +60,80 @@ class _BN:
                             sd[p + ".weight"], sd[p + ".bias"], self.training, 0.1, 1e-5)
 
 
-_STORE = [None]
-
-
-def _store(t):
-    return _STORE[0](t) if _STORE[0] is not None else t
-
-
 def bf16_round(t):
     """Round to the nearest bf16 value, keep fp32 storage (straight-through for autograd)."""
     return t + (t.detach().to(torch.bfloat16).float() - t.detach())
 
 
+def teacher_store(values, computed=None, grad_round=None, grads=None):
+    """`store` hook that replaces every named storage point by the tensor in `values` (NCHW fp32,
+    e.g. what the B200 plan holds in HBM) with a straight-through gradient, and records what the
+    oracle itself computed from the substituted upstream values in `computed`.  Downstream layers
+    and the whole backward pass then see exactly the product's forward activations, so layer-level
+    parity is free of the chaotic bf16 drift a free-running comparison accumulates.
+    `grad_round` (e.g. bf16_round) is applied to the gradient arriving at every storage point:
+    the statistical twin of the product's bf16 gradient buffers.  `grads` (dict) receives the
+    gradient w.r.t. every storage point."""
+    def store(name, t, pre=None):
+        if computed is not None:
+            computed[name] = t.detach()
+        v = values.get(name)
+        if v is not None:
+            v = v.to(t.dtype).reshape(t.shape)
+            if pre is not None:
+                # ReLU output: gradient flows where the SUBSTITUTED activation is positive, so a
+                # pre-activation within rounding distance of 0 cannot flip the mask between the
+                # two implementations (a handful of such flips dominate heavy-tailed gradients)
+                lin = pre * (v > 0).to(pre.dtype)
+                t = v + (lin - lin.detach())
+            else:
+                t = t + (v - t.detach())
+        if grads is not None and t.requires_grad:  # gradient w.r.t. this storage point
+            t.register_hook(lambda g, name=name: grads.__setitem__(name, g.detach().clone()))
+        if grad_round is not None and t.requires_grad:
+            # the product keeps activation gradients in bf16 at these same points
+            t.register_hook(lambda g: grad_round(g.detach()))
+        return t
+    return store
+
+
 def unet_forward(sd, x, backbone="resnet34", use_attention=True, training=True, new_stats=None,
-                 taps=None, storage_round=None):
+                 taps=None, storage_round=None, store=None):
     """logits = UNetWithBackbone.forward(x) (advanced_models.py:264-357) from state dict `sd`.
 
     `taps` (optional dict) receives named intermediate activations for layer-level parity.
-    `storage_round` (e.g. bf16_round) is applied to every conv weight, every conv output and every
-    stored activation: the "same arithmetic, bf16 storage" comparator for the B200 path, which
-    keeps activations in bf16 between kernels (all sums still accumulate in fp32)."""
+    `storage_round` (e.g. bf16_round) is applied to every tensor-core conv weight and to every
+    activation the B200 path stores in HBM between kernels: the "same arithmetic, bf16 storage"
+    comparator (all sums still accumulate in fp32).  `store(name, tensor) -> tensor` is called at
+    each of those storage points after rounding (see teacher_store)."""
     kind, depths = RESNET_LAYERS[backbone]
-    if storage_round is not None:
-        return _unet_forward_rounded(sd, x, backbone, use_attention, training, new_stats, taps, storage_round)
+    q = storage_round if storage_round is not None else (lambda t: t)
+
+    def st(name, t):
+        t = q(t)
+        if store is not None:
+            t = store(name, t)
+        if taps is not None:
+            taps[name] = t
+        return t
+
+    def relu_st(name, pre):  # ReLU whose output is a storage point
+        t = q(F.relu(pre))
+        if store is not None:
+            t = store(name, t, pre)
+        if taps is not None:
+            taps[name] = t
+        return t
 
     def bn(prefix):
         return _BN(sd, prefix, training, new_stats)
 
-    def tap(name, v):
-        if taps is not None:
-            taps[name] = v
-        return v
+    def conv(name, inp, wkey, bkey=None, stride=1, pad=0):  # tensor-core conv: bf16 weights + output
+        return st(name, F.conv2d(inp, q(sd[wkey]), sd[bkey] if bkey else None, stride, pad))
 
-    # stem: 7x7 s2 conv (1 input channel), BN, ReLU (:268-270); 3x3 s2 max-pool (:272)
-    x1 = F.relu(bn("bn1")(F.conv2d(x, sd["input_conv.weight"], None, 2, 3)))
-    tap("x1", x1)
+    # stem: 7x7 s2 conv (1 input channel, fp32 weights), BN, ReLU (:268-270); 3x3 s2 max-pool (:272)
+    y0 = st("stem.y", F.conv2d(x, sd["input_conv.weight"], None, 2, 3))
+    x1 = relu_st("x1", (bn("bn1")(y0)))
     h = F.max_pool2d(x1, 3, 2, 1)
     skips = [x1]
     for li, nblocks in enumerate(depths, start=1):  # enc1..enc4 (:273-276), torchvision blocks
@@ -103,44 +142,48 @@ def unet_forward(sd, x, backbone="resnet34", use_attention=True, training=True, 
             stride = 2 if (li > 1 and bi == 0) else 1
             idt = h
             if kind == "basic":
-                o = F.relu(bn(pre + ".bn1")(F.conv2d(h, sd[pre + ".conv1.weight"], None, stride, 1)))
-                o = bn(pre + ".bn2")(F.conv2d(o, sd[pre + ".conv2.weight"], None, 1, 1))
+                o = relu_st(pre + ".a1", (bn(pre + ".bn1")(conv(pre + ".y1", h, pre + ".conv1.weight", None, stride, 1))))
+                o = bn(pre + ".bn2")(conv(pre + ".y2", o, pre + ".conv2.weight", None, 1, 1))
             else:  # Bottleneck v1.5: stride on the 3x3
-                o = F.relu(bn(pre + ".bn1")(F.conv2d(h, sd[pre + ".conv1.weight"])))
-                o = F.relu(bn(pre + ".bn2")(F.conv2d(o, sd[pre + ".conv2.weight"], None, stride, 1)))
-                o = bn(pre + ".bn3")(F.conv2d(o, sd[pre + ".conv3.weight"]))
+                o = relu_st(pre + ".a1", (bn(pre + ".bn1")(conv(pre + ".y1", h, pre + ".conv1.weight"))))
+                o = relu_st(pre + ".a2", (bn(pre + ".bn2")(conv(pre + ".y2", o, pre + ".conv2.weight", None, stride, 1))))
+                o = bn(pre + ".bn3")(conv(pre + ".y3", o, pre + ".conv3.weight"))
             if pre + ".downsample.0.weight" in sd:
-                idt = bn(pre + ".downsample.1")(F.conv2d(h, sd[pre + ".downsample.0.weight"], None, stride))
-            h = F.relu(o + idt)
-        tap(f"x{li + 1}", h)
+                idt = bn(pre + ".downsample.1")(conv(pre + ".yd", h, pre + ".downsample.0.weight", None, stride))
+            h = relu_st(pre + ".out", (o + idt))
+        if taps is not None:
+            taps[f"x{li + 1}"] = h
         skips.append(h)
     x1, x2, x3, x4, x5 = skips
 
     def gate(k, g, s):  # AttentionGate.forward (:28-40)
         a = f"attention{k}"
-        g1 = bn(a + ".W_g.1")(F.conv2d(g, sd[a + ".W_g.0.weight"], sd[a + ".W_g.0.bias"]))
-        s1 = bn(a + ".W_x.1")(F.conv2d(s, sd[a + ".W_x.0.weight"], sd[a + ".W_x.0.bias"]))
-        psi = F.relu(g1 + s1)
-        psi = torch.sigmoid(bn(a + ".psi.1")(F.conv2d(psi, sd[a + ".psi.0.weight"], sd[a + ".psi.0.bias"])))
-        return _store(s * psi)
+        g1 = bn(a + ".W_g.1")(conv(f"att{k}.yg", g, a + ".W_g.0.weight", a + ".W_g.0.bias"))
+        s1 = bn(a + ".W_x.1")(conv(f"att{k}.ys", s, a + ".W_x.0.weight", a + ".W_x.0.bias"))
+        psi = relu_st(f"att{k}.pin", (g1 + s1))
+        pre = F.conv2d(psi, sd[a + ".psi.0.weight"], sd[a + ".psi.0.bias"])  # 1 channel: fp32 path
+        if store is not None:
+            pre = store(f"att{k}.pre", pre)
+        psi = torch.sigmoid(bn(a + ".psi.1")(pre))
+        return st(f"att{k}.out", s * psi)
 
-    def squeeze_excite(k, d):  # ChannelAttention.forward (:57-61); fc shared by both pools
+    def squeeze_excite(k, d):  # ChannelAttention.forward (:57-61); fc shared by both pools (fp32)
         c = f"ch_attention{k}"
 
         def fc(v):
             return F.conv2d(F.relu(F.conv2d(v, sd[c + ".fc.0.weight"])), sd[c + ".fc.2.weight"])
 
         w = fc(F.adaptive_avg_pool2d(d, 1)) + fc(F.adaptive_max_pool2d(d, 1))
-        return _store(d * torch.sigmoid(w))
+        return st(f"se{k}.out", d * torch.sigmoid(w))
 
     def dec_block(k, d):  # _decoder_block (:197-205)
         p = f"decoder{k}"
-        d = F.relu(bn(p + ".1")(F.conv2d(d, sd[p + ".0.weight"], sd[p + ".0.bias"], 1, 1)))
-        return F.relu(bn(p + ".4")(F.conv2d(d, sd[p + ".3.weight"], sd[p + ".3.bias"], 1, 1)))
+        d = relu_st(f"dec{k}.a", (bn(p + ".1")(conv(f"dec{k}.ya", d, p + ".0.weight", p + ".0.bias", 1, 1))))
+        return relu_st(f"dec{k}.b", (bn(p + ".4")(conv(f"dec{k}.yb", d, p + ".3.weight", p + ".3.bias", 1, 1))))
 
     d = x5
     for k, skip in ((4, x4), (3, x3), (2, x2), (1, x1)):  # (:284-334)
-        d = F.conv_transpose2d(d, sd[f"upconv{k}.weight"], sd[f"upconv{k}.bias"], 2)
+        d = st(f"up{k}", F.conv_transpose2d(d, q(sd[f"upconv{k}.weight"]), sd[f"upconv{k}.bias"], 2))
         if k == 1 and d.shape != skip.shape:  # centre crop only when both diffs > 0 (:318-325)
             dh, dw = skip.shape[2] - d.shape[2], skip.shape[3] - d.shape[3]
             if dh > 0 and dw > 0:
@@ -149,40 +192,17 @@ def unet_forward(sd, x, backbone="resnet34", use_attention=True, training=True, 
         d = dec_block(k, torch.cat((s, d), dim=1))  # skip FIRST (:288,292,...)
         if use_attention:
             d = squeeze_excite(k, d)
-        tap(f"d{k}", d)
-    d0 = F.conv_transpose2d(d, sd["upconv0.weight"], sd["upconv0.bias"], 2)  # (:337)
+        if taps is not None:
+            taps[f"d{k}"] = d
+    d0 = st("d0", F.conv_transpose2d(d, q(sd["upconv0.weight"]), sd["upconv0.bias"], 2))  # (:337)
     if d0.shape[2] != x.shape[2] or d0.shape[3] != x.shape[3]:  # (:340-347)
         dh, dw = d0.shape[2] - x.shape[2], d0.shape[3] - x.shape[3]
         if dh > 0 or dw > 0:
             d0 = d0[:, :, dh // 2:dh // 2 + x.shape[2], dw // 2:dw // 2 + x.shape[3]]
-    return F.conv2d(d0, sd["conv_final.weight"], sd["conv_final.bias"])  # (:350)
-
-
-def _unet_forward_rounded(sd, x, backbone, use_attention, training, new_stats, taps, q):
-    """Same network with `q` applied at every point where the B200 path stores bf16."""
-    import contextlib
-    orig = dict(conv2d=F.conv2d, conv_transpose2d=F.conv_transpose2d, relu=F.relu, batch_norm=F.batch_norm)
-
-    def conv2d(inp, w, b=None, *a, **k):
-        if w.shape[1] == 1 and w.shape[2] == 7:      # stem: fp32 weights and input, bf16 output
-            return q(orig["conv2d"](inp, w, b, *a, **k))
-        if w.shape[0] == 1 or inp.shape[2] * inp.shape[3] == 1:   # 1-channel convs / SE MLP: fp32
-            return orig["conv2d"](inp, w, b, *a, **k)
-        return q(orig["conv2d"](inp, q(w), b, *a, **k))
-
-    def conv_transpose2d(inp, w, b=None, *a, **k):
-        return q(orig["conv_transpose2d"](inp, q(w), b, *a, **k))
-
-    def relu(t, *a, **k):
-        return q(orig["relu"](t, *a, **k))
-
-    F.conv2d, F.conv_transpose2d, F.relu = conv2d, conv_transpose2d, relu
-    _STORE[0] = q
-    try:
-        return unet_forward(sd, x, backbone, use_attention, training, new_stats, taps, None)
-    finally:
-        _STORE[0] = None
-        F.conv2d, F.conv_transpose2d, F.relu = orig["conv2d"], orig["conv_transpose2d"], orig["relu"]
+    logits = F.conv2d(d0, sd["conv_final.weight"], sd["conv_final.bias"])  # (:350), fp32 path
+    if store is not None:
+        logits = store("logits", logits)
+    return logits
 
 
 def forward_backward(sd, x, target, loss_fn, **kw):
