@@ -56,10 +56,11 @@ class View:
 class Op:
     """Owns one planned op of libb2seg (and keeps its tensors alive)."""
 
-    def __init__(self, handle, keep, kind):
+    def __init__(self, handle, keep, kind, flops=0.0):
         self.handle = handle
         self.keep = keep
         self.kind = kind
+        self.flops = float(flops)  # algorithmic 2*M*N*K of a tensor-core op (bench roofline)
 
     def run(self):
         L.check(L.lib().b2seg_op_run(self.handle, L.stream_ptr()))
@@ -90,6 +91,12 @@ class Seq:
 
     def run(self):
         L.check(L.lib().b2seg_seq_run(self.handle, L.stream_ptr()))
+
+    def run_timed(self):
+        """Replay with an event pair around every op; returns per-op milliseconds (synchronises)."""
+        ms = (C.c_float * len(self.ops))()
+        L.check(L.lib().b2seg_seq_run_timed(self.handle, L.stream_ptr(), ms, len(self.ops)))
+        return list(ms)
 
     @property
     def launches(self):
@@ -161,7 +168,8 @@ def _fill_sub(sub, taps, out_offset=0):
 def _create_tapgemm(d, keep, kind):
     h = C.c_void_p()
     L.check(L.lib().b2seg_tapgemm_create(C.byref(d), C.byref(h)))
-    return Op(h, keep, kind)
+    taps = sum(d.sub[s].ntaps for s in range(d.nsub))
+    return Op(h, keep, kind, flops=2.0 * d.on * d.oh * d.ow * d.ngemm * d.cin * taps)
 
 
 def _srcs(d, views):
@@ -271,7 +279,7 @@ def wgrad_workspace_bytes(a_ch, b_ch, ntaps, n, h, w) -> int:
 def _create_wgrad(d, keep, kind):
     h = C.c_void_p()
     L.check(L.lib().b2seg_wgrad_create(C.byref(d), C.byref(h)))
-    return Op(h, keep, kind)
+    return Op(h, keep, kind, flops=2.0 * d.pn * d.ph * d.pw * d.a_src[0].c * d.b_src.c * d.ntaps)
 
 
 def conv_wgrad(x: View, dy: View, k: int, stride: int, grad: torch.Tensor, ws: torch.Tensor,

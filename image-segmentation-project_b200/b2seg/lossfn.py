@@ -123,3 +123,8 @@ def metrics_dict(stats_host, eps: float = 1e-7) -> dict:
         "iou": tp / (tp + fp + fn + eps),
         "accuracy": (tp + tn) / (tp + tn + fp + fn + eps),
     }
+
+
+# kernel launches one loss forward / backward enqueues (bench accounting; csrc/seg_loss.cu)
+LAUNCHES_FWD = 1
+LAUNCHES_BWD = 1

@@ -377,6 +377,26 @@ extern "C" int b2seg_seq_run(b2seg_seq* seq, void* stream) {
   }
   return B2SEG_OK;
 }
+extern "C" int b2seg_seq_run_timed(b2seg_seq* seq, void* stream, float* ms, int n_ops) {
+  B2_REQUIRE(seq && ms, "seq_run_timed: null");
+  B2_REQUIRE(n_ops == (int)seq->ops.size(), "seq_run_timed: n_ops %d != %d", n_ops,
+             (int)seq->ops.size());
+  cudaStream_t st = (cudaStream_t)stream;
+  std::vector<cudaEvent_t> ev(seq->ops.size() + 1);
+  for (auto& e : ev) B2_CHECK_CUDA(cudaEventCreate(&e));
+  int rc = B2SEG_OK;
+  B2_CHECK_CUDA(cudaEventRecord(ev[0], st));
+  for (size_t i = 0; i < seq->ops.size() && rc == B2SEG_OK; ++i) {
+    rc = seq->ops[i]->run(st);
+    cudaEventRecord(ev[i + 1], st);
+  }
+  cudaError_t err = cudaStreamSynchronize(st);
+  if (rc == B2SEG_OK && err == cudaSuccess)
+    for (size_t i = 0; i < seq->ops.size(); ++i) cudaEventElapsedTime(&ms[i], ev[i], ev[i + 1]);
+  for (auto& e : ev) cudaEventDestroy(e);
+  B2_CHECK_CUDA(err);
+  return rc;
+}
 extern "C" int b2seg_seq_launches(const b2seg_seq* seq) {
   int n = 0;
   if (seq)

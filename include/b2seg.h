@@ -159,6 +159,10 @@ int b2seg_seq_create(b2seg_seq** out);
 int b2seg_seq_append(b2seg_seq* seq, b2seg_op* op); /* does not take ownership */
 int b2seg_seq_run(b2seg_seq* seq, void* stream);
 int b2seg_seq_launches(const b2seg_seq* seq);
+/* Replays the sequence with a CUDA event pair around every op, synchronises the stream and
+ * writes each op's elapsed milliseconds to ms_per_op[0..n_ops) (profiling aid for bench.py's
+ * per-kernel roofline; not for the timed path). */
+int b2seg_seq_run_timed(b2seg_seq* seq, void* stream, float* ms_per_op /*host*/, int n_ops);
 int b2seg_seq_destroy(b2seg_seq* seq);
 
 /* NHWC bf16 activation view; strides in ELEMENTS, channel stride is 1.  A

@@ -1,0 +1,173 @@
+"""UNetWithBackbone on the B200 kernel plan vs the fp32 oracle restatement of the reference's
+forward/backward (oracle/unet_functional.py, itself pinned to reference fixtures in
+tests/test_oracle_cpu.py).
+
+The product stores activations in bf16 between kernels, the reference in fp32.  A free-running
+comparison of two 100-layer random-weight networks is dominated by that storage noise being
+amplified layer after layer (train-mode BatchNorm on 8x8 maps has a population of a few
+hundred values), which says nothing about kernel correctness.  The tests therefore compare
+*teacher-forced*: the oracle is fed the product's own stored activation at every storage point
+(straight-through for gradients), so each layer's forward output and each parameter gradient is
+checked on identical inputs.
+
+Tolerances (written here because `north_star` asks for stated tolerances):
+  * every stored activation:  ||ours - oracle|| / ||oracle|| <= 6e-3   (bf16 has 2^-9 = 2e-3
+    relative rounding; fp32 accumulation on both sides),
+  * loss on identical logits: 1e-3 relative (north_star) -- in fact ~1e-6,
+  * every parameter gradient: cosine >= 0.995 and relative L2 error <= max(8e-2, 4 x the
+    error of the oracle's own "bf16 activation-gradient" twin) -- gradients pass through
+    bf16 buffers ~60 times,
+  * free-running logits vs the fp32 reference: reported, bounded loosely (<= 0.35 rel).
+"""
+import copy
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel(a, b):
+    a, b = a.double().flatten(), b.double().flatten()
+    return float((a - b).norm() / b.norm().clamp(min=1e-30))
+
+
+def _cos(a, b):
+    a, b = a.double().flatten(), b.double().flatten()
+    return float((a @ b) / (a.norm() * b.norm()).clamp(min=1e-30))
+
+
+def _build(backbone, attn, seed=5):
+    import advanced_models
+    torch.manual_seed(seed)
+    model = advanced_models.UNetWithBackbone(1, backbone, pretrained=False, use_attention=attn)
+    sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    return model, sd
+
+
+CASES = [
+    ("resnet34", True, 64, 2, "combo"),
+    ("resnet34", False, 64, 2, "dice"),
+    ("resnet34", True, 128, 4, "combo"),
+    ("resnet50", False, 64, 2, "bce"),
+    ("resnet50", True, 64, 2, "focal"),
+    ("resnet34", True, 96, 1, "tversky"),   # 3x3 grid at enc4, batch 1
+]
+
+
+@pytest.mark.parametrize("backbone,attn,size,batch,loss_name", CASES)
+def test_train_step_teacher_forced(cuda, backbone, attn, size, batch, loss_name):
+    import losses
+    from b2seg import synth
+    from oracle import seg_losses, unet_functional as uf
+
+    model, sd = _build(backbone, attn)
+    model = model.to(cuda).train()
+    x, t = synth.cell_tiles(batch, size, seed=77)
+    logits = model(x.to(cuda))
+    crit = losses.get_loss_function({"loss_fn": loss_name})
+    loss = crit(logits, t.to(cuda))
+    loss.backward()
+    torch.cuda.synchronize()
+    plan = next(iter(model._plans.values()))
+    ours = plan.stored_nchw()
+
+    computed = {}
+    loss_fn = lambda lg, tt: seg_losses.loss_value(loss_name, lg, tt).float()
+    _, ref_loss, ref_grads = uf.forward_backward(
+        sd, x, t, loss_fn, backbone=backbone, use_attention=attn, training=True,
+        store=uf.teacher_store(ours, computed))
+    _, _, twin = uf.forward_backward(
+        sd, x, t, loss_fn, backbone=backbone, use_attention=attn, training=True,
+        store=uf.teacher_store(ours, None, grad_round=uf.bf16_round))
+
+    # forward: every storage point, on identical inputs
+    worst = max((_rel(v, computed[n]), n) for n, v in ours.items())
+    assert worst[0] <= 6e-3, worst
+    assert abs(float(loss) - ref_loss) <= 1e-3 * abs(ref_loss)
+
+    # backward: every parameter gradient
+    params = dict(model.named_parameters())
+    gmax = max(float(v.norm()) for v in ref_grads.values() if v is not None)
+    checked = 0
+    for n, p in params.items():
+        rg = ref_grads[n]
+        if rg is None:
+            continue
+        assert p.grad is not None, n
+        if float(rg.norm()) < 1e-5 * gmax:  # conv bias in front of BatchNorm: exactly-zero gradient
+            assert float(p.grad.norm()) < 1e-3 * gmax, n
+            continue
+        pg = p.grad.cpu()
+        tol = max(8e-2, 4 * _rel(twin[n], rg))
+        assert _cos(pg, rg) >= 0.995, (n, _cos(pg, rg))
+        assert _rel(pg, rg) <= tol, (n, _rel(pg, rg), tol)
+        checked += 1
+    assert checked > 100
+
+    # running statistics follow nn.BatchNorm2d (momentum 0.1, unbiased variance)
+    new_stats = {}
+    uf.unet_forward(sd, x, backbone=backbone, use_attention=attn, training=True, new_stats=new_stats,
+                    store=uf.teacher_store(ours))
+    state = model.state_dict()
+    for k, v in new_stats.items():
+        got = state[k].float().cpu()
+        assert torch.allclose(got, v.float(), rtol=2e-2, atol=2e-3), k
+
+
+@pytest.mark.parametrize("backbone,attn", [("resnet34", True), ("resnet50", False)])
+def test_eval_forward_matches_oracle(cuda, backbone, attn):
+    """model.eval(): running statistics, no_grad; free-running comparison is meaningful here
+    because eval-mode BatchNorm does not renormalise the noise."""
+    from b2seg import synth
+    from oracle import unet_functional as uf
+    model, sd = _build(backbone, attn, seed=9)
+    sd = uf.synth_state(sd, seed=3)  # non-trivial running stats / affine parameters
+    model.load_state_dict(sd)
+    model = model.to(cuda).eval()
+    x, _ = synth.cell_tiles(2, 64, seed=3)
+    with torch.no_grad():
+        got = model(x.to(cuda)).cpu()
+    ref = uf.unet_forward(sd, x, backbone=backbone, use_attention=attn, training=False)
+    twin = uf.unet_forward(sd, x, backbone=backbone, use_attention=attn, training=False,
+                           storage_round=uf.bf16_round)
+    # the bf16-storage twin of the oracle bounds what storage rounding alone does
+    assert _rel(got, ref) <= max(3e-2, 3 * _rel(twin, ref)), (_rel(got, ref), _rel(twin, ref))
+    # state dict untouched by an eval forward
+    for k, v in model.state_dict().items():
+        assert torch.equal(v.cpu(), sd[k]), k
+
+
+def test_module_contract(cuda):
+    """What the reference's callers rely on (cross_validation.py:84-100, train.py:207-226)."""
+    from oracle.state_layout import reference_state_shapes
+    model, sd = _build("resnet34", True)
+    ref_shapes = reference_state_shapes("resnet34", True)
+    assert [(k, tuple(v.shape)) for k, v in sd.items()] == [(k, tuple(v.shape)) for k, v in ref_shapes.items()]
+    model = model.to(cuda)
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3, weight_decay=1e-5)
+    x = torch.rand(2, 1, 64, 64, device=cuda)
+    t = (torch.rand(2, 1, 64, 64, device=cuda) > 0.8).float()
+    import losses
+    crit = losses.get_loss_function({"loss_fn": "combo"})
+    first = None
+    for _ in range(8):
+        out = model(x)
+        assert out.shape == (2, 1, 64, 64) and out.dtype == torch.float32
+        loss = crit(out, t)
+        opt.zero_grad()
+        loss.backward()
+        opt.step()
+        first = first if first is not None else float(loss)
+    assert float(loss) < first  # Adam on one batch must reduce the loss
+    best = copy.deepcopy(model.state_dict())
+    model.load_state_dict(best)
+    model.eval()
+    with torch.no_grad():
+        a = model(x)
+        b = model(x)
+    assert torch.equal(a, b)  # deterministic replay
+    with pytest.raises(Exception):
+        model(torch.rand(2, 1, 100, 100, device=cuda))  # reference crashes in torch.cat too
+    with pytest.raises(Exception):
+        model.cpu()(torch.rand(1, 1, 64, 64))  # no CPU fallback
