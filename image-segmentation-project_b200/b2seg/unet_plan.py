@@ -328,7 +328,7 @@ class UNetPlan:
         start = 0
         for j, (p, out, T, A, B_, sa, sb, st) in enumerate(self.pack_jobs):
             jobs[j] = L.PackJob(p.data_ptr(), out.data_ptr(), T, A, B_, 0, sa, sb, st, start)
-            start += T * A * B_
+            start += ((A + 31) // 32) * ((B_ + 31) // 32)  # job.start = first 32x32xT tile
         raw = torch.frombuffer(bytearray(bytes(jobs)), dtype=torch.uint8).to(self.dev)
         self.keep.append(raw)
         self.pack_op = eo.ew(L.EW_PACK, p=[raw], i=[len(self.pack_jobs), start])

@@ -9,7 +9,7 @@
 namespace {
 
 // ------------------------------------------------------------------ BN_FINALIZE ----
-// block = (32 channels, 32 row lanes); fp64 accumulation of the fp32 block partials.
+// grid (C/32, slices), block (32 channels, 32 row lanes): see ew_rows_reduce.
 __global__ void __launch_bounds__(1024) bn_finalize_kernel(const EwArgs a) {
   const float* partial = (const float*)a.p[0];
   const float* gamma = (const float*)a.p[1];
@@ -22,27 +22,11 @@ __global__ void __launch_bounds__(1024) bn_finalize_kernel(const EwArgs a) {
   const double count = (double)a.i[2];
   const bool training = a.i[3] != 0;
   const float eps = a.f[0], mom = a.f[1];
-  const size_t rstep = (size_t)(a.i[4] > 0 ? a.i[4] : 1) * 2 * C;  // floats between consecutive rows
-  __shared__ double sh[2][32][33];
-  const int tx = threadIdx.x, ty = threadIdx.y;
-  const int c = blockIdx.x * 32 + tx;
-  double s = 0.0, q = 0.0;
-  if (training && c < C) {
-    for (int r = ty; r < rows; r += 32) {
-      s += (double)partial[(size_t)r * rstep + c];
-      q += (double)partial[(size_t)r * rstep + C + c];
-    }
-  }
-  sh[0][ty][tx] = s;
-  sh[1][ty][tx] = q;
-  __syncthreads();
-  if (ty == 0 && c < C) {
+  ew_rows_reduce<2>(training ? partial : nullptr, rows, 2 * (long long)C, C, C, [&](int c, const double* v) {
     float mean, invstd;
     if (training) {
-      s = 0.0; q = 0.0;
-      for (int l = 0; l < 32; ++l) { s += sh[0][l][tx]; q += sh[1][l][tx]; }
-      const double m = s / count;
-      double var = q / count - m * m;
+      const double m = v[0] / count;
+      double var = v[1] / count - m * m;
       if (var < 0.0) var = 0.0;
       mean = (float)m;
       invstd = (float)(1.0 / sqrt(var + (double)eps));
@@ -51,6 +35,7 @@ __global__ void __launch_bounds__(1024) bn_finalize_kernel(const EwArgs a) {
         rmean[c] = (1.0f - mom) * rmean[c] + mom * mean;
         rvar[c] = (1.0f - mom) * rvar[c] + mom * (float)unb;
       }
+      if (nbt && c == 0) *nbt += 1;
     } else {
       mean = rmean[c];
       invstd = 1.0f / sqrtf(rvar[c] + eps);
@@ -61,27 +46,7 @@ __global__ void __launch_bounds__(1024) bn_finalize_kernel(const EwArgs a) {
     bnp[C + c] = b - mean * scale;
     bnp[2 * C + c] = mean;
     bnp[3 * C + c] = invstd;
-  }
-  if (training && nbt && blockIdx.x == 0 && tx == 0 && ty == 0) *nbt += 1;
-}
-
-// Folds `chunk` consecutive partial rows into the first row of each chunk (in place), so the
-// finalize kernel above never walks more than a few thousand rows with its C/32 blocks.
-__global__ void __launch_bounds__(1024) rows_fold_kernel(float* partial, int rows, int width, int chunk) {
-  __shared__ double sh[32][33];
-  const int tx = threadIdx.x, ty = threadIdx.y;
-  const int col = blockIdx.x * 32 + tx;
-  const int r0 = blockIdx.y * chunk, r1 = min(rows, r0 + chunk);
-  double s = 0.0;
-  if (col < width)
-    for (int r = r0 + ty; r < r1; r += 32) s += (double)partial[(size_t)r * width + col];
-  sh[ty][tx] = s;
-  __syncthreads();
-  if (ty == 0 && col < width && r0 < rows) {
-    s = 0.0;
-    for (int l = 0; l < 32; ++l) s += sh[l][tx];
-    partial[(size_t)r0 * width + col] = (float)s;
-  }
+  });
 }
 
 // -------------------------------------------------------------------- BN_APPLY ----
@@ -184,22 +149,8 @@ __global__ void __launch_bounds__(1024) bn_bwd_finalize_kernel(const EwArgs a) {
   const int rows = (int)a.i[0], C = (int)a.i[1];
   const double count = (double)a.i[2];
   const bool accumulate = a.i[3] != 0, training = a.i[4] != 0;
-  __shared__ double sh[2][32][33];
-  const int tx = threadIdx.x, ty = threadIdx.y;
-  const int c = blockIdx.x * 32 + tx;
-  double s = 0.0, q = 0.0;
-  if (c < C) {
-    for (int r = ty; r < rows; r += 32) {
-      s += (double)partial[((size_t)r * 2) * C + c];
-      q += (double)partial[((size_t)r * 2 + 1) * C + c];
-    }
-  }
-  sh[0][ty][tx] = s;
-  sh[1][ty][tx] = q;
-  __syncthreads();
-  if (ty == 0 && c < C) {
-    s = 0.0; q = 0.0;
-    for (int l = 0; l < 32; ++l) { s += sh[0][l][tx]; q += sh[1][l][tx]; }
+  ew_rows_reduce<2>(partial, rows, 2 * (long long)C, C, C, [&](int c, const double* v) {
+    const double s = v[0], q = v[1];
     const float g = gamma ? gamma[c] : 1.0f;
     const float c1 = g * bnp[3 * C + c];
     if (dgamma) dgamma[c] = accumulate ? dgamma[c] + (float)q : (float)q;
@@ -208,10 +159,10 @@ __global__ void __launch_bounds__(1024) bn_bwd_finalize_kernel(const EwArgs a) {
     coef[C + c] = training ? (float)(s / count) : 0.0f;
     coef[2 * C + c] = training ? (float)(q / count) : 0.0f;
     if (dbias) {  // gradient of a conv bias feeding this BN: sum of dy (0 with batch statistics)
-      const float v = training ? 0.0f : c1 * (float)s;
-      dbias[c] = accumulate ? dbias[c] + v : v;
+      const float vb = training ? 0.0f : c1 * (float)s;
+      dbias[c] = accumulate ? dbias[c] + vb : vb;
     }
-  }
+  });
 }
 
 __global__ void __launch_bounds__(kEwThreads) bn_bwd_apply_kernel(const EwArgs a) {
@@ -258,49 +209,53 @@ __global__ void __launch_bounds__(kEwThreads) colsum_kernel(const EwArgs a) {
                        });
 }
 
-// out[k] (+)= sum_r partial[r*stride + k]; block = (32 k, 32 row lanes)
+// out[k] (+)= sum_r partial[r*stride + k]; grid (K/32, slices), block (32 k, 32 row lanes)
 __global__ void __launch_bounds__(1024) colsum_finalize_kernel(const EwArgs a) {
   const float* partial = (const float*)a.p[0];
   float* out = (float*)a.p[1];
   const int rows = (int)a.i[0], K = (int)a.i[1];
   const bool accumulate = a.i[2] != 0;
-  const long long stride = a.i[3];
-  __shared__ double sh[32][33];
-  const int tx = threadIdx.x, ty = threadIdx.y;
-  const int k = blockIdx.x * 32 + tx;
-  double s = 0.0;
-  if (k < K)
-    for (int r = ty; r < rows; r += 32) s += (double)partial[(size_t)r * stride + k];
-  sh[ty][tx] = s;
-  __syncthreads();
-  if (ty == 0 && k < K) {
-    s = 0.0;
-    for (int l = 0; l < 32; ++l) s += sh[l][tx];
-    out[k] = accumulate ? out[k] + (float)s : (float)s;
-  }
+  ew_rows_reduce<1>(partial, rows, a.i[3], 0, K, [&](int k, const double* v) {
+    out[k] = accumulate ? out[k] + (float)v[0] : (float)v[0];
+  });
 }
 
 // ------------------------------------------------------------------------ PACK ----
-// One launch repacks every fp32 parameter into its bf16 GEMM operand layouts.
+// One launch repacks every fp32 parameter into its bf16 GEMM operand layouts:
+// out[t][a][b] = bf16(in[a*sa + b*sb + t*st]).  One block per 32(a) x 32(b) x T tile (job.start =
+// first tile of the job): the tile is read along whichever of a / b is contiguous with the taps
+// in the parameter (coalesced), transposed through shared memory and written along b.
+constexpr int kPackT = 9;
 __global__ void __launch_bounds__(kEwThreads) pack_kernel(const EwArgs a) {
+  __shared__ float sm[kPackT * (32 * 33 + 1)];
   const b2seg_pack_job* jobs = (const b2seg_pack_job*)a.p[0];
   const int njobs = (int)a.i[0];
-  const long long total = a.i[1];
-  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total;
-       e += (long long)gridDim.x * blockDim.x) {
-    int lo = 0, hi = njobs - 1;
-    while (lo < hi) {  // last job with start <= e
-      const int mid = (lo + hi + 1) >> 1;
-      if (jobs[mid].start <= e) lo = mid; else hi = mid - 1;
-    }
-    const b2seg_pack_job j = jobs[lo];
-    const long long r = e - j.start;
-    const long long ab = (long long)j.A * j.B;
-    const int t = (int)(r / ab);
-    const long long r2 = r % ab;
-    const int ia = (int)(r2 / j.B), ib = (int)(r2 % j.B);
-    const float v = j.in[(long long)ia * j.sa + (long long)ib * j.sb + (long long)t * j.st];
-    ((bf16*)j.out)[r] = __float2bfloat16_rn(v);
+  const long long tile = blockIdx.x;
+  int lo = 0, hi = njobs - 1;
+  while (lo < hi) {  // last job with start <= tile
+    const int mid = (lo + hi + 1) >> 1;
+    if (jobs[mid].start <= tile) lo = mid; else hi = mid - 1;
+  }
+  const b2seg_pack_job j = jobs[lo];
+  const int tilesB = (j.B + 31) / 32;
+  const int lt = (int)(tile - j.start);
+  const int a0 = (lt / tilesB) * 32, b0 = (lt % tilesB) * 32;
+  const bool inner_b = j.sb < j.sa;
+  const int T = j.T, runlen = 32 * T;
+  for (int e = threadIdx.x; e < 32 * runlen; e += blockDim.x) {
+    const int u = e / runlen, r = e % runlen, v = r / T, t = r % T;
+    const int la = inner_b ? u : v, lb = inner_b ? v : u;
+    float val = 0.0f;
+    if (a0 + la < j.A && b0 + lb < j.B)
+      val = j.in[(long long)(a0 + la) * j.sa + (long long)(b0 + lb) * j.sb + (long long)t * j.st];
+    sm[t * (32 * 33 + 1) + la * 33 + lb] = val;
+  }
+  __syncthreads();
+  bf16* out = (bf16*)j.out;
+  for (int e = threadIdx.x; e < T * 1024; e += blockDim.x) {
+    const int lb = e & 31, la = (e >> 5) & 31, t = e >> 10;
+    if (a0 + la < j.A && b0 + lb < j.B)
+      out[((long long)t * j.A + a0 + la) * j.B + b0 + lb] = __float2bfloat16_rn(sm[t * (32 * 33 + 1) + la * 33 + lb]);
   }
 }
 
@@ -319,23 +274,7 @@ __global__ void __launch_bounds__(kEwThreads) fill_kernel(const EwArgs a) {
     B2_CHECK_CUDA(cudaGetLastError());                                                    \
     return B2SEG_OK;                                                                      \
   }
-int launch_bn_finalize(const EwArgs& a, dim3 grid, dim3 block, size_t smem, cudaStream_t st) {
-  EwArgs b = a;
-  const int rows = (int)a.i[0], C = (int)a.i[1];
-  if (a.i[3] && rows > 2048) {  // training with many conv tiles: two-level row reduction
-    const int chunk = (rows + 255) / 256, slices = (rows + chunk - 1) / chunk;
-    rows_fold_kernel<<<dim3((2 * C + 31) / 32, slices), dim3(32, 32), 0, st>>>((float*)a.p[0], rows,
-                                                                               2 * C, chunk);
-    B2_CHECK_CUDA(cudaGetLastError());
-    b.i[0] = slices;
-    b.i[4] = chunk;
-  } else {
-    b.i[4] = 1;
-  }
-  bn_finalize_kernel<<<grid, block, smem, st>>>(b);
-  B2_CHECK_CUDA(cudaGetLastError());
-  return B2SEG_OK;
-}
+EW_LAUNCHER(launch_bn_finalize, bn_finalize_kernel)
 EW_LAUNCHER(launch_bn_apply, bn_apply_kernel)
 EW_LAUNCHER(launch_bn_bwd_reduce, bn_bwd_reduce_kernel)
 EW_LAUNCHER(launch_bn_bwd_finalize, bn_bwd_finalize_kernel)
@@ -362,10 +301,10 @@ int ew_plan_bn(const b2seg_ew_desc* d, EwPlan* pl) {
       B2_REQUIRE(p[6] && i[1] >= 1 && i[2] >= 1, "bn_finalize: bad arguments");
       B2_REQUIRE(!i[3] || (p[0] && i[0] >= 1), "bn_finalize: training needs partial sums");
       B2_REQUIRE(i[3] || (p[3] && p[4]), "bn_finalize: eval needs running statistics");
+      B2_REQUIRE((i[1] + 31) / 32 <= kFinMaxColBlocks, "bn_finalize: too many channels");
       pl->fn = launch_bn_finalize;
-      pl->grid = dim3((unsigned)((i[1] + 31) / 32));
+      pl->grid = dim3((unsigned)((i[1] + 31) / 32), i[3] ? ew_fin_slices(i[0], (int)((i[1] + 31) / 32)) : 1);
       pl->block = dim3(32, 32);
-      pl->launches = (i[3] && i[0] > 2048) ? 2 : 1;
       return B2SEG_OK;
     }
     case B2SEG_EW_BN_APPLY: {
@@ -404,8 +343,9 @@ int ew_plan_bn(const b2seg_ew_desc* d, EwPlan* pl) {
     case B2SEG_EW_BN_BWD_FINALIZE: {
       B2_REQUIRE(p[0] && p[2] && p[5] && i[0] >= 1 && i[1] >= 1 && i[2] >= 1,
                  "bn_bwd_finalize: bad arguments");
+      B2_REQUIRE((i[1] + 31) / 32 <= kFinMaxColBlocks, "bn_bwd_finalize: too many channels");
       pl->fn = launch_bn_bwd_finalize;
-      pl->grid = dim3((unsigned)((i[1] + 31) / 32));
+      pl->grid = dim3((unsigned)((i[1] + 31) / 32), ew_fin_slices(i[0], (int)((i[1] + 31) / 32)));
       pl->block = dim3(32, 32);
       return B2SEG_OK;
     }
@@ -420,15 +360,16 @@ int ew_plan_bn(const b2seg_ew_desc* d, EwPlan* pl) {
     }
     case B2SEG_EW_COLSUM_FINALIZE: {
       B2_REQUIRE(p[0] && p[1] && i[0] >= 1 && i[1] >= 1 && i[3] >= i[1], "colsum_finalize: bad arguments");
+      B2_REQUIRE((i[1] + 31) / 32 <= kFinMaxColBlocks, "colsum_finalize: too many columns");
       pl->fn = launch_colsum_finalize;
-      pl->grid = dim3((unsigned)((i[1] + 31) / 32));
+      pl->grid = dim3((unsigned)((i[1] + 31) / 32), ew_fin_slices(i[0], (int)((i[1] + 31) / 32)));
       pl->block = dim3(32, 32);
       return B2SEG_OK;
     }
     case B2SEG_EW_PACK: {
       B2_REQUIRE(p[0] && i[0] >= 1 && i[1] >= 1, "pack: bad arguments");
       pl->fn = launch_pack;
-      pl->grid = dim3(ew_blocks(i[1]));
+      pl->grid = dim3((unsigned)i[1]);  /* one block per 32 x 32 x T tile */
       pl->block = dim3(kEwThreads);
       return B2SEG_OK;
     }

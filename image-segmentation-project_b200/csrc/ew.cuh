@@ -49,6 +49,18 @@ static inline int ew_blocks(long long work_items) {  // elementwise grid: 256 th
   if (b < 1) b = 1;
   return (int)b;
 }
+// Number of row slices (gridDim.y) of a column-reduce finalize kernel: each (32 x 32)-thread
+// block then walks <= ~8 rows per thread; the last block to finish folds the slices.
+static inline int ew_fin_slices(long long rows, int colblocks) {
+  long long s = (rows + 255) / 256;
+  if (s > 64) s = 64;
+  while (s > 1 && s * colblocks > 1024) --s;
+  if (s < 1) s = 1;
+  return (int)s;
+}
+constexpr int kFinMaxColBlocks = 128;  // 4096 columns
+constexpr int kFinMaxSlices = 64;
+
 // sub-warp group size (power of two <= 32) for kernels that reduce over the channels of a pixel
 static inline int ew_group(int C) {
   const int cv = C / 8;
@@ -86,6 +98,66 @@ __device__ __forceinline__ F8 ld_f8(const float* p) {
   r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w;
   r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
   return r;
+}
+
+// Scratch of the column-reduce finalize kernels.  One set per device context: the kernels that
+// use it are enqueued on ONE stream by a plan (they never overlap each other).
+static __device__ double g_fin_scratch[kFinMaxColBlocks * kFinMaxSlices * 2 * 32];
+static __device__ unsigned g_fin_counters[kFinMaxColBlocks];
+
+// Deterministic sum over the rows of a block-partial buffer.  grid = (ceil(ncols/32), S),
+// block = (32 columns, 32 row lanes).  Accumulator k of column c in row r lives at
+// partial[r*rstride + k*koff + c].  Slice s sums rows s*32+ty, s*32+ty+32*S, ... in fp64; the
+// last slice block to arrive (atomic ticket) adds the S slice sums in slice order and calls
+// epi(c, sums) for its 32 columns -- the summation order is fixed, so results are bit-reproducible.
+template <int NACC, class Epi>
+__device__ __forceinline__ void ew_rows_reduce(const float* partial, int rows, long long rstride,
+                                               long long koff, int ncols, Epi epi) {
+  __shared__ double sh[NACC][32][33];
+  __shared__ int is_last;
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  const int c = blockIdx.x * 32 + tx;
+  const int S = gridDim.y, s = blockIdx.y;
+  double acc[NACC];
+#pragma unroll
+  for (int k = 0; k < NACC; ++k) acc[k] = 0.0;
+  if (c < ncols && partial != nullptr) {
+    for (int r = s * 32 + ty; r < rows; r += 32 * S) {
+#pragma unroll
+      for (int k = 0; k < NACC; ++k) acc[k] += (double)partial[(size_t)r * rstride + k * koff + c];
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < NACC; ++k) sh[k][ty][tx] = acc[k];
+  __syncthreads();
+  if (ty < NACC) {
+    double v = 0.0;
+    for (int l = 0; l < 32; ++l) v += sh[ty][l][tx];
+    sh[ty][0][tx] = v;
+    if (S > 1) g_fin_scratch[(((size_t)blockIdx.x * S + s) * NACC + ty) * 32 + tx] = v;
+  }
+  if (S > 1) {
+    __threadfence();
+    __syncthreads();
+    if (tx == 0 && ty == 0) is_last = (atomicAdd(&g_fin_counters[blockIdx.x], 1u) == (unsigned)(S - 1));
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    if (ty < NACC) {
+      double v = 0.0;
+      for (int q = 0; q < S; ++q)
+        v += *((volatile double*)&g_fin_scratch[(((size_t)blockIdx.x * S + q) * NACC + ty) * 32 + tx]);
+      sh[ty][0][tx] = v;
+    }
+    if (tx == 0 && ty == 0) g_fin_counters[blockIdx.x] = 0;
+  }
+  __syncthreads();
+  if (ty == 0 && c < ncols) {
+    double v[NACC];
+#pragma unroll
+    for (int k = 0; k < NACC; ++k) v[k] = sh[k][0][tx];
+    epi(c, v);
+  }
 }
 
 // Block-level per-channel reduction.  Thread t owns channel vector t % cv and pixel lane

@@ -145,65 +145,89 @@ __global__ void __launch_bounds__(kEwThreads) se_bwd_reduce_kernel(const EwArgs 
                        });
 }
 
-// one block; samples are processed in order so dW1/dW2 accumulate deterministically.
-__global__ void __launch_bounds__(kEwThreads) se_mlp_bwd_kernel(const EwArgs a) {
+// Backward of the shared MLP, two launches.  (1) grid = N samples: gate gradient ds[C], hidden
+// gradients dha/dhm[Ch] and the pooled-input gradients dpool; ds / dh are parked behind the
+// [N][rows][C] block partials inside `part` (its forward shape was [N][rows][3][C]).
+// (2) grid over the weight elements: dW2[c][h] and dW1[h][c] summed over samples in sample
+// order (deterministic).
+__global__ void __launch_bounds__(kEwThreads) se_mlp_bwd_sample_kernel(const EwArgs a) {
   extern __shared__ float sm[];  // ds[C], dha[Ch], dhm[Ch]
-  const float* part = (const float*)a.p[0];
+  float* part = (float*)a.p[0];
   const float* w1 = (const float*)a.p[1];
   const float* w2 = (const float*)a.p[2];
   const float* saved = (const float*)a.p[3];
   const float* hidden = (const float*)a.p[4];
-  float* dW1 = (float*)a.p[5];
-  float* dW2 = (float*)a.p[6];
   float* dpool = (float*)a.p[7];
   const int N = (int)a.i[0], C = (int)a.i[2], Ch = (int)a.i[3], rows = (int)a.i[4];
-  const bool accumulate = a.i[5] != 0;
+  const int n = blockIdx.x;
   float* ds = sm;
   float* dha = sm + C;
   float* dhm = dha + Ch;
+  float* ds_out = part + (size_t)N * rows * C + (size_t)n * C;
+  float* dh_out = part + (size_t)2 * N * rows * C + (size_t)n * 2 * Ch;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
-  for (int n = 0; n < N; ++n) {
-    const float* sv = saved + (size_t)n * 4 * C;
-    const float* hid = hidden + (size_t)n * 2 * Ch;
-    const bool add = accumulate || n > 0;
-    __syncthreads();
-    for (int c = threadIdx.x; c < C; c += blockDim.x) {
-      float s = 0.0f;
-      for (int r = 0; r < rows; ++r) s += part[((size_t)n * rows + r) * C + c];
-      const float g = sv[2 * C + c];
-      ds[c] = s * g * (1.0f - g);
+  const float* sv = saved + (size_t)n * 4 * C;
+  const float* hid = hidden + (size_t)n * 2 * Ch;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float s = 0.0f;
+    for (int r = 0; r < rows; ++r) s += part[((size_t)n * rows + r) * C + c];
+    const float g = sv[2 * C + c];
+    const float v = s * g * (1.0f - g);
+    ds[c] = v;
+    ds_out[c] = v;
+  }
+  __syncthreads();
+  for (int h = warp; h < Ch; h += nw) {
+    float s = 0.0f;
+    for (int c = lane; c < C; c += 32) s = fmaf(ds[c], w2[(size_t)c * Ch + h], s);
+    s = warp_sum(s);
+    if (lane == 0) {
+      dha[h] = hid[h] > 0.0f ? s : 0.0f;
+      dhm[h] = hid[Ch + h] > 0.0f ? s : 0.0f;
+      dh_out[h] = dha[h];
+      dh_out[Ch + h] = dhm[h];
     }
-    __syncthreads();
-    for (int h = warp; h < Ch; h += nw) {
-      float s = 0.0f;
-      for (int c = lane; c < C; c += 32) s = fmaf(ds[c], w2[(size_t)c * Ch + h], s);
-      s = warp_sum(s);
-      if (lane == 0) {
-        dha[h] = hid[h] > 0.0f ? s : 0.0f;
-        dhm[h] = hid[Ch + h] > 0.0f ? s : 0.0f;
-      }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float da = 0.0f, dm = 0.0f;
+    for (int h = 0; h < Ch; ++h) {
+      const float w = w1[(size_t)h * C + c];
+      da = fmaf(dha[h], w, da);
+      dm = fmaf(dhm[h], w, dm);
     }
-    for (int e = threadIdx.x; e < C * Ch; e += blockDim.x) {  // dW2[c][h]
-      const int c = e / Ch, h = e % Ch;
-      const float v = ds[c] * (hid[h] + hid[Ch + h]);
-      dW2[e] = add ? dW2[e] + v : v;
+    dpool[((size_t)n * 2) * C + c] = da;
+    dpool[((size_t)n * 2 + 1) * C + c] = dm;
+  }
+}
+
+__global__ void __launch_bounds__(kEwThreads) se_mlp_bwd_weight_kernel(const EwArgs a) {
+  const float* part = (const float*)a.p[0];
+  const float* saved = (const float*)a.p[3];
+  const float* hidden = (const float*)a.p[4];
+  float* dW1 = (float*)a.p[5];
+  float* dW2 = (float*)a.p[6];
+  const int N = (int)a.i[0], C = (int)a.i[2], Ch = (int)a.i[3], rows = (int)a.i[4];
+  const bool accumulate = a.i[5] != 0;
+  const float* ds = part + (size_t)N * rows * C;
+  const float* dh = part + (size_t)2 * N * rows * C;
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e < C * Ch) {  // dW2[c][h] = sum_n ds[n][c] * (hid_a[n][h] + hid_m[n][h])
+    const int c = e / Ch, h = e % Ch;
+    float s = 0.0f;
+    for (int n = 0; n < N; ++n)
+      s = fmaf(ds[(size_t)n * C + c], hidden[(size_t)n * 2 * Ch + h] + hidden[(size_t)n * 2 * Ch + Ch + h], s);
+    dW2[e] = accumulate ? dW2[e] + s : s;
+  } else if (e < 2 * C * Ch) {  // dW1[h][c] = sum_n dha[n][h]*avg[n][c] + dhm[n][h]*max[n][c]
+    const int e1 = e - C * Ch;
+    const int h = e1 / C, c = e1 % C;
+    float s = 0.0f;
+    for (int n = 0; n < N; ++n) {
+      const float* sv = saved + (size_t)n * 4 * C;
+      s = fmaf(dh[(size_t)n * 2 * Ch + h], sv[c], s);
+      s = fmaf(dh[(size_t)n * 2 * Ch + Ch + h], sv[C + c], s);
     }
-    __syncthreads();
-    for (int e = threadIdx.x; e < C * Ch; e += blockDim.x) {  // dW1[h][c]
-      const int h = e / C, c = e % C;
-      const float v = dha[h] * sv[c] + dhm[h] * sv[C + c];
-      dW1[e] = add ? dW1[e] + v : v;
-    }
-    for (int c = threadIdx.x; c < C; c += blockDim.x) {
-      float da = 0.0f, dm = 0.0f;
-      for (int h = 0; h < Ch; ++h) {
-        const float w = w1[(size_t)h * C + c];
-        da = fmaf(dha[h], w, da);
-        dm = fmaf(dhm[h], w, dm);
-      }
-      dpool[((size_t)n * 2) * C + c] = da;
-      dpool[((size_t)n * 2 + 1) * C + c] = dm;
-    }
+    dW1[e1] = accumulate ? dW1[e1] + s : s;
   }
 }
 
@@ -245,7 +269,14 @@ EW_LAUNCHER(launch_se_pool, se_pool_kernel)
 EW_LAUNCHER(launch_se_mlp, se_mlp_kernel)
 EW_LAUNCHER(launch_se_scale, se_scale_kernel)
 EW_LAUNCHER(launch_se_bwd_reduce, se_bwd_reduce_kernel)
-EW_LAUNCHER(launch_se_mlp_bwd, se_mlp_bwd_kernel)
+int launch_se_mlp_bwd(const EwArgs& a, dim3 grid, dim3 block, size_t smem, cudaStream_t st) {
+  se_mlp_bwd_sample_kernel<<<grid, block, smem, st>>>(a);
+  B2_CHECK_CUDA(cudaGetLastError());
+  const int elems = 2 * (int)a.i[2] * (int)a.i[3];
+  se_mlp_bwd_weight_kernel<<<(elems + kEwThreads - 1) / kEwThreads, kEwThreads, 0, st>>>(a);
+  B2_CHECK_CUDA(cudaGetLastError());
+  return B2SEG_OK;
+}
 EW_LAUNCHER(launch_se_bwd_apply, se_bwd_apply_kernel)
 
 }  // namespace
@@ -293,7 +324,8 @@ int ew_plan_se(const b2seg_ew_desc* d, EwPlan* pl) {
       B2_REQUIRE(p[0] && p[1] && p[2] && p[3] && p[4] && p[5] && p[6] && p[7] && i[3] >= 1 && i[4] == rows,
                  "se_mlp_bwd: bad arguments");
       pl->fn = launch_se_mlp_bwd;
-      pl->grid = dim3(1);
+      pl->grid = dim3(N);
+      pl->launches = 2;
       pl->smem = (size_t)(C + 2 * i[3]) * sizeof(float);
       return B2SEG_OK;
     case B2SEG_EW_SE_BWD_APPLY:

@@ -52,7 +52,8 @@ struct TGSmem {
   static constexpr int B_BYTES = BLOCK_N * 128;
   static constexpr int STAGE = A_BYTES + B_BYTES;
   static constexpr int BAR_OFF = NSTAGES * STAGE;
-  static constexpr int TOTAL = BAR_OFF + (2 * NSTAGES + 1) * 8 + 16 + 1024 /*align slack*/;
+  static constexpr int STAT_OFF = BAR_OFF + (2 * NSTAGES + 1) * 8 + 16;  // [4 warps][2][BLOCK_N] f32
+  static constexpr int TOTAL = STAT_OFF + 4 * 2 * BLOCK_N * 4 + 1024 /*align slack*/;
 };
 
 template <int BLOCK_N, int NSTAGES>
@@ -141,9 +142,7 @@ __global__ void __launch_bounds__(kThreadsTG)
     const long long row_off =
         sub.out_off + (long long)pn * p.osn + (long long)phh * p.osh + (long long)pw * p.osw;
     const int cq_mask = (1 << p.cq_shift) - 1;
-    float* stat_row = nullptr;
-    if (p.stats)
-      stat_row = p.stats + (size_t)(((size_t)blockIdx.z * p.mtiles + mtile) * 4 + wq) * 2 * p.ngemm;
+    float* stat_sm = reinterpret_cast<float*>(smem + L::STAT_OFF) + wq * 2 * BLOCK_N;
 
     mbar_wait(tmem_full, 0);
     tcgen05_fence_after();
@@ -181,7 +180,7 @@ __global__ void __launch_bounds__(kThreadsTG)
           *reinterpret_cast<uint4*>(dst) = pk;
         }
       }
-      if (stat_row) {
+      if (p.stats) {
         float s1[32], s2[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
@@ -191,8 +190,18 @@ __global__ void __launch_bounds__(kThreadsTG)
         }
         const float a = warp_transpose_sum32(s1, lane);
         const float b = warp_transpose_sum32(s2, lane);
-        stat_row[colc + lane] = a;
-        stat_row[p.ngemm + colc + lane] = b;
+        stat_sm[c * 32 + lane] = a;
+        stat_sm[BLOCK_N + c * 32 + lane] = b;
+      }
+    }
+    if (p.stats) {  // fold the four warps' sums: one (sum, sumsq) row per pixel tile
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      const float* sm0 = reinterpret_cast<const float*>(smem + L::STAT_OFF);
+      float* row = p.stats + (size_t)mtile * 2 * p.ngemm;
+      for (int e = threadIdx.x - 64; e < 2 * BLOCK_N; e += 128) {
+        const float v = (sm0[e] + sm0[2 * BLOCK_N + e]) + (sm0[4 * BLOCK_N + e] + sm0[6 * BLOCK_N + e]);
+        const int k = e / BLOCK_N, cc = e % BLOCK_N;
+        row[k * p.ngemm + col0 + cc] = v;
       }
     }
     tcgen05_fence_before();
@@ -253,7 +262,7 @@ extern "C" int b2seg_tapgemm_stat_rows(int on, int oh, int ow) {
   int wt, ht, nt;
   b2_pick_pixel_tile(on, oh, ow, &wt, &ht, &nt);
   const int tiles = ((ow + wt - 1) / wt) * ((oh + ht - 1) / ht) * ((on + nt - 1) / nt);
-  return tiles * 4;
+  return tiles;
 }
 
 extern "C" int b2seg_tapgemm_create(const b2seg_tapgemm_desc* d, b2seg_op** out) {

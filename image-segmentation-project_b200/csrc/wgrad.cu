@@ -164,26 +164,38 @@ __global__ void __launch_bounds__(kThreadsWG, 1)
 }
 
 // Sum split-K partials in fixed order and scatter into the gradient layout.
-// thread -> (chunk, row i in chunk, column j); j fastest for coalesced partial reads.
+// grid (cchunks, ceil(b_channels/16), 64/kRedI); a block owns kRedI channels of the tap side x 16
+// columns x all taps.  Partials are read along the column index (coalesced), transposed through
+// shared memory and written along (channel, tap) -- contiguous in OIHW / IOHW parameter layouts.
+constexpr int kRedI = 8, kRedJ = 16;
 __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const __grid_constant__ WgradParams p) {
-  const long long total = (long long)p.nchunks * 64 * p.b_channels;
-  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-       idx += (long long)gridDim.x * blockDim.x) {
-    const int j = (int)(idx % p.b_channels);
-    const long long rest = idx / p.b_channels;
-    const int i = (int)(rest % 64);
-    const int chunk = (int)(rest / 64);
-    const int tap = chunk / p.cchunks;
-    const int ch = (chunk % p.cchunks) * 64 + i;
-    if (ch >= p.a_channels) continue;
-    const int pair = chunk >> 1, row = (chunk & 1) * 64 + i;
-    const float* src = p.ws + ((size_t)pair * 128 + row) * p.ncols_pad + j;
-    const size_t split_stride = (size_t)p.npairs * 128 * p.ncols_pad;
+  __shared__ float sm[kRedJ][kRedI * B2SEG_MAX_TAPS + 1];
+  const int cchunk = blockIdx.x, j0 = blockIdx.y * kRedJ, i0 = blockIdx.z * kRedI;
+  const size_t split_stride = (size_t)p.npairs * 128 * p.ncols_pad;
+  const int n1 = p.ntaps * kRedI * kRedJ;
+  for (int e = threadIdx.x; e < n1; e += blockDim.x) {
+    const int jj = e % kRedJ, i = (e / kRedJ) % kRedI, tap = e / (kRedJ * kRedI);
+    const int chunk = tap * p.cchunks + cchunk;
+    const int pair = chunk >> 1, row = (chunk & 1) * 64 + i0 + i;
+    const int j = j0 + jj;
     float acc = 0.0f;
-    for (int s = 0; s < p.nsplit; ++s) acc += src[(size_t)s * split_stride];
+    if (j < p.b_channels) {
+      const float* src = p.ws + ((size_t)pair * 128 + row) * p.ncols_pad + j;
+      for (int s = 0; s < p.nsplit; ++s) acc += src[(size_t)s * split_stride];
+    }
+    sm[jj][i * p.ntaps + tap] = acc;
+  }
+  __syncthreads();
+  const int run = kRedI * p.ntaps;
+  for (int e = threadIdx.x; e < kRedJ * run; e += blockDim.x) {
+    const int jj = e / run, r = e % run;
+    const int i = r / p.ntaps, tap = r % p.ntaps;
+    const int ch = cchunk * 64 + i0 + i, j = j0 + jj;
+    if (ch >= p.a_channels || j >= p.b_channels) continue;
     float* dst = p.grad + p.taps[tap].out_base + (long long)ch * p.row_stride +
                  (long long)j * p.col_stride;
-    *dst = p.accumulate ? *dst + acc : acc;
+    const float v = sm[jj][r];
+    *dst = p.accumulate ? *dst + v : v;
   }
 }
 
@@ -191,7 +203,7 @@ struct WgradOp : b2seg_op {
   WgradParams p;
   dim3 grid;
   int block_n;
-  int reduce_blocks;
+  dim3 reduce_grid;
   const char* name() const override { return "wgrad"; }
   int launches() const override { return 2; }
   int run(cudaStream_t st) override {
@@ -200,7 +212,7 @@ struct WgradOp : b2seg_op {
     else
       wgrad_kernel<64, 4><<<grid, kThreadsWG, WGSmem<64, 4>::TOTAL, st>>>(p);
     B2_CHECK_CUDA(cudaGetLastError());
-    wgrad_reduce_kernel<<<reduce_blocks, 256, 0, st>>>(p);
+    wgrad_reduce_kernel<<<reduce_grid, 256, 0, st>>>(p);
     B2_CHECK_CUDA(cudaGetLastError());
     return B2SEG_OK;
   }
@@ -308,10 +320,7 @@ extern "C" int b2seg_wgrad_create(const b2seg_wgrad_desc* d, b2seg_op** out) {
   p.accumulate = d->accumulate;
   op->block_n = g.block_n;
   op->grid = dim3(g.npairs, g.ntiles, g.nsplit);
-  const long long total = (long long)g.nchunks * 64 * b_ch;
-  long long rb = (total + 255) / 256;
-  if (rb > 148 * 16) rb = 148 * 16;
-  op->reduce_blocks = (int)rb;
+  op->reduce_grid = dim3(g.cchunks, (b_ch + kRedJ - 1) / kRedJ, 64 / kRedI);
   int rc = g.block_n == 128 ? set_wg_attr<128, 3>() : set_wg_attr<64, 4>();
   if (rc != B2SEG_OK) { delete op; return rc; }
   *out = op;

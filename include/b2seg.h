@@ -315,7 +315,7 @@ enum {
    * p0 x bf16  p1 partial f32 [rows][C]   i0 P i1 C i2 ld */
   B2SEG_EW_COLSUM = 13,
   /* every fp32 parameter -> its bf16 GEMM operand layouts, one launch.
-   * p0 device table of b2seg_pack_job  i0 number of jobs  i1 total elements */
+   * p0 device table of b2seg_pack_job  i0 number of jobs  i1 total 32x32xT tiles (T <= 9) */
   B2SEG_EW_PACK = 14,
   /* AttentionGate tail (advanced_models.py:34-40): psi = sigmoid(BN1(psi_pre)); out[p,c] = x[p,c]*psi[p].
    * p0 psi_pre f32 [P]  p1 bnp (1 channel)  p2 x bf16  p3 out bf16  p4 psi f32 [P] (saved)
@@ -339,7 +339,8 @@ enum {
   /* backward 1: part[n][row][c] = sum_p dout*x.  p0 dout bf16  p1 x bf16  p2 part f32 [N][rows][C]
    * i0 N i1 HW i2 C i3 ld_dout i4 ld_x */
   B2SEG_EW_SE_BWD_REDUCE = 20,
-  /* backward 2 (tiny, one block): MLP backward -> dW1, dW2, dpool = (davg, dmax).
+  /* backward 2 (two launches: per-sample, then per weight element summed in sample order): MLP
+   * backward -> dW1, dW2, dpool = (davg, dmax).  Uses the tail of `part` ([N][rows][3][C]) as scratch.
    * p0 part  p1 w1  p2 w2  p3 saved  p4 hidden  p5 dW1 f32  p6 dW2 f32  p7 dpool f32 [N][2][C]
    * i0 N i1 HW i2 C i3 Ch i4 rows i5 accumulate into dW1/dW2 */
   B2SEG_EW_SE_MLP_BWD = 21,
@@ -350,7 +351,8 @@ enum {
   B2SEG_EW_FILL = 23,
 };
 
-/* out[t][a][b] = bf16(in[a*sa + b*sb + t*st]); `start` = elements of all earlier jobs. */
+/* out[t][a][b] = bf16(in[a*sa + b*sb + t*st]); `start` = number of 32x32xT tiles
+ * (ceil(A/32)*ceil(B/32) per job) of all earlier jobs. */
 typedef struct b2seg_pack_job {
   const float* in;
   void* out;
