@@ -61,6 +61,7 @@ class Op:
         self.keep = keep
         self.kind = kind
         self.flops = float(flops)  # algorithmic 2*M*N*K of a tensor-core op (bench roofline)
+        self.desc = ""
 
     def run(self):
         L.check(L.lib().b2seg_op_run(self.handle, L.stream_ptr()))
@@ -169,7 +170,9 @@ def _create_tapgemm(d, keep, kind):
     h = C.c_void_p()
     L.check(L.lib().b2seg_tapgemm_create(C.byref(d), C.byref(h)))
     taps = sum(d.sub[s].ntaps for s in range(d.nsub))
-    return Op(h, keep, kind, flops=2.0 * d.on * d.oh * d.ow * d.ngemm * d.cin * taps)
+    op = Op(h, keep, kind, flops=2.0 * d.on * d.oh * d.ow * d.ngemm * d.cin * taps)
+    op.desc = f"M={d.on * d.oh * d.ow} ({d.on}x{d.oh}x{d.ow}) N={d.ngemm} K={taps}x{d.cin} nsub={d.nsub}"
+    return op
 
 
 def _srcs(d, views):
@@ -279,7 +282,9 @@ def wgrad_workspace_bytes(a_ch, b_ch, ntaps, n, h, w) -> int:
 def _create_wgrad(d, keep, kind):
     h = C.c_void_p()
     L.check(L.lib().b2seg_wgrad_create(C.byref(d), C.byref(h)))
-    return Op(h, keep, kind, flops=2.0 * d.pn * d.ph * d.pw * d.a_src[0].c * d.b_src.c * d.ntaps)
+    op = Op(h, keep, kind, flops=2.0 * d.pn * d.ph * d.pw * d.a_src[0].c * d.b_src.c * d.ntaps)
+    op.desc = f"pix={d.pn * d.ph * d.pw} ({d.pn}x{d.ph}x{d.pw}) A={d.ntaps}x{d.a_src[0].c} B={d.b_src.c}"
+    return op
 
 
 def conv_wgrad(x: View, dy: View, k: int, stride: int, grad: torch.Tensor, ws: torch.Tensor,
