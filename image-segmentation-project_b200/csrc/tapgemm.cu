@@ -42,6 +42,7 @@ struct alignas(64) TapGemmParams {
   const float* bias;
   float* stats;
   int accumulate;
+  int nitems;  // mtiles * (ngemm / BLOCK_N) * nsub
 };
 
 constexpr int kThreadsTG = 192;
@@ -52,10 +53,29 @@ struct TGSmem {
   static constexpr int B_BYTES = BLOCK_N * 128;
   static constexpr int STAGE = A_BYTES + B_BYTES;
   static constexpr int BAR_OFF = NSTAGES * STAGE;
-  static constexpr int STAT_OFF = BAR_OFF + (2 * NSTAGES + 1) * 8 + 16;  // [4 warps][2][BLOCK_N] f32
+  // full[NS], empty[NS], tmem_full[2], tmem_empty[2], tmem slot
+  static constexpr int STAT_OFF = BAR_OFF + (2 * NSTAGES + 4) * 8 + 16;  // [4 warps][2][BLOCK_N] f32
   static constexpr int TOTAL = STAT_OFF + 4 * 2 * BLOCK_N * 4 + 1024 /*align slack*/;
 };
 
+// Work item `idx` -> (column tile, pixel tile, sub-problem); column tiles of one pixel tile are
+// adjacent in the order so CTAs running side by side share the A bricks through L2.
+struct TGItem {
+  int ntile, mtile, sub;
+};
+__device__ __forceinline__ TGItem tg_item(int idx, int ntiles, int mtiles) {
+  TGItem it;
+  it.ntile = idx % ntiles;
+  const int r = idx / ntiles;
+  it.mtile = r % mtiles;
+  it.sub = r / mtiles;
+  return it;
+}
+
+// Persistent kernel: every CTA walks the work items blockIdx.x, blockIdx.x + gridDim.x, ...
+// The shared-memory ring never drains between items, and the fp32 accumulator is double
+// buffered in TMEM (2 x BLOCK_N columns), so the TMA producer and the MMA issuer run ahead
+// into the next item while the four epilogue warps drain the previous one.
 template <int BLOCK_N, int NSTAGES>
 __global__ void __launch_bounds__(kThreadsTG)
     tapgemm_kernel(const __grid_constant__ TapGemmParams p) {
@@ -65,29 +85,28 @@ __global__ void __launch_bounds__(kThreadsTG)
                                              ~(uintptr_t)1023);
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::BAR_OFF);
   uint64_t* empty_bar = full_bar + NSTAGES;
-  uint64_t* tmem_full = empty_bar + NSTAGES;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  uint64_t* tmem_full = empty_bar + NSTAGES;   // [2]
+  uint64_t* tmem_empty = tmem_full + 2;        // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const TapSub& sub = p.sub[blockIdx.z];
-  const int mtile = blockIdx.x;
-  const int tw = mtile % p.tilesW, th = (mtile / p.tilesW) % p.tilesH,
-            tn = mtile / (p.tilesW * p.tilesH);
-  const int w0 = tw * p.wt, h0 = th * p.ht, n0 = tn * p.nt;
-  const int col0 = blockIdx.y * BLOCK_N;
-  const int total_iters = sub.ntaps * p.kchunks;
+  const int ntiles = p.ngemm / BLOCK_N;
+  const int nitems = p.nitems;
 
   if (warp == 0 && lane == 0) {
     for (int i = 0; i < NSTAGES; ++i) {
       mbar_init(&full_bar[i], 1);
       mbar_init(&empty_bar[i], 1);
     }
-    mbar_init(tmem_full, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tmem_full[i], 1);
+      mbar_init(&tmem_empty[i], 4);  // one arrive per epilogue warp
+    }
     fence_barrier_init();
     tma_prefetch_desc(&p.tmB);
-    tma_prefetch_desc(&p.tmA[sub.src[0]]);
+    tma_prefetch_desc(&p.tmA[0]);
   }
-  if (warp == 1) tmem_alloc<BLOCK_N>(tmem_slot);
+  if (warp == 1) tmem_alloc<2 * BLOCK_N>(tmem_slot);
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
@@ -96,18 +115,26 @@ __global__ void __launch_bounds__(kThreadsTG)
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
-      int it = 0;
-      for (int t = 0; t < sub.ntaps; ++t) {
-        const CUtensorMap* tmA = &p.tmA[sub.src[t]];
-        const int cw = w0 + sub.dw[t], ch = h0 + sub.dh[t], wtap = sub.wt[t];
-        for (int kc = 0; kc < p.kchunks; ++kc, ++it) {
-          const int s = it % NSTAGES;
-          const uint32_t ph = (uint32_t)(it / NSTAGES) & 1u;
-          mbar_wait(&empty_bar[s], ph ^ 1u);
-          mbar_expect_tx(&full_bar[s], L::STAGE);
-          uint8_t* sa = smem + s * L::STAGE;
-          tma_load_4d(sa, tmA, &full_bar[s], kc * 64, cw, ch, n0);
-          tma_load_3d(sa + A_BYTES, &p.tmB, &full_bar[s], kc * 64, col0, wtap);
+      uint32_t it = 0;
+      for (int idx = blockIdx.x; idx < nitems; idx += gridDim.x) {
+        const TGItem w = tg_item(idx, ntiles, p.mtiles);
+        const TapSub& sub = p.sub[w.sub];
+        const int tw = w.mtile % p.tilesW, th = (w.mtile / p.tilesW) % p.tilesH,
+                  tn = w.mtile / (p.tilesW * p.tilesH);
+        const int w0 = tw * p.wt, h0 = th * p.ht, n0 = tn * p.nt;
+        const int col0 = w.ntile * BLOCK_N;
+        for (int t = 0; t < sub.ntaps; ++t) {
+          const CUtensorMap* tmA = &p.tmA[sub.src[t]];
+          const int cw = w0 + sub.dw[t], ch = h0 + sub.dh[t], wtap = sub.wt[t];
+          for (int kc = 0; kc < p.kchunks; ++kc, ++it) {
+            const uint32_t s = it % NSTAGES;
+            const uint32_t ph = (it / NSTAGES) & 1u;
+            mbar_wait(&empty_bar[s], ph ^ 1u);
+            mbar_expect_tx(&full_bar[s], L::STAGE);
+            uint8_t* sa = smem + s * L::STAGE;
+            tma_load_4d(sa, tmA, &full_bar[s], kc * 64, cw, ch, n0);
+            tma_load_3d(sa + A_BYTES, &p.tmB, &full_bar[s], kc * 64, col0, wtap);
+          }
         }
       }
     }
@@ -115,21 +142,30 @@ __global__ void __launch_bounds__(kThreadsTG)
     // ===================== MMA issuer =====================
     if (lane == 0) {
       constexpr uint32_t idesc = umma_idesc_bf16(128, BLOCK_N, 0, 0);
-      for (int it = 0; it < total_iters; ++it) {
-        const int s = it % NSTAGES;
-        const uint32_t ph = (uint32_t)(it / NSTAGES) & 1u;
-        mbar_wait(&full_bar[s], ph);
+      uint32_t it = 0, tile = 0;
+      for (int idx = blockIdx.x; idx < nitems; idx += gridDim.x, ++tile) {
+        const TGItem w = tg_item(idx, ntiles, p.mtiles);
+        const int iters = p.sub[w.sub].ntaps * p.kchunks;
+        const uint32_t acc = tile & 1u, aph = (tile >> 1) & 1u;
+        mbar_wait(&tmem_empty[acc], aph ^ 1u);  // epilogue has drained this accumulator
         tcgen05_fence_after();
-        const uint32_t sa = smem_u32(smem + s * L::STAGE);
-        const uint64_t adesc = umma_smem_desc(sa, 16, 1024);
-        const uint64_t bdesc = umma_smem_desc(sa + A_BYTES, 16, 1024);
+        const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
+        for (int i = 0; i < iters; ++i, ++it) {
+          const uint32_t s = it % NSTAGES;
+          const uint32_t ph = (it / NSTAGES) & 1u;
+          mbar_wait(&full_bar[s], ph);
+          tcgen05_fence_after();
+          const uint32_t sa = smem_u32(smem + s * L::STAGE);
+          const uint64_t adesc = umma_smem_desc(sa, 16, 1024);
+          const uint64_t bdesc = umma_smem_desc(sa + A_BYTES, 16, 1024);
 #pragma unroll
-        for (int k = 0; k < 4; ++k)  // 4 x (K = 16 bf16 = 32 B) per 64-channel chunk
-          umma_bf16_ss(tmem_base, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
-                       (it | k) != 0 ? 1u : 0u);
-        tcgen05_commit(&empty_bar[s]);  // smem slot free once these MMAs retire
+          for (int k = 0; k < 4; ++k)  // 4 x (K = 16 bf16 = 32 B) per 64-channel chunk
+            umma_bf16_ss(tmem_d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
+                         (i | k) != 0 ? 1u : 0u);
+          tcgen05_commit(&empty_bar[s]);  // smem slot free once these MMAs retire
+        }
+        tcgen05_commit(&tmem_full[acc]);
       }
-      tcgen05_commit(tmem_full);
     }
   } else {
     // ===================== epilogue =====================
@@ -137,71 +173,86 @@ __global__ void __launch_bounds__(kThreadsTG)
     const int r = wq * 32 + lane;
     const int hw = p.ht * p.wt;
     const int ln = r / hw, lh = (r % hw) / p.wt, lw = r % p.wt;
-    const int pn = n0 + ln, phh = h0 + lh, pw = w0 + lw;
-    const bool row_ok = pn < p.on && phh < p.oh && pw < p.ow;
-    const long long row_off =
-        sub.out_off + (long long)pn * p.osn + (long long)phh * p.osh + (long long)pw * p.osw;
     const int cq_mask = (1 << p.cq_shift) - 1;
     float* stat_sm = reinterpret_cast<float*>(smem + L::STAT_OFF) + wq * 2 * BLOCK_N;
-
-    mbar_wait(tmem_full, 0);
-    tcgen05_fence_after();
+    uint32_t tile = 0;
+    for (int idx = blockIdx.x; idx < nitems; idx += gridDim.x, ++tile) {
+      const TGItem w = tg_item(idx, ntiles, p.mtiles);
+      const TapSub& sub = p.sub[w.sub];
+      const int tw = w.mtile % p.tilesW, th = (w.mtile / p.tilesW) % p.tilesH,
+                tn = w.mtile / (p.tilesW * p.tilesH);
+      const int pn = tn * p.nt + ln, phh = th * p.ht + lh, pw = tw * p.wt + lw;
+      const int col0 = w.ntile * BLOCK_N;
+      const bool row_ok = pn < p.on && phh < p.oh && pw < p.ow;
+      const long long row_off =
+          sub.out_off + (long long)pn * p.osn + (long long)phh * p.osh + (long long)pw * p.osw;
+      const uint32_t acc = tile & 1u, aph = (tile >> 1) & 1u;
+      mbar_wait(&tmem_full[acc], aph);
+      tcgen05_fence_after();
+      const uint32_t tmem_d = tmem_base + acc * BLOCK_N + ((uint32_t)(wq * 32) << 16);
 #pragma unroll 1
-    for (int c = 0; c < BLOCK_N / 32; ++c) {
-      float v[32];
-      tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(c * 32), v);
-      const int colc = col0 + c * 32;
-      if (p.bias) {
+      for (int c = 0; c < BLOCK_N / 32; ++c) {
+        float v[32];
+        tmem_ld_32x32b_x32(tmem_d + (uint32_t)(c * 32), v);
+        if (c == BLOCK_N / 32 - 1) {  // accumulator fully read: hand it back to the MMA issuer
+          tcgen05_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+        }
+        const int colc = col0 + c * 32;
+        if (p.bias) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + ((colc + j) & cq_mask));
-      }
-      if (row_ok) {
+          for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + ((colc + j) & cq_mask));
+        }
+        if (row_ok) {
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          const int col = colc + g * 8;
-          const int q = col >> p.cq_shift;
-          bf16* dst = p.out + row_off + (long long)(q >> 1) * p.oqh + (long long)(q & 1) * p.oqw +
-                      (col & cq_mask);
-          float o[8];
+          for (int g = 0; g < 4; ++g) {
+            const int col = colc + g * 8;
+            const int q = col >> p.cq_shift;
+            bf16* dst = p.out + row_off + (long long)(q >> 1) * p.oqh + (long long)(q & 1) * p.oqw +
+                        (col & cq_mask);
+            float o[8];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) o[j] = v[g * 8 + j];
-          if (p.accumulate) {
-            const uint4 old = *reinterpret_cast<const uint4*>(dst);
-            const float2 a0 = bf2_to_f2(old.x), a1 = bf2_to_f2(old.y), a2 = bf2_to_f2(old.z),
-                         a3 = bf2_to_f2(old.w);
-            o[0] += a0.x; o[1] += a0.y; o[2] += a1.x; o[3] += a1.y;
-            o[4] += a2.x; o[5] += a2.y; o[6] += a3.x; o[7] += a3.y;
+            for (int j = 0; j < 8; ++j) o[j] = v[g * 8 + j];
+            if (p.accumulate) {
+              const uint4 old = *reinterpret_cast<const uint4*>(dst);
+              const float2 a0 = bf2_to_f2(old.x), a1 = bf2_to_f2(old.y), a2 = bf2_to_f2(old.z),
+                           a3 = bf2_to_f2(old.w);
+              o[0] += a0.x; o[1] += a0.y; o[2] += a1.x; o[3] += a1.y;
+              o[4] += a2.x; o[5] += a2.y; o[6] += a3.x; o[7] += a3.y;
+            }
+            uint4 pk;
+            pk.x = f2_to_bf2(o[0], o[1]);
+            pk.y = f2_to_bf2(o[2], o[3]);
+            pk.z = f2_to_bf2(o[4], o[5]);
+            pk.w = f2_to_bf2(o[6], o[7]);
+            *reinterpret_cast<uint4*>(dst) = pk;
           }
-          uint4 pk;
-          pk.x = f2_to_bf2(o[0], o[1]);
-          pk.y = f2_to_bf2(o[2], o[3]);
-          pk.z = f2_to_bf2(o[4], o[5]);
-          pk.w = f2_to_bf2(o[6], o[7]);
-          *reinterpret_cast<uint4*>(dst) = pk;
         }
-      }
-      if (p.stats) {
-        float s1[32], s2[32];
+        if (p.stats) {
+          float s1[32], s2[32];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const float x = row_ok ? v[j] : 0.0f;
-          s1[j] = x;
-          s2[j] = x * x;
+          for (int j = 0; j < 32; ++j) {
+            const float x = row_ok ? v[j] : 0.0f;
+            s1[j] = x;
+            s2[j] = x * x;
+          }
+          const float a = warp_transpose_sum32(s1, lane);
+          const float b = warp_transpose_sum32(s2, lane);
+          stat_sm[c * 32 + lane] = a;
+          stat_sm[BLOCK_N + c * 32 + lane] = b;
         }
-        const float a = warp_transpose_sum32(s1, lane);
-        const float b = warp_transpose_sum32(s2, lane);
-        stat_sm[c * 32 + lane] = a;
-        stat_sm[BLOCK_N + c * 32 + lane] = b;
       }
-    }
-    if (p.stats) {  // fold the four warps' sums: one (sum, sumsq) row per pixel tile
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      const float* sm0 = reinterpret_cast<const float*>(smem + L::STAT_OFF);
-      float* row = p.stats + (size_t)mtile * 2 * p.ngemm;
-      for (int e = threadIdx.x - 64; e < 2 * BLOCK_N; e += 128) {
-        const float v = (sm0[e] + sm0[2 * BLOCK_N + e]) + (sm0[4 * BLOCK_N + e] + sm0[6 * BLOCK_N + e]);
-        const int k = e / BLOCK_N, cc = e % BLOCK_N;
-        row[k * p.ngemm + col0 + cc] = v;
+      if (p.stats) {  // fold the four warps' sums: one (sum, sumsq) row per pixel tile
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        const float* sm0 = reinterpret_cast<const float*>(smem + L::STAT_OFF);
+        float* row = p.stats + (size_t)w.mtile * 2 * p.ngemm;
+        for (int e = threadIdx.x - 64; e < 2 * BLOCK_N; e += 128) {
+          const float x = (sm0[e] + sm0[2 * BLOCK_N + e]) + (sm0[4 * BLOCK_N + e] + sm0[6 * BLOCK_N + e]);
+          const int k = e / BLOCK_N, cc = e % BLOCK_N;
+          row[k * p.ngemm + col0 + cc] = x;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");  // stat_sm is rewritten by the next item
       }
     }
     tcgen05_fence_before();
@@ -209,7 +260,7 @@ __global__ void __launch_bounds__(kThreadsTG)
   __syncthreads();
   if (warp == 1) {
     tcgen05_fence_after();
-    tmem_dealloc<BLOCK_N>(tmem_base);
+    tmem_dealloc<2 * BLOCK_N>(tmem_base);
   }
 }
 
@@ -347,7 +398,11 @@ extern "C" int b2seg_tapgemm_create(const b2seg_tapgemm_desc* d, b2seg_op** out)
   p.bias = d->bias;
   p.stats = d->stats;
   p.accumulate = d->accumulate;
-  op->grid = dim3(p.mtiles, d->ngemm / bn, d->nsub);
+  p.nitems = p.mtiles * (d->ngemm / bn) * d->nsub;
+  {  // persistent grid: two CTAs per SM (96 KB of shared memory and <= 256 TMEM columns each)
+    const int cap = 2 * b2_num_sms();
+    op->grid = dim3(p.nitems < cap ? p.nitems : cap, 1, 1);
+  }
   int rc;
   if (bn == 128) rc = set_smem_attr<128, 3>();
   else if (bn == 64) rc = set_smem_attr<64, 4>();

@@ -165,25 +165,28 @@ __global__ void __launch_bounds__(kThreadsWG, 1)
 
 // Sum split-K partials in fixed order and scatter into the gradient layout.
 // grid (cchunks, ceil(b_channels/16), 64/kRedI); a block owns kRedI channels of the tap side x 16
-// columns x all taps.  Partials are read along the column index (coalesced), transposed through
-// shared memory and written along (channel, tap) -- contiguous in OIHW / IOHW parameter layouts.
-constexpr int kRedI = 8, kRedJ = 16;
+// columns x all taps.  The splits are dealt round-robin to kRedG thread groups (partial sums in
+// split order, combined as ((g0+g1)+(g2+g3)): fixed order, bit-reproducible).  Partials are read
+// along the column index (coalesced), transposed through shared memory and written along
+// (channel, tap) -- contiguous in OIHW / IOHW parameter layouts.
+constexpr int kRedI = 4, kRedJ = 16, kRedG = 4;
 __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const __grid_constant__ WgradParams p) {
-  __shared__ float sm[kRedJ][kRedI * B2SEG_MAX_TAPS + 1];
+  __shared__ float sm[kRedG][kRedJ][kRedI * B2SEG_MAX_TAPS + 1];
   const int cchunk = blockIdx.x, j0 = blockIdx.y * kRedJ, i0 = blockIdx.z * kRedI;
   const size_t split_stride = (size_t)p.npairs * 128 * p.ncols_pad;
   const int n1 = p.ntaps * kRedI * kRedJ;
-  for (int e = threadIdx.x; e < n1; e += blockDim.x) {
-    const int jj = e % kRedJ, i = (e / kRedJ) % kRedI, tap = e / (kRedJ * kRedI);
+  for (int e = threadIdx.x; e < n1 * kRedG; e += blockDim.x) {
+    const int g = e / n1, o = e % n1;
+    const int jj = o % kRedJ, i = (o / kRedJ) % kRedI, tap = o / (kRedJ * kRedI);
     const int chunk = tap * p.cchunks + cchunk;
     const int pair = chunk >> 1, row = (chunk & 1) * 64 + i0 + i;
     const int j = j0 + jj;
     float acc = 0.0f;
     if (j < p.b_channels) {
       const float* src = p.ws + ((size_t)pair * 128 + row) * p.ncols_pad + j;
-      for (int s = 0; s < p.nsplit; ++s) acc += src[(size_t)s * split_stride];
+      for (int s = g; s < p.nsplit; s += kRedG) acc += __ldg(src + (size_t)s * split_stride);
     }
-    sm[jj][i * p.ntaps + tap] = acc;
+    sm[g][jj][i * p.ntaps + tap] = acc;
   }
   __syncthreads();
   const int run = kRedI * p.ntaps;
@@ -194,7 +197,7 @@ __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const __grid_constant
     if (ch >= p.a_channels || j >= p.b_channels) continue;
     float* dst = p.grad + p.taps[tap].out_base + (long long)ch * p.row_stride +
                  (long long)j * p.col_stride;
-    const float v = sm[jj][r];
+    const float v = (sm[0][jj][r] + sm[1][jj][r]) + (sm[2][jj][r] + sm[3][jj][r]);
     *dst = p.accumulate ? *dst + v : v;
   }
 }
@@ -236,8 +239,9 @@ WgradGeom wgrad_geom(int a_ch, int b_ch, int ntaps, int pn, int ph, int pw) {
   g.block_n = b_ch > 64 ? 128 : 64;
   g.ntiles = (b_ch + g.block_n - 1) / g.block_n;
   g.ncols_pad = g.ntiles * g.block_n;
+  // one CTA per SM (192 KB of shared memory): split K so the grid is a single full wave
   const int ctas = g.npairs * g.ntiles;
-  int ns = (2 * b2_num_sms() + ctas - 1) / ctas;
+  int ns = b2_num_sms() / ctas;
   // keep at least 4 pixel bricks per CTA so the pipeline has something to hide
   if (ns > (g.ktiles + 3) / 4) ns = (g.ktiles + 3) / 4;
   if (ns < 1) ns = 1;
