@@ -125,6 +125,24 @@ __device__ __forceinline__ float warp_transpose_sum32(float (&v)[32], int lane) 
   return v[0];
 }
 
+// Warp-uniform helpers.  The TMA-producer and MMA-issuer warps run CONVERGED (all 32 lanes walk
+// the pipeline loops and poll the mbarriers) and only the single async instruction is predicated
+// on elect.sync: descriptors and coordinates then live in uniform registers.  Guarding a whole
+// role with `if (lane == 0)` instead makes ptxas wrap every UTCHMMA / UTMALDG in an
+// ELECT + 5x R2UR.BROADCAST + BRA.U.ANY loop (~18 SASS instructions, ~190 cycles per MMA measured).
+__device__ __forceinline__ int warp_id_uniform() {
+  return __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+}
+__device__ __forceinline__ bool elect_one_sync() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+
 // ---------------------------------------------------------------------------
 // Shared-memory address, mbarrier, TMA.
 // ---------------------------------------------------------------------------

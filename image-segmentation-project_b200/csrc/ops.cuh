@@ -24,8 +24,11 @@ int b2_view_tmap(CUtensorMap* out, const b2seg_tensor4* v, int wt, int ht, int n
 // pixel-tile shape (wt*ht*nt == 128) for an (n,h,w) iteration grid
 static inline void b2_pick_pixel_tile(int n, int h, int w, int* wt, int* ht, int* nt) {
   auto p2 = [](int x) { int p = 1; while (p < x) p <<= 1; return p; };
-  int a = p2(w); if (a > 16) a = 16;
+  int a = p2(w); if (a > 8) a = 8;  // 8-wide bricks: one brick row = one 8-row UMMA group (conv3x3.cu)
   int b = p2(h); if (b > 128 / a) b = 128 / a;
   *wt = a; *ht = b; *nt = 128 / (a * b);
   (void)n;
 }
+
+// conv3x3.cu: halo-reuse kernel for 3x3 stride-1 tap tables; *out stays NULL when not applicable.
+int b2_halo3x3_try_create(const b2seg_tapgemm_desc* d, b2seg_op** out);

@@ -16,6 +16,7 @@
 // Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM alloc + MMA
 // issuer, warps 2..5 = epilogue (TMEM lane quadrant = warp_id % 4).
 #include <new>
+#include <stdlib.h>
 #include <string.h>
 
 #include "ops.cuh"
@@ -89,7 +90,7 @@ __global__ void __launch_bounds__(kThreadsTG)
   uint64_t* tmem_empty = tmem_full + 2;        // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = warp_id_uniform(), lane = threadIdx.x & 31;
   const int ntiles = p.ngemm / BLOCK_N;
   const int nitems = p.nitems;
 
@@ -113,8 +114,8 @@ __global__ void __launch_bounds__(kThreadsTG)
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
+    // ===================== TMA producer (converged warp, elected issue) =====================
+    {
       uint32_t it = 0;
       for (int idx = blockIdx.x; idx < nitems; idx += gridDim.x) {
         const TGItem w = tg_item(idx, ntiles, p.mtiles);
@@ -130,17 +131,20 @@ __global__ void __launch_bounds__(kThreadsTG)
             const uint32_t s = it % NSTAGES;
             const uint32_t ph = (it / NSTAGES) & 1u;
             mbar_wait(&empty_bar[s], ph ^ 1u);
-            mbar_expect_tx(&full_bar[s], L::STAGE);
-            uint8_t* sa = smem + s * L::STAGE;
-            tma_load_4d(sa, tmA, &full_bar[s], kc * 64, cw, ch, n0);
-            tma_load_3d(sa + A_BYTES, &p.tmB, &full_bar[s], kc * 64, col0, wtap);
+            if (elect_one_sync()) {
+              mbar_expect_tx(&full_bar[s], L::STAGE);
+              uint8_t* sa = smem + s * L::STAGE;
+              tma_load_4d(sa, tmA, &full_bar[s], kc * 64, cw, ch, n0);
+              tma_load_3d(sa + A_BYTES, &p.tmB, &full_bar[s], kc * 64, col0, wtap);
+            }
+            __syncwarp();
           }
         }
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // ===================== MMA issuer (converged warp, elected issue) =====================
+    {
       constexpr uint32_t idesc = umma_idesc_bf16(128, BLOCK_N, 0, 0);
       uint32_t it = 0, tile = 0;
       for (int idx = blockIdx.x; idx < nitems; idx += gridDim.x, ++tile) {
@@ -158,13 +162,16 @@ __global__ void __launch_bounds__(kThreadsTG)
           const uint32_t sa = smem_u32(smem + s * L::STAGE);
           const uint64_t adesc = umma_smem_desc(sa, 16, 1024);
           const uint64_t bdesc = umma_smem_desc(sa + A_BYTES, 16, 1024);
+          if (elect_one_sync()) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k)  // 4 x (K = 16 bf16 = 32 B) per 64-channel chunk
-            umma_bf16_ss(tmem_d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
-                         (i | k) != 0 ? 1u : 0u);
-          tcgen05_commit(&empty_bar[s]);  // smem slot free once these MMAs retire
+            for (int k = 0; k < 4; ++k)  // 4 x (K = 16 bf16 = 32 B) per 64-channel chunk
+              umma_bf16_ss(tmem_d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
+                           (i | k) != 0 ? 1u : 0u);
+            tcgen05_commit(&empty_bar[s]);  // smem slot free once these MMAs retire
+            if (i == iters - 1) tcgen05_commit(&tmem_full[acc]);
+          }
+          __syncwarp();
         }
-        tcgen05_commit(&tmem_full[acc]);
       }
     }
   } else {
@@ -331,6 +338,12 @@ extern "C" int b2seg_tapgemm_create(const b2seg_tapgemm_desc* d, b2seg_op** out)
   if (d->cq > 0) {
     cq_shift = ilog2_exact(d->cq);
     B2_REQUIRE(cq_shift >= 3, "tapgemm_create: cq %d must be a power of two >= 8", d->cq);
+  }
+  if (!getenv("B2SEG_NO_HALO")) {  // 3x3 stride-1: halo-reuse kernel (conv3x3.cu)
+    b2seg_op* h = nullptr;
+    int hrc = b2_halo3x3_try_create(d, &h);
+    if (hrc != B2SEG_OK) return hrc;
+    if (h) { *out = h; return B2SEG_OK; }
   }
   auto* op = new (std::nothrow) TapGemmOp();
   B2_REQUIRE(op, "tapgemm_create: out of host memory");

@@ -60,7 +60,7 @@ __global__ void __launch_bounds__(kThreadsWG, 1)
   uint64_t* tmem_full = empty_bar + NSTAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = warp_id_uniform(), lane = threadIdx.x & 31;
   const int pair = blockIdx.x, ntile = blockIdx.y, split = blockIdx.z;
   const int my_ktiles = (p.ktiles - split + p.nsplit - 1) / p.nsplit;  // split, split+nsplit, ...
 
@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(kThreadsWG, 1)
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
+    {  // converged producer warp, elected issue
       // the two 64-channel chunks forming this CTA's M = 128
       int ch[2] = {2 * pair, min(2 * pair + 1, p.nchunks - 1)};
       const CUtensorMap* tm[2];
@@ -101,18 +101,21 @@ __global__ void __launch_bounds__(kThreadsWG, 1)
         const int s = it % NSTAGES;
         const uint32_t ph = (uint32_t)(it / NSTAGES) & 1u;
         mbar_wait(&empty_bar[s], ph ^ 1u);
-        mbar_expect_tx(&full_bar[s], L::STAGE);
-        uint8_t* st = smem + s * L::STAGE;
-        tma_load_4d(st, tm[0], &full_bar[s], c0[0], w0 + dw[0], h0 + dh[0], n0);
-        tma_load_4d(st + CHUNK_BYTES, tm[1], &full_bar[s], c0[1], w0 + dw[1], h0 + dh[1], n0);
+        if (elect_one_sync()) {
+          mbar_expect_tx(&full_bar[s], L::STAGE);
+          uint8_t* st = smem + s * L::STAGE;
+          tma_load_4d(st, tm[0], &full_bar[s], c0[0], w0 + dw[0], h0 + dh[0], n0);
+          tma_load_4d(st + CHUNK_BYTES, tm[1], &full_bar[s], c0[1], w0 + dw[1], h0 + dh[1], n0);
 #pragma unroll
-        for (int b = 0; b < L::NB; ++b)
-          tma_load_4d(st + (2 + b) * CHUNK_BYTES, &p.tmB, &full_bar[s],
-                      ntile * BLOCK_N + b * 64, w0, h0, n0);
+          for (int b = 0; b < L::NB; ++b)
+            tma_load_4d(st + (2 + b) * CHUNK_BYTES, &p.tmB, &full_bar[s],
+                        ntile * BLOCK_N + b * 64, w0, h0, n0);
+        }
+        __syncwarp();
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {  // converged MMA warp, elected issue
       constexpr uint32_t idesc = umma_idesc_bf16(128, BLOCK_N, 1, 1);
       for (int it = 0; it < my_ktiles; ++it) {
         const int s = it % NSTAGES;
@@ -121,15 +124,18 @@ __global__ void __launch_bounds__(kThreadsWG, 1)
         tcgen05_fence_after();
         const uint32_t sa = smem_u32(smem + s * L::STAGE);
         const uint32_t sb = sa + 2 * CHUNK_BYTES;
+        if (elect_one_sync()) {
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {  // 16 pixels (rows of 128 B) per MMA
-          const uint64_t adesc = umma_smem_desc(sa + k * 2048, CHUNK_BYTES, 1024);
-          const uint64_t bdesc = umma_smem_desc(sb + k * 2048, CHUNK_BYTES, 1024);
-          umma_bf16_ss(tmem_base, adesc, bdesc, idesc, (it | k) != 0 ? 1u : 0u);
+          for (int k = 0; k < 8; ++k) {  // 16 pixels (rows of 128 B) per MMA
+            const uint64_t adesc = umma_smem_desc(sa + k * 2048, CHUNK_BYTES, 1024);
+            const uint64_t bdesc = umma_smem_desc(sb + k * 2048, CHUNK_BYTES, 1024);
+            umma_bf16_ss(tmem_base, adesc, bdesc, idesc, (it | k) != 0 ? 1u : 0u);
+          }
+          tcgen05_commit(&empty_bar[s]);
+          if (it == my_ktiles - 1) tcgen05_commit(tmem_full);
         }
-        tcgen05_commit(&empty_bar[s]);
+        __syncwarp();
       }
-      tcgen05_commit(tmem_full);
     }
   } else {
     const int wq = warp & 3;
