@@ -41,11 +41,11 @@ struct alignas(64) HaloParams {
   const float* bias;
   float* stats;
   int accumulate;
-  int resident, a_stages, b_slots;
+  int resident, a_stages, b_slots, stat_rows;
   int a_stage_bytes, b_off, bar_off, stat_off;
 };
 
-template <int BLOCK_N>
+template <int BLOCK_N, bool STATS>
 __global__ void __launch_bounds__(kThreadsH, 1)
     halo3x3_kernel(const __grid_constant__ HaloParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -93,19 +93,20 @@ __global__ void __launch_bounds__(kThreadsH, 1)
   if (warp == 0) {
     // ===================== TMA producer (converged warp, elected issue) =====================
     {
-      uint32_t ait = 0, bit = 0;
+      uint32_t s = 0, ph = 1, bs = 0, bph = 1;  // ring slots and the parity a free slot shows
       bool first = true;
+      const uint32_t halo_bytes = (uint32_t)(pitch * (p.ht + 2) * 128);
       for (int mt = mt0; mt < p.mtiles; mt += mstep, first = false) {
         const int tw = mt % p.tilesW, th = (mt / p.tilesW) % p.tilesH, n0 = mt / (p.tilesW * p.tilesH);
         const int w0 = tw * p.wt - 1, h0 = th * p.ht - 1;
-        for (int kc = 0; kc < p.kchunks; ++kc, ++ait) {
-          const uint32_t s = ait % p.a_stages, ph = (ait / p.a_stages) & 1u;
-          mbar_wait(&a_empty[s], ph ^ 1u);
+        for (int kc = 0; kc < p.kchunks; ++kc) {
+          mbar_wait(&a_empty[s], ph);
           if (elect_one_sync()) {
-            mbar_expect_tx(&a_full[s], (uint32_t)(pitch * (p.ht + 2) * 128));
+            mbar_expect_tx(&a_full[s], halo_bytes);
             tma_load_4d(smem + s * p.a_stage_bytes, &p.tmA, &a_full[s], kc * 64, w0, h0, n0);
           }
           __syncwarp();
+          if (++s == (uint32_t)p.a_stages) { s = 0; ph ^= 1u; }
           if (p.resident) {
             if (first) {
               for (int t = 0; t < 9; ++t) {
@@ -119,14 +120,14 @@ __global__ void __launch_bounds__(kThreadsH, 1)
               }
             }
           } else {
-            for (int t = 0; t < 9; ++t, ++bit) {
-              const uint32_t bs = bit % p.b_slots, bph = (bit / p.b_slots) & 1u;
-              mbar_wait(&b_empty[bs], bph ^ 1u);
+            for (int t = 0; t < 9; ++t) {
+              mbar_wait(&b_empty[bs], bph);
               if (elect_one_sync()) {
                 mbar_expect_tx(&b_full[bs], B_SLAB);
                 tma_load_3d(smem + p.b_off + bs * B_SLAB, &p.tmB, &b_full[bs], kc * 64, col0, p.wtap[t]);
               }
               __syncwarp();
+              if (++bs == (uint32_t)p.b_slots) { bs = 0; bph ^= 1u; }
             }
           }
         }
@@ -136,52 +137,71 @@ __global__ void __launch_bounds__(kThreadsH, 1)
     // ===================== MMA issuer (converged warp, elected issue) =====================
     {
       constexpr uint32_t idesc = umma_idesc_bf16(128, BLOCK_N, 0, 0);
-      uint32_t ait = 0, bit = 0, tile = 0;
-      uint32_t tap_off[9];
+      constexpr uint32_t BSLAB16 = B_SLAB >> 4;
+      uint32_t toff16[9];  // tap (dh,dw) -> rows into the halo tile, in 16-byte descriptor units
 #pragma unroll
-      for (int t = 0; t < 9; ++t) tap_off[t] = (uint32_t)(((p.dh[t] + 1) * pitch + (p.dw[t] + 1)) * 128);
-      const uint32_t sbo = (uint32_t)pitch * 128;
-      const uint32_t sA0 = smem_u32(smem), sB0 = smem_u32(smem + p.b_off);
+      for (int t = 0; t < 9; ++t) toff16[t] = (uint32_t)(((p.dh[t] + 1) * pitch + (p.dw[t] + 1)) * 8);
+      const uint32_t a_stage16 = (uint32_t)p.a_stage_bytes >> 4;
+      const uint64_t adesc0 = umma_smem_desc(smem_u32(smem), 16, (uint32_t)pitch * 128);
+      const uint64_t bdesc0 = umma_smem_desc(smem_u32(smem + p.b_off), 16, 1024);
+      uint32_t s = 0, ph = 0, bs = 0, bph = 0, tile = 0;
       for (int mt = mt0; mt < p.mtiles; mt += mstep, ++tile) {
         const uint32_t acc = tile & 1u, aph = (tile >> 1) & 1u;
         mbar_wait(&tmem_empty[acc], aph ^ 1u);
         tcgen05_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
-        for (int kc = 0; kc < p.kchunks; ++kc, ++ait) {
-          const uint32_t s = ait % p.a_stages, ph = (ait / p.a_stages) & 1u;
+        for (int kc = 0; kc < p.kchunks; ++kc) {
           mbar_wait(&a_full[s], ph);
           tcgen05_fence_after();
-          const uint32_t sa = sA0 + s * p.a_stage_bytes;
-#pragma unroll
-          for (int t = 0; t < 9; ++t) {
-            uint32_t bs;
-            if (p.resident) {
-              bs = kc * 9 + t;
-              if (tile == 0) {
-                mbar_wait(&b_full[bs], 0);
-                tcgen05_fence_after();
-              }
-            } else {
-              bs = bit % p.b_slots;
-              mbar_wait(&b_full[bs], (bit / p.b_slots) & 1u);
-              tcgen05_fence_after();
-              ++bit;
-            }
-            const uint64_t adesc = umma_smem_desc(sa + tap_off[t], 16, sbo);
-            const uint64_t bdesc = umma_smem_desc(sB0 + bs * B_SLAB, 16, 1024);
+          const uint64_t ad_s = adesc0 + (uint64_t)(s * a_stage16);
+          const bool last = kc == p.kchunks - 1;
+          if (p.resident && tile != 0) {
+            // steady state: weights are resident, the whole chunk (9 taps x 4 MMAs) is one issue block
+            const uint64_t bd_k = bdesc0 + (uint64_t)((uint32_t)kc * 9u * BSLAB16);
             if (elect_one_sync()) {
 #pragma unroll
-              for (int k = 0; k < 4; ++k)
-                umma_bf16_ss(tmem_d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
-                             (kc | t | k) != 0 ? 1u : 0u);
-              if (!p.resident) tcgen05_commit(&b_empty[bs]);
-              if (t == 8) {
-                tcgen05_commit(&a_empty[s]);
-                if (kc == p.kchunks - 1) tcgen05_commit(&tmem_full[acc]);
+              for (int t = 0; t < 9; ++t) {
+                const uint64_t ad = ad_s + (uint64_t)toff16[t];
+                const uint64_t bd = bd_k + (uint64_t)(t * BSLAB16);
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                  umma_bf16_ss(tmem_d, ad + (uint64_t)(2 * k), bd + (uint64_t)(2 * k), idesc,
+                               (t | k) != 0 ? 1u : (kc != 0 ? 1u : 0u));
               }
+              tcgen05_commit(&a_empty[s]);
+              if (last) tcgen05_commit(&tmem_full[acc]);
             }
             __syncwarp();
+          } else {
+#pragma unroll
+            for (int t = 0; t < 9; ++t) {
+              uint32_t slot;
+              if (p.resident) {
+                slot = kc * 9 + t;
+                mbar_wait(&b_full[slot], 0);
+              } else {
+                slot = bs;
+                mbar_wait(&b_full[bs], bph);
+              }
+              tcgen05_fence_after();
+              const uint64_t ad = ad_s + (uint64_t)toff16[t];
+              const uint64_t bd = bdesc0 + (uint64_t)(slot * BSLAB16);
+              if (elect_one_sync()) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                  umma_bf16_ss(tmem_d, ad + (uint64_t)(2 * k), bd + (uint64_t)(2 * k), idesc,
+                               (kc | t | k) != 0 ? 1u : 0u);
+                if (!p.resident) tcgen05_commit(&b_empty[bs]);
+                if (t == 8) {
+                  tcgen05_commit(&a_empty[s]);
+                  if (last) tcgen05_commit(&tmem_full[acc]);
+                }
+              }
+              __syncwarp();
+              if (!p.resident && ++bs == (uint32_t)p.b_slots) { bs = 0; bph ^= 1u; }
+            }
           }
+          if (++s == (uint32_t)p.a_stages) { s = 0; ph ^= 1u; }
         }
       }
     }
@@ -191,8 +211,18 @@ __global__ void __launch_bounds__(kThreadsH, 1)
     const int half = (warp - 2) >> 2;    // which 32-column chunks this warp drains
     const int r = wq * 32 + lane;
     const int lh = r / p.wt, lw = r % p.wt;
-    float* stat_sm = reinterpret_cast<float*>(smem + p.stat_off) + wq * 2 * BLOCK_N;
     constexpr int NCH = BLOCK_N / 32;
+    constexpr int MYCH = (NCH + 1) / 2;  // chunks per warp (chunk c = half + 2*ci)
+    // BatchNorm partial sums stay in registers across ALL tiles of this CTA (row r of every tile,
+    // this warp's columns); the cross-lane reduction runs once, after the tile loop.
+    constexpr int SCH = STATS ? MYCH : 1;
+    float s1[SCH][32], s2[SCH][32];
+    if (STATS) {
+#pragma unroll
+      for (int ci = 0; ci < SCH; ++ci)
+#pragma unroll
+        for (int j = 0; j < 32; ++j) s1[ci][j] = s2[ci][j] = 0.0f;
+    }
     uint32_t tile = 0;
     for (int mt = mt0; mt < p.mtiles; mt += mstep, ++tile) {
       const int tw = mt % p.tilesW, th = (mt / p.tilesW) % p.tilesH, pn = mt / (p.tilesW * p.tilesH);
@@ -200,72 +230,94 @@ __global__ void __launch_bounds__(kThreadsH, 1)
       const bool row_ok = phh < p.oh && pw < p.ow;
       const long long row_off = (long long)pn * p.osn + (long long)phh * p.osh + (long long)pw * p.osw;
       const uint32_t acc = tile & 1u, aph = (tile >> 1) & 1u;
+      // accumulate mode: fetch the old output values BEFORE waiting for the accumulator, so
+      // their (uncoalesced, one pixel row per lane) latency hides behind the MMAs
+      uint4 old[MYCH][4];
+      if (!STATS && p.accumulate && row_ok) {
+#pragma unroll
+        for (int ci = 0; ci < MYCH; ++ci) {
+          const int c = half + 2 * ci;
+          if (c < NCH) {
+#pragma unroll
+            for (int g = 0; g < 4; ++g)
+              old[ci][g] = *reinterpret_cast<const uint4*>(p.out + row_off + col0 + c * 32 + g * 8);
+          }
+        }
+      }
       mbar_wait(&tmem_full[acc], aph);
       tcgen05_fence_after();
       const uint32_t tmem_d = tmem_base + acc * BLOCK_N + ((uint32_t)(wq * 32) << 16);
       if (half >= NCH) {  // BLOCK_N == 32: the second warp of the quadrant has no columns
         if (lane == 0) mbar_arrive(&tmem_empty[acc]);
       }
-#pragma unroll 1
-      for (int c = half; c < NCH; c += 2) {
-        float v[32];
-        tmem_ld_32x32b_x32(tmem_d + (uint32_t)(c * 32), v);
-        if (c + 2 >= NCH) {  // this warp's last chunk is in registers: release the accumulator
-          tcgen05_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&tmem_empty[acc]);
-        }
-        const int colc = col0 + c * 32;
-        if (p.bias) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + colc + j);
-        }
-        if (row_ok) {
-          bf16* dst = p.out + row_off + colc;
+      for (int ci = 0; ci < MYCH; ++ci) {
+        const int c = half + 2 * ci;
+        if (c < NCH) {
+          float v[32];
+          tmem_ld_32x32b_x32(tmem_d + (uint32_t)(c * 32), v);
+          if (c + 2 >= NCH) {  // this warp's last chunk is in registers: release the accumulator
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+          }
+          const int colc = col0 + c * 32;
+          if (p.bias) {
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            float o[8];
+            for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + colc + j);
+          }
+          if (row_ok) {
+            bf16* dst = p.out + row_off + colc;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) o[j] = v[g * 8 + j];
-            if (p.accumulate) {
-              const uint4 old = *reinterpret_cast<const uint4*>(dst + g * 8);
-              const float2 a0 = bf2_to_f2(old.x), a1 = bf2_to_f2(old.y), a2 = bf2_to_f2(old.z),
-                           a3 = bf2_to_f2(old.w);
-              o[0] += a0.x; o[1] += a0.y; o[2] += a1.x; o[3] += a1.y;
-              o[4] += a2.x; o[5] += a2.y; o[6] += a3.x; o[7] += a3.y;
+            for (int g = 0; g < 4; ++g) {
+              float o[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) o[j] = v[g * 8 + j];
+              if (!STATS && p.accumulate) {
+                const uint4 od = old[ci][g];
+                const float2 a0 = bf2_to_f2(od.x), a1 = bf2_to_f2(od.y), a2 = bf2_to_f2(od.z),
+                             a3 = bf2_to_f2(od.w);
+                o[0] += a0.x; o[1] += a0.y; o[2] += a1.x; o[3] += a1.y;
+                o[4] += a2.x; o[5] += a2.y; o[6] += a3.x; o[7] += a3.y;
+              }
+              uint4 pk;
+              pk.x = f2_to_bf2(o[0], o[1]);
+              pk.y = f2_to_bf2(o[2], o[3]);
+              pk.z = f2_to_bf2(o[4], o[5]);
+              pk.w = f2_to_bf2(o[6], o[7]);
+              *reinterpret_cast<uint4*>(dst + g * 8) = pk;
             }
-            uint4 pk;
-            pk.x = f2_to_bf2(o[0], o[1]);
-            pk.y = f2_to_bf2(o[2], o[3]);
-            pk.z = f2_to_bf2(o[4], o[5]);
-            pk.w = f2_to_bf2(o[6], o[7]);
-            *reinterpret_cast<uint4*>(dst + g * 8) = pk;
+            if (STATS) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                s1[ci][j] += v[j];
+                s2[ci][j] = fmaf(v[j], v[j], s2[ci][j]);
+              }
+            }
           }
         }
-        if (p.stats) {
-          float s1[32], s2[32];
+      }
+    }
+    if (STATS) {  // one (sum, sumsq) row per CTA group; rows no group owns are zero-filled
+      float* stat_sm = reinterpret_cast<float*>(smem + p.stat_off) + wq * 2 * BLOCK_N;
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const float x = row_ok ? v[j] : 0.0f;
-            s1[j] = x;
-            s2[j] = x * x;
-          }
-          const float a = warp_transpose_sum32(s1, lane);
-          const float b = warp_transpose_sum32(s2, lane);
+      for (int ci = 0; ci < MYCH; ++ci) {
+        const int c = half + 2 * ci;
+        if (c < NCH) {
+          const float a = warp_transpose_sum32(s1[ci], lane);
+          const float b = warp_transpose_sum32(s2[ci], lane);
           stat_sm[c * 32 + lane] = a;
           stat_sm[BLOCK_N + c * 32 + lane] = b;
         }
       }
-      if (p.stats) {  // fold the four quadrants: one (sum, sumsq) row per pixel tile
-        asm volatile("bar.sync 1, 256;" ::: "memory");
-        const float* sm0 = reinterpret_cast<const float*>(smem + p.stat_off);
-        float* row = p.stats + (size_t)mt * 2 * p.ngemm;
-        for (int e = threadIdx.x - 64; e < 2 * BLOCK_N; e += 256) {
-          const float x = (sm0[e] + sm0[2 * BLOCK_N + e]) + (sm0[4 * BLOCK_N + e] + sm0[6 * BLOCK_N + e]);
-          const int k = e / BLOCK_N, cc = e % BLOCK_N;
-          row[k * p.ngemm + col0 + cc] = x;
-        }
-        asm volatile("bar.sync 1, 256;" ::: "memory");  // stat_sm is rewritten by the next tile
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      const float* sm0 = reinterpret_cast<const float*>(smem + p.stat_off);
+      for (int e = threadIdx.x - 64; e < 2 * BLOCK_N; e += 256) {
+        const float x = (sm0[e] + sm0[2 * BLOCK_N + e]) + (sm0[4 * BLOCK_N + e] + sm0[6 * BLOCK_N + e]);
+        const int k = e / BLOCK_N, cc = e % BLOCK_N;
+        p.stats[((size_t)mt0 * 2 + k) * p.ngemm + col0 + cc] = x;
+        for (int rr = mt0 + mstep; rr < p.stat_rows; rr += mstep)
+          p.stats[((size_t)rr * 2 + k) * p.ngemm + col0 + cc] = 0.0f;
       }
     }
     tcgen05_fence_before();
@@ -284,9 +336,15 @@ struct HaloOp : b2seg_op {
   size_t smem;
   const char* name() const override { return "halo3x3"; }
   int run(cudaStream_t st) override {
-    if (block_n == 128) halo3x3_kernel<128><<<grid, kThreadsH, smem, st>>>(p);
-    else if (block_n == 64) halo3x3_kernel<64><<<grid, kThreadsH, smem, st>>>(p);
-    else halo3x3_kernel<32><<<grid, kThreadsH, smem, st>>>(p);
+#define HALO_LAUNCH(BN)                                                        \
+  do {                                                                        \
+    if (p.stats) halo3x3_kernel<BN, true><<<grid, kThreadsH, smem, st>>>(p);  \
+    else halo3x3_kernel<BN, false><<<grid, kThreadsH, smem, st>>>(p);         \
+  } while (0)
+    if (block_n == 128) HALO_LAUNCH(128);
+    else if (block_n == 64) HALO_LAUNCH(64);
+    else HALO_LAUNCH(32);
+#undef HALO_LAUNCH
     B2_CHECK_CUDA(cudaGetLastError());
     return B2SEG_OK;
   }
@@ -298,8 +356,10 @@ template <int BN>
 int set_halo_attr() {
   static bool done = false;
   if (!done) {
-    B2_CHECK_CUDA(cudaFuncSetAttribute(halo3x3_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       kSmemMax));
+    B2_CHECK_CUDA(cudaFuncSetAttribute(halo3x3_kernel<BN, true>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemMax));
+    B2_CHECK_CUDA(cudaFuncSetAttribute(halo3x3_kernel<BN, false>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemMax));
     done = true;
   }
   return B2SEG_OK;
@@ -314,6 +374,7 @@ int b2_halo3x3_try_create(const b2seg_tapgemm_desc* d, b2seg_op** out) {
   if (d->nsrc != 1 || d->nsub != 1 || d->sub[0].ntaps != 9 || d->cq > 0 || d->wtaps != 9) return B2SEG_OK;
   const auto& sub = d->sub[0];
   if (sub.out_offset != 0) return B2SEG_OK;
+  if (d->stats && d->accumulate) return B2SEG_OK;  // not a combination the halo epilogue implements
   unsigned seen = 0;
   for (int t = 0; t < 9; ++t) {
     const auto& tp = sub.taps[t];
@@ -396,6 +457,7 @@ int b2_halo3x3_try_create(const b2seg_tapgemm_desc* d, b2seg_op** out) {
   p.bias = d->bias;
   p.stats = d->stats;
   p.accumulate = d->accumulate;
+  p.stat_rows = b2seg_tapgemm_stat_rows(d->on, d->oh, d->ow);
   p.resident = resident; p.a_stages = a_stages; p.b_slots = b_slots;
   p.a_stage_bytes = a_stage;
   p.b_off = a_stages * a_stage;

@@ -43,7 +43,7 @@ struct alignas(64) TapGemmParams {
   const float* bias;
   float* stats;
   int accumulate;
-  int nitems;  // mtiles * (ngemm / BLOCK_N) * nsub
+  int nsub, stat_rows;
 };
 
 constexpr int kThreadsTG = 192;
@@ -55,21 +55,20 @@ struct TGSmem {
   static constexpr int STAGE = A_BYTES + B_BYTES;
   static constexpr int BAR_OFF = NSTAGES * STAGE;
   // full[NS], empty[NS], tmem_full[2], tmem_empty[2], tmem slot
-  static constexpr int STAT_OFF = BAR_OFF + (2 * NSTAGES + 4) * 8 + 16;  // [4 warps][2][BLOCK_N] f32
-  static constexpr int TOTAL = STAT_OFF + 4 * 2 * BLOCK_N * 4 + 1024 /*align slack*/;
+  // [4 warps][2][BLOCK_N] f32 per-tile sums + [2][BLOCK_N] f32 running totals
+  static constexpr int STAT_OFF = BAR_OFF + (2 * NSTAGES + 4) * 8 + 16;
+  static constexpr int TOTAL = STAT_OFF + 5 * 2 * BLOCK_N * 4 + 1024 /*align slack*/;
 };
 
-// Work item `idx` -> (column tile, pixel tile, sub-problem); column tiles of one pixel tile are
-// adjacent in the order so CTAs running side by side share the A bricks through L2.
+// A CTA keeps ONE column tile (blockIdx.x % ntiles; neighbouring CTAs share the A bricks through
+// L2) and walks the (pixel tile, sub-problem) pairs  g, g + groups, ...  of its group g.
 struct TGItem {
-  int ntile, mtile, sub;
+  int mtile, sub;
 };
-__device__ __forceinline__ TGItem tg_item(int idx, int ntiles, int mtiles) {
+__device__ __forceinline__ TGItem tg_item(int j, int mtiles) {
   TGItem it;
-  it.ntile = idx % ntiles;
-  const int r = idx / ntiles;
-  it.mtile = r % mtiles;
-  it.sub = r / mtiles;
+  it.mtile = j % mtiles;
+  it.sub = j / mtiles;
   return it;
 }
 
@@ -92,7 +91,9 @@ __global__ void __launch_bounds__(kThreadsTG)
 
   const int warp = warp_id_uniform(), lane = threadIdx.x & 31;
   const int ntiles = p.ngemm / BLOCK_N;
-  const int nitems = p.nitems;
+  const int ntile = blockIdx.x % ntiles, grp = blockIdx.x / ntiles, groups = gridDim.x / ntiles;
+  const int njobs = p.mtiles * p.nsub;
+  const int col0 = ntile * BLOCK_N;
 
   if (warp == 0 && lane == 0) {
     for (int i = 0; i < NSTAGES; ++i) {
@@ -116,21 +117,18 @@ __global__ void __launch_bounds__(kThreadsTG)
   if (warp == 0) {
     // ===================== TMA producer (converged warp, elected issue) =====================
     {
-      uint32_t it = 0;
-      for (int idx = blockIdx.x; idx < nitems; idx += gridDim.x) {
-        const TGItem w = tg_item(idx, ntiles, p.mtiles);
+      uint32_t s = 0, ph = 1;  // ring slot and the parity a free slot shows
+      for (int j = grp; j < njobs; j += groups) {
+        const TGItem w = tg_item(j, p.mtiles);
         const TapSub& sub = p.sub[w.sub];
         const int tw = w.mtile % p.tilesW, th = (w.mtile / p.tilesW) % p.tilesH,
                   tn = w.mtile / (p.tilesW * p.tilesH);
         const int w0 = tw * p.wt, h0 = th * p.ht, n0 = tn * p.nt;
-        const int col0 = w.ntile * BLOCK_N;
         for (int t = 0; t < sub.ntaps; ++t) {
           const CUtensorMap* tmA = &p.tmA[sub.src[t]];
           const int cw = w0 + sub.dw[t], ch = h0 + sub.dh[t], wtap = sub.wt[t];
-          for (int kc = 0; kc < p.kchunks; ++kc, ++it) {
-            const uint32_t s = it % NSTAGES;
-            const uint32_t ph = (it / NSTAGES) & 1u;
-            mbar_wait(&empty_bar[s], ph ^ 1u);
+          for (int kc = 0; kc < p.kchunks; ++kc) {
+            mbar_wait(&empty_bar[s], ph);
             if (elect_one_sync()) {
               mbar_expect_tx(&full_bar[s], L::STAGE);
               uint8_t* sa = smem + s * L::STAGE;
@@ -138,6 +136,7 @@ __global__ void __launch_bounds__(kThreadsTG)
               tma_load_3d(sa + A_BYTES, &p.tmB, &full_bar[s], kc * 64, col0, wtap);
             }
             __syncwarp();
+            if (++s == NSTAGES) { s = 0; ph ^= 1u; }
           }
         }
       }
@@ -146,31 +145,32 @@ __global__ void __launch_bounds__(kThreadsTG)
     // ===================== MMA issuer (converged warp, elected issue) =====================
     {
       constexpr uint32_t idesc = umma_idesc_bf16(128, BLOCK_N, 0, 0);
-      uint32_t it = 0, tile = 0;
-      for (int idx = blockIdx.x; idx < nitems; idx += gridDim.x, ++tile) {
-        const TGItem w = tg_item(idx, ntiles, p.mtiles);
+      // descriptors of ring slot 0; slot s adds s * STAGE / 16 to the 14-bit address field
+      const uint64_t adesc0 = umma_smem_desc(smem_u32(smem), 16, 1024);
+      const uint64_t bdesc0 = umma_smem_desc(smem_u32(smem) + A_BYTES, 16, 1024);
+      uint32_t s = 0, ph = 0, tile = 0;
+      for (int j = grp; j < njobs; j += groups, ++tile) {
+        const TGItem w = tg_item(j, p.mtiles);
         const int iters = p.sub[w.sub].ntaps * p.kchunks;
         const uint32_t acc = tile & 1u, aph = (tile >> 1) & 1u;
         mbar_wait(&tmem_empty[acc], aph ^ 1u);  // epilogue has drained this accumulator
         tcgen05_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
-        for (int i = 0; i < iters; ++i, ++it) {
-          const uint32_t s = it % NSTAGES;
-          const uint32_t ph = (it / NSTAGES) & 1u;
+        for (int i = 0; i < iters; ++i) {
           mbar_wait(&full_bar[s], ph);
           tcgen05_fence_after();
-          const uint32_t sa = smem_u32(smem + s * L::STAGE);
-          const uint64_t adesc = umma_smem_desc(sa, 16, 1024);
-          const uint64_t bdesc = umma_smem_desc(sa + A_BYTES, 16, 1024);
+          const uint64_t so = (uint64_t)(s * (uint32_t)(L::STAGE >> 4));
+          const uint64_t adesc = adesc0 + so, bdesc = bdesc0 + so;
           if (elect_one_sync()) {
+            umma_bf16_ss(tmem_d, adesc, bdesc, idesc, i != 0 ? 1u : 0u);
 #pragma unroll
-            for (int k = 0; k < 4; ++k)  // 4 x (K = 16 bf16 = 32 B) per 64-channel chunk
-              umma_bf16_ss(tmem_d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
-                           (i | k) != 0 ? 1u : 0u);
+            for (int k = 1; k < 4; ++k)  // 4 x (K = 16 bf16 = 32 B) per 64-channel chunk
+              umma_bf16_ss(tmem_d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, 1u);
             tcgen05_commit(&empty_bar[s]);  // smem slot free once these MMAs retire
             if (i == iters - 1) tcgen05_commit(&tmem_full[acc]);
           }
           __syncwarp();
+          if (++s == NSTAGES) { s = 0; ph ^= 1u; }
         }
       }
     }
@@ -182,22 +182,39 @@ __global__ void __launch_bounds__(kThreadsTG)
     const int ln = r / hw, lh = (r % hw) / p.wt, lw = r % p.wt;
     const int cq_mask = (1 << p.cq_shift) - 1;
     float* stat_sm = reinterpret_cast<float*>(smem + L::STAT_OFF) + wq * 2 * BLOCK_N;
+    // running (sum, sumsq) of this CTA over all its tiles: entry e is owned by one thread
+    float* run_sm = reinterpret_cast<float*>(smem + L::STAT_OFF) + 8 * BLOCK_N;
+    if (p.stats)
+      for (int e = threadIdx.x - 64; e < 2 * BLOCK_N; e += 128) run_sm[e] = 0.0f;
     uint32_t tile = 0;
-    for (int idx = blockIdx.x; idx < nitems; idx += gridDim.x, ++tile) {
-      const TGItem w = tg_item(idx, ntiles, p.mtiles);
+    for (int j = grp; j < njobs; j += groups, ++tile) {
+      const TGItem w = tg_item(j, p.mtiles);
       const TapSub& sub = p.sub[w.sub];
       const int tw = w.mtile % p.tilesW, th = (w.mtile / p.tilesW) % p.tilesH,
                 tn = w.mtile / (p.tilesW * p.tilesH);
       const int pn = tn * p.nt + ln, phh = th * p.ht + lh, pw = tw * p.wt + lw;
-      const int col0 = w.ntile * BLOCK_N;
       const bool row_ok = pn < p.on && phh < p.oh && pw < p.ow;
       const long long row_off =
           sub.out_off + (long long)pn * p.osn + (long long)phh * p.osh + (long long)pw * p.osw;
       const uint32_t acc = tile & 1u, aph = (tile >> 1) & 1u;
+      // accumulate mode: fetch the old output values BEFORE waiting for the accumulator, so
+      // their (uncoalesced, one pixel row per lane) latency hides behind the MMAs
+      uint4 old[BLOCK_N / 32][4];
+      if (p.accumulate && row_ok) {
+#pragma unroll
+        for (int c = 0; c < BLOCK_N / 32; ++c)
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            const int col = col0 + c * 32 + g * 8;
+            const int q = col >> p.cq_shift;
+            old[c][g] = *reinterpret_cast<const uint4*>(
+                p.out + row_off + (long long)(q >> 1) * p.oqh + (long long)(q & 1) * p.oqw + (col & cq_mask));
+          }
+      }
       mbar_wait(&tmem_full[acc], aph);
       tcgen05_fence_after();
       const uint32_t tmem_d = tmem_base + acc * BLOCK_N + ((uint32_t)(wq * 32) << 16);
-#pragma unroll 1
+#pragma unroll
       for (int c = 0; c < BLOCK_N / 32; ++c) {
         float v[32];
         tmem_ld_32x32b_x32(tmem_d + (uint32_t)(c * 32), v);
@@ -222,9 +239,9 @@ __global__ void __launch_bounds__(kThreadsTG)
 #pragma unroll
             for (int j = 0; j < 8; ++j) o[j] = v[g * 8 + j];
             if (p.accumulate) {
-              const uint4 old = *reinterpret_cast<const uint4*>(dst);
-              const float2 a0 = bf2_to_f2(old.x), a1 = bf2_to_f2(old.y), a2 = bf2_to_f2(old.z),
-                           a3 = bf2_to_f2(old.w);
+              const uint4 od = old[c][g];
+              const float2 a0 = bf2_to_f2(od.x), a1 = bf2_to_f2(od.y), a2 = bf2_to_f2(od.z),
+                           a3 = bf2_to_f2(od.w);
               o[0] += a0.x; o[1] += a0.y; o[2] += a1.x; o[3] += a1.y;
               o[4] += a2.x; o[5] += a2.y; o[6] += a3.x; o[7] += a3.y;
             }
@@ -250,16 +267,20 @@ __global__ void __launch_bounds__(kThreadsTG)
           stat_sm[BLOCK_N + c * 32 + lane] = b;
         }
       }
-      if (p.stats) {  // fold the four warps' sums: one (sum, sumsq) row per pixel tile
+      if (p.stats) {  // fold the four warps' sums into the CTA's running totals
         asm volatile("bar.sync 1, 128;" ::: "memory");
         const float* sm0 = reinterpret_cast<const float*>(smem + L::STAT_OFF);
-        float* row = p.stats + (size_t)w.mtile * 2 * p.ngemm;
-        for (int e = threadIdx.x - 64; e < 2 * BLOCK_N; e += 128) {
-          const float x = (sm0[e] + sm0[2 * BLOCK_N + e]) + (sm0[4 * BLOCK_N + e] + sm0[6 * BLOCK_N + e]);
-          const int k = e / BLOCK_N, cc = e % BLOCK_N;
-          row[k * p.ngemm + col0 + cc] = x;
-        }
+        for (int e = threadIdx.x - 64; e < 2 * BLOCK_N; e += 128)
+          run_sm[e] += (sm0[e] + sm0[2 * BLOCK_N + e]) + (sm0[4 * BLOCK_N + e] + sm0[6 * BLOCK_N + e]);
         asm volatile("bar.sync 1, 128;" ::: "memory");  // stat_sm is rewritten by the next item
+      }
+    }
+    if (p.stats) {  // one (sum, sumsq) row per CTA group; rows no group owns are zero-filled
+      for (int e = threadIdx.x - 64; e < 2 * BLOCK_N; e += 128) {
+        const int k = e / BLOCK_N, cc = e % BLOCK_N;
+        p.stats[((size_t)grp * 2 + k) * p.ngemm + col0 + cc] = run_sm[e];
+        for (int rr = grp + groups; rr < p.stat_rows; rr += groups)
+          p.stats[((size_t)rr * 2 + k) * p.ngemm + col0 + cc] = 0.0f;
       }
     }
     tcgen05_fence_before();
@@ -320,7 +341,8 @@ extern "C" int b2seg_tapgemm_stat_rows(int on, int oh, int ow) {
   int wt, ht, nt;
   b2_pick_pixel_tile(on, oh, ow, &wt, &ht, &nt);
   const int tiles = ((ow + wt - 1) / wt) * ((oh + ht - 1) / ht) * ((on + nt - 1) / nt);
-  return tiles;
+  const int cap = 2 * b2_num_sms();  // one row per CTA group of the persistent conv kernels
+  return tiles < cap ? tiles : cap;
 }
 
 extern "C" int b2seg_tapgemm_create(const b2seg_tapgemm_desc* d, b2seg_op** out) {
@@ -411,10 +433,15 @@ extern "C" int b2seg_tapgemm_create(const b2seg_tapgemm_desc* d, b2seg_op** out)
   p.bias = d->bias;
   p.stats = d->stats;
   p.accumulate = d->accumulate;
-  p.nitems = p.mtiles * (d->ngemm / bn) * d->nsub;
-  {  // persistent grid: two CTAs per SM (96 KB of shared memory and <= 256 TMEM columns each)
-    const int cap = 2 * b2_num_sms();
-    op->grid = dim3(p.nitems < cap ? p.nitems : cap, 1, 1);
+  p.nsub = d->nsub;
+  p.stat_rows = b2seg_tapgemm_stat_rows(d->on, d->oh, d->ow);
+  {  // persistent grid: two CTAs per SM (96 KB of shared memory and <= 256 TMEM columns each),
+     // a multiple of the column-tile count so that a CTA keeps one column tile
+    const int ntiles = d->ngemm / bn;
+    int groups = 2 * b2_num_sms() / ntiles;
+    if (groups > p.mtiles * d->nsub) groups = p.mtiles * d->nsub;
+    if (groups < 1) groups = 1;
+    op->grid = dim3(groups * ntiles, 1, 1);
   }
   int rc;
   if (bn == 128) rc = set_smem_attr<128, 3>();

@@ -93,14 +93,13 @@ __global__ void __launch_bounds__(kThreadsWG, 1)
         dw[i] = p.taps[tap].dw;
         c0[i] = (ch[i] % p.cchunks) * 64;
       }
-      for (int it = 0; it < my_ktiles; ++it) {
-        const int kt = split + it * p.nsplit;
+      uint32_t s = 0, ph = 1;  // ring slot and the parity a free slot shows
+      int kt = split;
+      for (int it = 0; it < my_ktiles; ++it, kt += p.nsplit) {
         const int tw = kt % p.tilesW, th = (kt / p.tilesW) % p.tilesH,
                   tn = kt / (p.tilesW * p.tilesH);
         const int w0 = tw * p.wt, h0 = th * p.ht, n0 = tn * p.nt;
-        const int s = it % NSTAGES;
-        const uint32_t ph = (uint32_t)(it / NSTAGES) & 1u;
-        mbar_wait(&empty_bar[s], ph ^ 1u);
+        mbar_wait(&empty_bar[s], ph);
         if (elect_one_sync()) {
           mbar_expect_tx(&full_bar[s], L::STAGE);
           uint8_t* st = smem + s * L::STAGE;
@@ -112,29 +111,31 @@ __global__ void __launch_bounds__(kThreadsWG, 1)
                         ntile * BLOCK_N + b * 64, w0, h0, n0);
         }
         __syncwarp();
+        if (++s == NSTAGES) { s = 0; ph ^= 1u; }
       }
     }
   } else if (warp == 1) {
     {  // converged MMA warp, elected issue
       constexpr uint32_t idesc = umma_idesc_bf16(128, BLOCK_N, 1, 1);
+      // descriptors of ring slot 0, K step 0; slot s adds s*STAGE/16, K step k adds 2048/16
+      const uint64_t adesc0 = umma_smem_desc(smem_u32(smem), CHUNK_BYTES, 1024);
+      const uint64_t bdesc0 = umma_smem_desc(smem_u32(smem) + 2 * CHUNK_BYTES, CHUNK_BYTES, 1024);
+      uint32_t s = 0, ph = 0;
       for (int it = 0; it < my_ktiles; ++it) {
-        const int s = it % NSTAGES;
-        const uint32_t ph = (uint32_t)(it / NSTAGES) & 1u;
         mbar_wait(&full_bar[s], ph);
         tcgen05_fence_after();
-        const uint32_t sa = smem_u32(smem + s * L::STAGE);
-        const uint32_t sb = sa + 2 * CHUNK_BYTES;
+        const uint64_t so = (uint64_t)(s * (uint32_t)(L::STAGE >> 4));
+        const uint64_t ad = adesc0 + so, bd = bdesc0 + so;
         if (elect_one_sync()) {
+          umma_bf16_ss(tmem_base, ad, bd, idesc, it != 0 ? 1u : 0u);
 #pragma unroll
-          for (int k = 0; k < 8; ++k) {  // 16 pixels (rows of 128 B) per MMA
-            const uint64_t adesc = umma_smem_desc(sa + k * 2048, CHUNK_BYTES, 1024);
-            const uint64_t bdesc = umma_smem_desc(sb + k * 2048, CHUNK_BYTES, 1024);
-            umma_bf16_ss(tmem_base, adesc, bdesc, idesc, (it | k) != 0 ? 1u : 0u);
-          }
+          for (int k = 1; k < 8; ++k)  // 16 pixels (rows of 128 B) per MMA
+            umma_bf16_ss(tmem_base, ad + (uint64_t)(k * 128), bd + (uint64_t)(k * 128), idesc, 1u);
           tcgen05_commit(&empty_bar[s]);
           if (it == my_ktiles - 1) tcgen05_commit(tmem_full);
         }
         __syncwarp();
+        if (++s == NSTAGES) { s = 0; ph ^= 1u; }
       }
     }
   } else {
