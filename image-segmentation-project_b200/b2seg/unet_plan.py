@@ -187,16 +187,21 @@ class UNetPlan:
         """dz = (da [+ da2]) * [mask > 0];  dy = BatchNorm-backward(dz);  dgamma, dbeta (, dbias)."""
         P, C_ = y.n * y.h * y.w, y.c
         rows = eo.partial_rows(L.EW_BN_BWD_REDUCE, P, C_)
+        self_mask = isinstance(mask, str)  # "self": a = relu(BN(y)), the mask is recomputed from y
+        if self_mask:
+            assert mask == "self"
+            mask = None
         pp = [da, da2, mask, y, bnp]
         ii = [P, C_, da.sw, da2.sw if da2 else 0, mask.sw if mask else 0, y.sw]
-        self.B(eo.ew(L.EW_BN_BWD_REDUCE, p=pp + [self.part], i=ii))
+        tail = [0, 0, 0, 1 if self_mask else 0]  # i6..i8 unused by REDUCE, i9 = self-mask flag
+        self.B(eo.ew(L.EW_BN_BWD_REDUCE, p=pp + [self.part], i=ii + tail))
         coef = self._alloc((3, C_), F32)
         self.B(eo.ew(L.EW_BN_BWD_FINALIZE,
                      p=[self.part, self.params[prefix + ".weight"], bnp, self.gview(prefix + ".weight"),
                         self.gview(prefix + ".bias"), coef, dbias],
                      i=[rows, C_, P, 0, 1 if self.training else 0]))
         self.B(eo.ew(L.EW_BN_BWD_APPLY, p=pp + [coef, dy, dz],
-                     i=ii + [dy.sw, dz.sw if dz else 0, 2 if dz_acc else 1]))
+                     i=ii + [dy.sw, dz.sw if dz else 0, 2 if dz_acc else 1, 1 if self_mask else 0]))
 
     def conv_backward(self, x: Act, dy: View, wname, k, stride, want_dx=True):
         """Weight gradient into the flat buffer and (accumulating) data gradient into x.g."""
@@ -250,7 +255,7 @@ class UNetPlan:
 
         def bwd_stem():
             dy0 = View(self._alloc((N, h1, w1, 64), BF16))
-            self.bn_backward("bn1", x1.g, x1.v, y0, bnp0, dy0)
+            self.bn_backward("bn1", x1.g, "self", y0, bnp0, dy0)
             self.stored_g.update({"stem.y": dy0, "x1": x1.g})
             rows = eo.stem_wgrad_rows(N, H, W)
             wsS = self._alloc((rows, 3136), F32)
@@ -372,7 +377,7 @@ class UNetPlan:
                 self.bn_backward(pre + ".bn2", out.g, out.v, y2, b2, dy2, dz=hin.g, dz_acc=hin.take_grad())
             self.conv_backward(a1, dy2, pre + ".conv2.weight", 3, 1)
             dy1 = self._like(y1)
-            self.bn_backward(pre + ".bn1", a1.g, a1.v, y1, b1, dy1)
+            self.bn_backward(pre + ".bn1", a1.g, "self", y1, b1, dy1)
             self.conv_backward(hin, dy1, pre + ".conv1.weight", 3, stride)
             if ds:
                 dyd = self._like(yd)
@@ -415,10 +420,10 @@ class UNetPlan:
                 self.bn_backward(pre + ".bn3", out.g, out.v, y3, b3, dy3, dz=hin.g, dz_acc=hin.take_grad())
             self.conv_backward(a2, dy3, pre + ".conv3.weight", 1, 1)
             dy2 = self._like(y2)
-            self.bn_backward(pre + ".bn2", a2.g, a2.v, y2, b2, dy2)
+            self.bn_backward(pre + ".bn2", a2.g, "self", y2, b2, dy2)
             self.conv_backward(a1, dy2, pre + ".conv2.weight", 3, stride)
             dy1 = self._like(y1)
-            self.bn_backward(pre + ".bn1", a1.g, a1.v, y1, b1, dy1)
+            self.bn_backward(pre + ".bn1", a1.g, "self", y1, b1, dy1)
             self.conv_backward(hin, dy1, pre + ".conv1.weight", 1, 1)
             if ds:
                 dyd = self._like(yd)
@@ -458,10 +463,10 @@ class UNetPlan:
 
         def bwd_dec():
             dyb = self._like(yb)
-            self.bn_backward(p + ".4", b.g, b.v, yb, bb, dyb, dbias=self.gview(p + ".3.bias"))
+            self.bn_backward(p + ".4", b.g, "self", yb, bb, dyb, dbias=self.gview(p + ".3.bias"))
             self.conv_backward(a, dyb, p + ".3.weight", 3, 1)
             dya = self._like(ya)
-            self.bn_backward(p + ".1", a.g, a.v, ya, ba, dya, dbias=self.gview(p + ".0.bias"))
+            self.bn_backward(p + ".1", a.g, "self", ya, ba, dya, dbias=self.gview(p + ".0.bias"))
             self.conv_backward(catA, dya, p + ".0.weight", 3, 1)  # first writer of the whole dcat
             up.gw = True
             if not self.attn:

@@ -1,5 +1,6 @@
 // libb2seg.so — ABI bookkeeping: version, thread-local error text, device query,
 // TMA descriptor encoding via the driver entry point.
+#include <stdlib.h>
 #include <cudaTypedefs.h>
 #include <stdarg.h>
 #include <string.h>
@@ -33,6 +34,15 @@ extern "C" int b2seg_device_info(char* name, int len, int* sms, int* cc) {
   if (sms) *sms = prop.multiProcessorCount;
   if (cc) *cc = prop.major * 10 + prop.minor;
   return B2SEG_OK;
+}
+
+bool b2_pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B2SEG_PDL");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v != 0;
 }
 
 int b2_encode_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,

@@ -39,6 +39,7 @@ __device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + __ex
 
 // ------------------------------------------------------------------- DOT1_FWD ----
 __global__ void __launch_bounds__(kEwThreads) dot1_fwd_kernel(const EwArgs a) {
+  pdl_prologue();
   const bf16* v = (const bf16*)a.p[0];
   const float* w = (const float*)a.p[1];
   const float* b = (const float*)a.p[2];
@@ -79,6 +80,7 @@ __global__ void __launch_bounds__(kEwThreads) dot1_fwd_kernel(const EwArgs a) {
 // ------------------------------------------------------------------- DOT1_BWD ----
 // ds[p] = dscalar[p]  or  BatchNorm2d(1)-backward of it;  dv = ds * w;  partial = (dW[C], db).
 __global__ void __launch_bounds__(kEwThreads) dot1_bwd_kernel(const EwArgs a) {
+  pdl_prologue();
   extern __shared__ float red[];  // [gpb][C]
   const float* dsc = (const float*)a.p[0];
   const bf16* v = (const bf16*)a.p[1];
@@ -139,6 +141,7 @@ __global__ void __launch_bounds__(kEwThreads) dot1_bwd_kernel(const EwArgs a) {
 
 // ----------------------------------------------------------------- GATE_APPLY ----
 __global__ void __launch_bounds__(kEwThreads) gate_apply_kernel(const EwArgs a) {
+  pdl_prologue();
   const float* pre = (const float*)a.p[0];
   const float* bnp = (const float*)a.p[1];
   const bf16* x = (const bf16*)a.p[2];
@@ -163,6 +166,7 @@ __global__ void __launch_bounds__(kEwThreads) gate_apply_kernel(const EwArgs a) 
 
 // ------------------------------------------------------------------- GATE_BWD ----
 __global__ void __launch_bounds__(kEwThreads) gate_bwd_kernel(const EwArgs a) {
+  pdl_prologue();
   const bf16* dout = (const bf16*)a.p[0];
   const bf16* x = (const bf16*)a.p[1];
   const float* psi = (const float*)a.p[2];
@@ -217,7 +221,7 @@ __global__ void __launch_bounds__(kEwThreads) gate_bwd_kernel(const EwArgs a) {
 
 #define EW_LAUNCHER(name, kernel)                                                         \
   int name(const EwArgs& a, dim3 grid, dim3 block, size_t smem, cudaStream_t st) {        \
-    kernel<<<grid, block, smem, st>>>(a);                                                 \
+    B2_CHECK_CUDA(b2_launch(kernel, grid, block, smem, st, a));                                                 \
     B2_CHECK_CUDA(cudaGetLastError());                                                    \
     return B2SEG_OK;                                                                      \
   }

@@ -11,6 +11,7 @@ namespace {
 // ------------------------------------------------------------------ BN_FINALIZE ----
 // grid (C/32, slices), block (32 channels, 32 row lanes): see ew_rows_reduce.
 __global__ void __launch_bounds__(1024) bn_finalize_kernel(const EwArgs a) {
+  pdl_prologue();
   const float* partial = (const float*)a.p[0];
   const float* gamma = (const float*)a.p[1];
   const float* beta = (const float*)a.p[2];
@@ -51,6 +52,7 @@ __global__ void __launch_bounds__(1024) bn_finalize_kernel(const EwArgs a) {
 
 // -------------------------------------------------------------------- BN_APPLY ----
 __global__ void __launch_bounds__(kEwThreads) bn_apply_kernel(const EwArgs a) {
+  pdl_prologue();
   const bf16* y = (const bf16*)a.p[0];
   const float* bnp = (const float*)a.p[1];
   bf16* out = (bf16*)a.p[2];
@@ -94,6 +96,7 @@ struct BnBwdIn {
   const float* bnp;
   long long ld1, ld2, lda, ldy;
   int C;
+  int self_mask;  // ReLU mask recomputed from y: [bf16(y*scale+shift) > 0] (no activation read)
 };
 __device__ __forceinline__ BnBwdIn bn_bwd_in(const EwArgs& a) {
   BnBwdIn s;
@@ -102,6 +105,7 @@ __device__ __forceinline__ BnBwdIn bn_bwd_in(const EwArgs& a) {
   s.bnp = (const float*)a.p[4];
   s.C = (int)a.i[1];
   s.ld1 = a.i[2]; s.ld2 = a.i[3]; s.lda = a.i[4]; s.ldy = a.i[5];
+  s.self_mask = (int)a.i[9];
   return s;
 }
 // dz = (da1 [+ da2]) * [act > 0];  yhat = (y - mean) * invstd
@@ -118,12 +122,21 @@ __device__ __forceinline__ void bn_bwd_load(const BnBwdIn& s, long long p, int c
     for (int j = 0; j < 8; ++j) dz.v[j] = m.v[j] > 0.0f ? dz.v[j] : 0.0f;
   }
   yh = ld_bf8(s.y + p * s.ldy + c0);
+  if (s.self_mask) {  // the forward pass stored bf16(relu(fma(y, scale, shift))): same arithmetic here
+    const F8 sc = ld_f8(s.bnp + c0), sf = ld_f8(s.bnp + s.C + c0);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float act = __bfloat162float(__float2bfloat16_rn(fmaf(yh.v[j], sc.v[j], sf.v[j])));
+      dz.v[j] = act > 0.0f ? dz.v[j] : 0.0f;
+    }
+  }
   const F8 mean = ld_f8(s.bnp + 2 * s.C + c0), inv = ld_f8(s.bnp + 3 * s.C + c0);
 #pragma unroll
   for (int j = 0; j < 8; ++j) yh.v[j] = (yh.v[j] - mean.v[j]) * inv.v[j];
 }
 
 __global__ void __launch_bounds__(kEwThreads) bn_bwd_reduce_kernel(const EwArgs a) {
+  pdl_prologue();
   extern __shared__ float red[];
   const BnBwdIn s = bn_bwd_in(a);
   ew_channel_reduce<2>(0, a.i[0], s.C, (float*)a.p[5], red,
@@ -139,6 +152,7 @@ __global__ void __launch_bounds__(kEwThreads) bn_bwd_reduce_kernel(const EwArgs 
 }
 
 __global__ void __launch_bounds__(1024) bn_bwd_finalize_kernel(const EwArgs a) {
+  pdl_prologue();
   const float* partial = (const float*)a.p[0];
   const float* gamma = (const float*)a.p[1];
   const float* bnp = (const float*)a.p[2];
@@ -166,6 +180,7 @@ __global__ void __launch_bounds__(1024) bn_bwd_finalize_kernel(const EwArgs a) {
 }
 
 __global__ void __launch_bounds__(kEwThreads) bn_bwd_apply_kernel(const EwArgs a) {
+  pdl_prologue();
   const BnBwdIn s = bn_bwd_in(a);
   const float* coef = (const float*)a.p[5];
   bf16* dy = (bf16*)a.p[6];
@@ -198,6 +213,7 @@ __global__ void __launch_bounds__(kEwThreads) bn_bwd_apply_kernel(const EwArgs a
 
 // ---------------------------------------------------------------------- COLSUM ----
 __global__ void __launch_bounds__(kEwThreads) colsum_kernel(const EwArgs a) {
+  pdl_prologue();
   extern __shared__ float red[];
   const bf16* x = (const bf16*)a.p[0];
   const long long ld = a.i[2];
@@ -211,6 +227,7 @@ __global__ void __launch_bounds__(kEwThreads) colsum_kernel(const EwArgs a) {
 
 // out[k] (+)= sum_r partial[r*stride + k]; grid (K/32, slices), block (32 k, 32 row lanes)
 __global__ void __launch_bounds__(1024) colsum_finalize_kernel(const EwArgs a) {
+  pdl_prologue();
   const float* partial = (const float*)a.p[0];
   float* out = (float*)a.p[1];
   const int rows = (int)a.i[0], K = (int)a.i[1];
@@ -227,6 +244,7 @@ __global__ void __launch_bounds__(1024) colsum_finalize_kernel(const EwArgs a) {
 // in the parameter (coalesced), transposed through shared memory and written along b.
 constexpr int kPackT = 9;
 __global__ void __launch_bounds__(kEwThreads) pack_kernel(const EwArgs a) {
+  pdl_prologue();
   __shared__ float sm[kPackT * (32 * 33 + 1)];
   const b2seg_pack_job* jobs = (const b2seg_pack_job*)a.p[0];
   const int njobs = (int)a.i[0];
@@ -260,6 +278,7 @@ __global__ void __launch_bounds__(kEwThreads) pack_kernel(const EwArgs a) {
 }
 
 __global__ void __launch_bounds__(kEwThreads) fill_kernel(const EwArgs a) {
+  pdl_prologue();
   uint32_t* dst = (uint32_t*)a.p[0];
   const long long n = a.i[0] / 4;
   const uint32_t pat = (uint32_t)a.i[1];
@@ -270,7 +289,7 @@ __global__ void __launch_bounds__(kEwThreads) fill_kernel(const EwArgs a) {
 
 #define EW_LAUNCHER(name, kernel)                                                         \
   int name(const EwArgs& a, dim3 grid, dim3 block, size_t smem, cudaStream_t st) {        \
-    kernel<<<grid, block, smem, st>>>(a);                                                 \
+    B2_CHECK_CUDA(b2_launch(kernel, grid, block, smem, st, a));                                                 \
     B2_CHECK_CUDA(cudaGetLastError());                                                    \
     return B2SEG_OK;                                                                      \
   }

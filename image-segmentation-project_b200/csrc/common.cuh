@@ -125,6 +125,22 @@ __device__ __forceinline__ float warp_transpose_sum32(float (&v)[32], int lane) 
   return v[0];
 }
 
+// Programmatic dependent launch: every planned kernel opens with pdl_prologue().  When the launch
+// carries the programmatic-stream-serialization attribute (b2_launch below) the NEXT kernel of the
+// stream may place its CTAs and run its own prologue while this grid is still draining; it then
+// blocks in griddepcontrol.wait until this grid has completed and its writes are visible.  Without
+// the attribute both instructions are no-ops.  Nothing may touch global memory before the wait.
+__device__ __forceinline__ void pdl_trigger() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_wait() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_prologue() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 // Warp-uniform helpers.  The TMA-producer and MMA-issuer warps run CONVERGED (all 32 lanes walk
 // the pipeline loops and poll the mbarriers) and only the single async instruction is predicated
 // on elect.sync: descriptors and coordinates then live in uniform registers.  Guarding a whole
@@ -311,6 +327,28 @@ __device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, float (&v)[32
 }
 
 #endif  // __CUDACC__
+
+#ifdef __CUDACC__
+// ---------------------------------------------------------------------------
+// Host: kernel launch with the PDL attribute (B2SEG_PDL=0 in the environment turns it off).
+// ---------------------------------------------------------------------------
+bool b2_pdl_enabled();
+template <typename... KArgs, typename... Args>
+static inline cudaError_t b2_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                                    cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = b2_pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, args...);
+}
+#endif
 
 // ---------------------------------------------------------------------------
 // Host: TMA descriptor encoding through the driver entry point (no -lcuda).

@@ -48,6 +48,7 @@ struct alignas(64) HaloParams {
 template <int BLOCK_N, bool STATS>
 __global__ void __launch_bounds__(kThreadsH, 1)
     halo3x3_kernel(const __grid_constant__ HaloParams p) {
+  pdl_trigger();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~(uintptr_t)1023);
@@ -89,6 +90,7 @@ __global__ void __launch_bounds__(kThreadsH, 1)
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();  // barriers, TMEM and descriptors are set up; now wait for the producer grid
 
   if (warp == 0) {
     // ===================== TMA producer (converged warp, elected issue) =====================
@@ -338,8 +340,8 @@ struct HaloOp : b2seg_op {
   int run(cudaStream_t st) override {
 #define HALO_LAUNCH(BN)                                                        \
   do {                                                                        \
-    if (p.stats) halo3x3_kernel<BN, true><<<grid, kThreadsH, smem, st>>>(p);  \
-    else halo3x3_kernel<BN, false><<<grid, kThreadsH, smem, st>>>(p);         \
+    if (p.stats) B2_CHECK_CUDA(b2_launch(halo3x3_kernel<BN, true>, grid, dim3(kThreadsH), smem, st, p));  \
+    else B2_CHECK_CUDA(b2_launch(halo3x3_kernel<BN, false>, grid, dim3(kThreadsH), smem, st, p));         \
   } while (0)
     if (block_n == 128) HALO_LAUNCH(128);
     else if (block_n == 64) HALO_LAUNCH(64);

@@ -9,6 +9,7 @@ __device__ __forceinline__ float sigm(float x) { return 1.0f / (1.0f + __expf(-x
 
 // grid (rows, N).  part [N][rows][3][C] = sum, max, argmax (int bits) over this block's pixels.
 __global__ void __launch_bounds__(kEwThreads) se_pool_kernel(const EwArgs a) {
+  pdl_prologue();
   extern __shared__ float red[];  // [3][pl][C]
   const bf16* x = (const bf16*)a.p[0];
   float* part = (float*)a.p[1];
@@ -57,6 +58,7 @@ __global__ void __launch_bounds__(kEwThreads) se_pool_kernel(const EwArgs a) {
 
 // grid N, 256 threads.  saved [N][4][C] = avg, max, gate, argmax(int bits); hidden [N][2][Ch].
 __global__ void __launch_bounds__(kEwThreads) se_mlp_kernel(const EwArgs a) {
+  pdl_prologue();
   extern __shared__ float sm[];  // avg[C], mx[C], hid[2*Ch]
   const float* part = (const float*)a.p[0];
   const float* w1 = (const float*)a.p[1];
@@ -108,6 +110,7 @@ __global__ void __launch_bounds__(kEwThreads) se_mlp_kernel(const EwArgs a) {
 }
 
 __global__ void __launch_bounds__(kEwThreads) se_scale_kernel(const EwArgs a) {
+  pdl_prologue();
   const bf16* x = (const bf16*)a.p[0];
   const float* saved = (const float*)a.p[1];
   bf16* out = (bf16*)a.p[2];
@@ -130,6 +133,7 @@ __global__ void __launch_bounds__(kEwThreads) se_scale_kernel(const EwArgs a) {
 
 // grid (rows, N): part [N][rows][C] = sum_p dout*x
 __global__ void __launch_bounds__(kEwThreads) se_bwd_reduce_kernel(const EwArgs a) {
+  pdl_prologue();
   extern __shared__ float red[];
   const bf16* dout = (const bf16*)a.p[0];
   const bf16* x = (const bf16*)a.p[1];
@@ -151,6 +155,7 @@ __global__ void __launch_bounds__(kEwThreads) se_bwd_reduce_kernel(const EwArgs 
 // (2) grid over the weight elements: dW2[c][h] and dW1[h][c] summed over samples in sample
 // order (deterministic).
 __global__ void __launch_bounds__(kEwThreads) se_mlp_bwd_sample_kernel(const EwArgs a) {
+  pdl_prologue();
   extern __shared__ float sm[];  // ds[C], dha[Ch], dhm[Ch]
   float* part = (float*)a.p[0];
   const float* w1 = (const float*)a.p[1];
@@ -202,6 +207,7 @@ __global__ void __launch_bounds__(kEwThreads) se_mlp_bwd_sample_kernel(const EwA
 }
 
 __global__ void __launch_bounds__(kEwThreads) se_mlp_bwd_weight_kernel(const EwArgs a) {
+  pdl_prologue();
   const float* part = (const float*)a.p[0];
   const float* saved = (const float*)a.p[3];
   const float* hidden = (const float*)a.p[4];
@@ -232,6 +238,7 @@ __global__ void __launch_bounds__(kEwThreads) se_mlp_bwd_weight_kernel(const EwA
 }
 
 __global__ void __launch_bounds__(kEwThreads) se_bwd_apply_kernel(const EwArgs a) {
+  pdl_prologue();
   const bf16* dout = (const bf16*)a.p[0];
   const float* saved = (const float*)a.p[1];
   const float* dpool = (const float*)a.p[2];
@@ -261,7 +268,7 @@ __global__ void __launch_bounds__(kEwThreads) se_bwd_apply_kernel(const EwArgs a
 
 #define EW_LAUNCHER(name, kernel)                                                         \
   int name(const EwArgs& a, dim3 grid, dim3 block, size_t smem, cudaStream_t st) {        \
-    kernel<<<grid, block, smem, st>>>(a);                                                 \
+    B2_CHECK_CUDA(b2_launch(kernel, grid, block, smem, st, a));                                                 \
     B2_CHECK_CUDA(cudaGetLastError());                                                    \
     return B2SEG_OK;                                                                      \
   }
@@ -270,10 +277,10 @@ EW_LAUNCHER(launch_se_mlp, se_mlp_kernel)
 EW_LAUNCHER(launch_se_scale, se_scale_kernel)
 EW_LAUNCHER(launch_se_bwd_reduce, se_bwd_reduce_kernel)
 int launch_se_mlp_bwd(const EwArgs& a, dim3 grid, dim3 block, size_t smem, cudaStream_t st) {
-  se_mlp_bwd_sample_kernel<<<grid, block, smem, st>>>(a);
+  B2_CHECK_CUDA(b2_launch(se_mlp_bwd_sample_kernel, grid, block, smem, st, a));
   B2_CHECK_CUDA(cudaGetLastError());
   const int elems = 2 * (int)a.i[2] * (int)a.i[3];
-  se_mlp_bwd_weight_kernel<<<(elems + kEwThreads - 1) / kEwThreads, kEwThreads, 0, st>>>(a);
+  B2_CHECK_CUDA(b2_launch(se_mlp_bwd_weight_kernel, dim3((elems + kEwThreads - 1) / kEwThreads), dim3(kEwThreads), 0, st, a));
   B2_CHECK_CUDA(cudaGetLastError());
   return B2SEG_OK;
 }

@@ -43,6 +43,7 @@ __device__ __forceinline__ void stem_load_patch(float (*patch)[ST_PWP], const fl
 }
 
 __global__ void __launch_bounds__(256) stem_fwd_kernel(const EwArgs a) {
+  pdl_prologue();
   const float* x = (const float*)a.p[0];
   const float* w = (const float*)a.p[1];
   bf16* y = (bf16*)a.p[2];
@@ -119,6 +120,7 @@ __global__ void __launch_bounds__(256) stem_fwd_kernel(const EwArgs a) {
 
 // dW[c][tap] = sum_pix dy[pix, c] * x[2*oh-3+kh, 2*ow-3+kw]; thread = (16-channel group, tap).
 __global__ void __launch_bounds__(256) stem_wgrad_kernel(const EwArgs a) {
+  pdl_prologue();
   const float* x = (const float*)a.p[0];
   const bf16* dy = (const bf16*)a.p[1];
   float* ws = (float*)a.p[2];
@@ -180,6 +182,7 @@ __global__ void __launch_bounds__(256) stem_wgrad_kernel(const EwArgs a) {
 // ------------------------------------------------------------------ max-pool ----
 // torch max_pool2d semantics: padding never wins, first maximum in (kh, kw) scan order wins.
 __global__ void __launch_bounds__(kEwThreads) maxpool_fwd_kernel(const EwArgs a) {
+  pdl_prologue();
   const bf16* x = (const bf16*)a.p[0];
   bf16* out = (bf16*)a.p[1];
   uint8_t* idx = (uint8_t*)a.p[2];
@@ -222,6 +225,7 @@ __global__ void __launch_bounds__(kEwThreads) maxpool_fwd_kernel(const EwArgs a)
 }
 
 __global__ void __launch_bounds__(kEwThreads) maxpool_bwd_kernel(const EwArgs a) {
+  pdl_prologue();
   const bf16* dout = (const bf16*)a.p[0];
   const uint8_t* idx = (const uint8_t*)a.p[1];
   bf16* dx = (bf16*)a.p[2];
@@ -267,7 +271,7 @@ __global__ void __launch_bounds__(kEwThreads) maxpool_bwd_kernel(const EwArgs a)
 
 #define EW_LAUNCHER(name, kernel)                                                         \
   int name(const EwArgs& a, dim3 grid, dim3 block, size_t smem, cudaStream_t st) {        \
-    kernel<<<grid, block, smem, st>>>(a);                                                 \
+    B2_CHECK_CUDA(b2_launch(kernel, grid, block, smem, st, a));                                                 \
     B2_CHECK_CUDA(cudaGetLastError());                                                    \
     return B2SEG_OK;                                                                      \
   }

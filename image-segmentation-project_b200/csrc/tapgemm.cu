@@ -79,6 +79,7 @@ __device__ __forceinline__ TGItem tg_item(int j, int mtiles) {
 template <int BLOCK_N, int NSTAGES>
 __global__ void __launch_bounds__(kThreadsTG)
     tapgemm_kernel(const __grid_constant__ TapGemmParams p) {
+  pdl_trigger();
   using L = TGSmem<BLOCK_N, NSTAGES>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -113,6 +114,7 @@ __global__ void __launch_bounds__(kThreadsTG)
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();  // barriers, TMEM and descriptors are set up; now wait for the producer grid
 
   if (warp == 0) {
     // ===================== TMA producer (converged warp, elected issue) =====================
@@ -300,7 +302,7 @@ struct TapGemmOp : b2seg_op {
   const char* name() const override { return "tapgemm"; }
   int run(cudaStream_t st) override {
 #define TG_LAUNCH(BN, NS)                                                            \
-  tapgemm_kernel<BN, NS><<<grid, kThreadsTG, TGSmem<BN, NS>::TOTAL, st>>>(p)
+  B2_CHECK_CUDA(b2_launch(tapgemm_kernel<BN, NS>, grid, dim3(kThreadsTG), (size_t)TGSmem<BN, NS>::TOTAL, st, p))
     if (block_n == 128) TG_LAUNCH(128, 3);
     else if (block_n == 64) TG_LAUNCH(64, 4);
     else TG_LAUNCH(32, 4);

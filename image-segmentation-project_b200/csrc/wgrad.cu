@@ -51,6 +51,7 @@ struct WGSmem {
 template <int BLOCK_N, int NSTAGES>
 __global__ void __launch_bounds__(kThreadsWG, 1)
     wgrad_kernel(const __grid_constant__ WgradParams p) {
+  pdl_trigger();
   using L = WGSmem<BLOCK_N, NSTAGES>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -78,6 +79,7 @@ __global__ void __launch_bounds__(kThreadsWG, 1)
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();  // barriers, TMEM and descriptors are set up; now wait for the producer grid
 
   if (warp == 0) {
     {  // converged producer warp, elected issue
@@ -178,6 +180,7 @@ __global__ void __launch_bounds__(kThreadsWG, 1)
 // (channel, tap) -- contiguous in OIHW / IOHW parameter layouts.
 constexpr int kRedI = 4, kRedJ = 16, kRedG = 4;
 __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const __grid_constant__ WgradParams p) {
+  pdl_prologue();
   __shared__ float sm[kRedG][kRedJ][kRedI * B2SEG_MAX_TAPS + 1];
   const int cchunk = blockIdx.x, j0 = blockIdx.y * kRedJ, i0 = blockIdx.z * kRedI;
   const size_t split_stride = (size_t)p.npairs * 128 * p.ncols_pad;
@@ -218,11 +221,11 @@ struct WgradOp : b2seg_op {
   int launches() const override { return 2; }
   int run(cudaStream_t st) override {
     if (block_n == 128)
-      wgrad_kernel<128, 3><<<grid, kThreadsWG, WGSmem<128, 3>::TOTAL, st>>>(p);
+      B2_CHECK_CUDA(b2_launch(wgrad_kernel<128, 3>, grid, dim3(kThreadsWG), (size_t)WGSmem<128, 3>::TOTAL, st, p));
     else
-      wgrad_kernel<64, 4><<<grid, kThreadsWG, WGSmem<64, 4>::TOTAL, st>>>(p);
+      B2_CHECK_CUDA(b2_launch(wgrad_kernel<64, 4>, grid, dim3(kThreadsWG), (size_t)WGSmem<64, 4>::TOTAL, st, p));
     B2_CHECK_CUDA(cudaGetLastError());
-    wgrad_reduce_kernel<<<reduce_grid, 256, 0, st>>>(p);
+    B2_CHECK_CUDA(b2_launch(wgrad_reduce_kernel, reduce_grid, dim3(256), 0, st, p));
     B2_CHECK_CUDA(cudaGetLastError());
     return B2SEG_OK;
   }

@@ -275,7 +275,9 @@ enum {
   /* BatchNorm backward phase 1: dz = (da1 [+ da2]) * [a > 0]; block partials of (dz, dz*yhat).
    * p0 da1 bf16  p1 da2 bf16|NULL  p2 a bf16|NULL (ReLU mask source)  p3 y bf16 (pre-BN)  p4 bnp
    * p5 out partial f32 [rows][2][C], rows = b2seg_ew_partial_rows(kind, P, C)
-   * i0 P  i1 C  i2 ld_da1  i3 ld_da2  i4 ld_a  i5 ld_y */
+   * i0 P  i1 C  i2 ld_da1  i3 ld_da2  i4 ld_a  i5 ld_y
+   * i9 self-mask: with p2 NULL, the ReLU mask is recomputed as [bf16(y*scale+shift) > 0] from y
+   *    and bnp (the activation of a plain conv-BN-ReLU is never re-read) */
   B2SEG_EW_BN_BWD_REDUCE = 3,
   /* p0 partial  p1 gamma|NULL  p2 bnp  p3 dgamma f32|NULL  p4 dbeta f32|NULL  p5 out coef f32 [3][C]
    * p6 dbias f32|NULL (gradient of a conv bias feeding this BN: 0 with batch statistics)
@@ -283,7 +285,7 @@ enum {
   B2SEG_EW_BN_BWD_FINALIZE = 4,
   /* phase 2: dy = c1*(dz - c2 - yhat*c3) -> bf16; optionally also emits dz (residual branch).
    * p0..p4 as BN_BWD_REDUCE  p5 coef  p6 dy bf16  p7 dz bf16|NULL
-   * i0..i5 as BN_BWD_REDUCE  i6 ld_dy  i7 ld_dz  i8 dz mode (1 store, 2 accumulate) */
+   * i0..i5 as BN_BWD_REDUCE  i6 ld_dy  i7 ld_dz  i8 dz mode (1 store, 2 accumulate)  i9 self-mask */
   B2SEG_EW_BN_BWD_APPLY = 5,
   /* MaxPool2d(3, stride 2, pad 1) (advanced_models.py:83,272) + argmax byte (kh*3+kw) per element.
    * p0 x bf16 [N,H,W,C]  p1 out bf16 [N,H/2,W/2,C]  p2 idx u8 [N,H/2,W/2,C]
