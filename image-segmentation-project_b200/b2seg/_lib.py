@@ -118,6 +118,7 @@ _SIGS = {
     "b2seg_seq_append": (C.c_int, [_vp, _vp]),
     "b2seg_seq_run": (C.c_int, [_vp, _vp]),
     "b2seg_seq_launches": (C.c_int, [_vp]),
+    "b2seg_seq_is_graph": (C.c_int, [_vp]),
     "b2seg_seq_run_timed": (C.c_int, [_vp, _vp, C.POINTER(C.c_float), _i]),
     "b2seg_seq_destroy": (C.c_int, [_vp]),
     "b2seg_tapgemm_create": (C.c_int, [C.POINTER(TapGemmDesc), C.POINTER(_vp)]),

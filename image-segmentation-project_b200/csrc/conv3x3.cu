@@ -18,6 +18,7 @@
 // Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM alloc + MMA issuer,
 // warps 2..9 = epilogue.
 #include <new>
+#include <stdlib.h>
 #include <string.h>
 
 #include "ops.cuh"
@@ -27,6 +28,7 @@ namespace {
 constexpr int kThreadsH = 320;
 constexpr int kMaxAStages = 8;
 constexpr int kMaxBSlots = 18;
+constexpr int kAcc = 2;  // TMEM accumulator stages (4 measured no faster; 2 leaves TMEM for a PDL-overlapped successor)
 
 struct alignas(64) HaloParams {
   CUtensorMap tmA;  // box (64 ch, wt+2, ht+2, 1)
@@ -42,6 +44,7 @@ struct alignas(64) HaloParams {
   float* stats;
   int accumulate;
   int resident, a_stages, b_slots, stat_rows;
+  int probe;  // B2SEG_PROBE bits (perf experiments only): 1 no output stores, 2 no stats, 4 no MMAs, 8 issue every chunk's MMAs 3x
   int a_stage_bytes, b_off, bar_off, stat_off;
 };
 
@@ -57,9 +60,9 @@ __global__ void __launch_bounds__(kThreadsH, 1)
   uint64_t* a_empty = a_full + kMaxAStages;
   uint64_t* b_full = a_empty + kMaxAStages;
   uint64_t* b_empty = b_full + kMaxBSlots;
-  uint64_t* tmem_full = b_empty + kMaxBSlots;  // [2]
-  uint64_t* tmem_empty = tmem_full + 2;        // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  uint64_t* tmem_full = b_empty + kMaxBSlots;  // [kAcc]
+  uint64_t* tmem_empty = tmem_full + kAcc;     // [kAcc]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + kAcc);
 
   const int warp = warp_id_uniform(), lane = threadIdx.x & 31;
   // this CTA keeps one column tile (its weights may be resident) and strides over pixel tiles
@@ -77,7 +80,7 @@ __global__ void __launch_bounds__(kThreadsH, 1)
       mbar_init(&b_full[i], 1);
       mbar_init(&b_empty[i], 1);
     }
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < kAcc; ++i) {
       mbar_init(&tmem_full[i], 1);
       mbar_init(&tmem_empty[i], 8);  // one arrive per epilogue warp
     }
@@ -85,7 +88,7 @@ __global__ void __launch_bounds__(kThreadsH, 1)
     tma_prefetch_desc(&p.tmA);
     tma_prefetch_desc(&p.tmB);
   }
-  if (warp == 1) tmem_alloc<2 * BLOCK_N>(tmem_slot);
+  if (warp == 1) tmem_alloc<kAcc * BLOCK_N>(tmem_slot);
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
@@ -104,8 +107,12 @@ __global__ void __launch_bounds__(kThreadsH, 1)
         for (int kc = 0; kc < p.kchunks; ++kc) {
           mbar_wait(&a_empty[s], ph);
           if (elect_one_sync()) {
-            mbar_expect_tx(&a_full[s], halo_bytes);
-            tma_load_4d(smem + s * p.a_stage_bytes, &p.tmA, &a_full[s], kc * 64, w0, h0, n0);
+            if ((p.probe & 16) && !first) {
+              mbar_arrive(&a_full[s]);  // probe: no A traffic after the first tile
+            } else {
+              mbar_expect_tx(&a_full[s], halo_bytes);
+              tma_load_4d(smem + s * p.a_stage_bytes, &p.tmA, &a_full[s], kc * 64, w0, h0, n0);
+            }
           }
           __syncwarp();
           if (++s == (uint32_t)p.a_stages) { s = 0; ph ^= 1u; }
@@ -148,7 +155,7 @@ __global__ void __launch_bounds__(kThreadsH, 1)
       const uint64_t bdesc0 = umma_smem_desc(smem_u32(smem + p.b_off), 16, 1024);
       uint32_t s = 0, ph = 0, bs = 0, bph = 0, tile = 0;
       for (int mt = mt0; mt < p.mtiles; mt += mstep, ++tile) {
-        const uint32_t acc = tile & 1u, aph = (tile >> 1) & 1u;
+        const uint32_t acc = tile % kAcc, aph = (tile / kAcc) & 1u;
         mbar_wait(&tmem_empty[acc], aph ^ 1u);
         tcgen05_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
@@ -161,8 +168,19 @@ __global__ void __launch_bounds__(kThreadsH, 1)
             // steady state: weights are resident, the whole chunk (9 taps x 4 MMAs) is one issue block
             const uint64_t bd_k = bdesc0 + (uint64_t)((uint32_t)kc * 9u * BSLAB16);
             if (elect_one_sync()) {
+              for (int rep = (p.probe & 8) ? 2 : 0; rep > 0; --rep) {  // probe: extra MMA passes
+#pragma unroll
+                for (int t = 0; t < 9; ++t) {
+                  const uint64_t ad = ad_s + (uint64_t)toff16[t];
+                  const uint64_t bd = bd_k + (uint64_t)(t * BSLAB16);
+#pragma unroll
+                  for (int k = 0; k < 4; ++k)
+                    umma_bf16_ss(tmem_d, ad + (uint64_t)(2 * k), bd + (uint64_t)(2 * k), idesc, 1u);
+                }
+              }
 #pragma unroll
               for (int t = 0; t < 9; ++t) {
+                if (p.probe & 4) break;
                 const uint64_t ad = ad_s + (uint64_t)toff16[t];
                 const uint64_t bd = bd_k + (uint64_t)(t * BSLAB16);
 #pragma unroll
@@ -231,7 +249,7 @@ __global__ void __launch_bounds__(kThreadsH, 1)
       const int phh = th * p.ht + lh, pw = tw * p.wt + lw;
       const bool row_ok = phh < p.oh && pw < p.ow;
       const long long row_off = (long long)pn * p.osn + (long long)phh * p.osh + (long long)pw * p.osw;
-      const uint32_t acc = tile & 1u, aph = (tile >> 1) & 1u;
+      const uint32_t acc = tile % kAcc, aph = (tile / kAcc) & 1u;
       // accumulate mode: fetch the old output values BEFORE waiting for the accumulator, so
       // their (uncoalesced, one pixel row per lane) latency hides behind the MMAs
       uint4 old[MYCH][4];
@@ -268,7 +286,7 @@ __global__ void __launch_bounds__(kThreadsH, 1)
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + colc + j);
           }
-          if (row_ok) {
+          if (row_ok && !(p.probe & 1)) {
             bf16* dst = p.out + row_off + colc;
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
@@ -289,7 +307,9 @@ __global__ void __launch_bounds__(kThreadsH, 1)
               pk.w = f2_to_bf2(o[6], o[7]);
               *reinterpret_cast<uint4*>(dst + g * 8) = pk;
             }
-            if (STATS) {
+          }
+          if (row_ok) {
+            if (STATS && !(p.probe & 2)) {
 #pragma unroll
               for (int j = 0; j < 32; ++j) {
                 s1[ci][j] += v[j];
@@ -327,7 +347,7 @@ __global__ void __launch_bounds__(kThreadsH, 1)
   __syncthreads();
   if (warp == 1) {
     tcgen05_fence_after();
-    tmem_dealloc<2 * BLOCK_N>(tmem_base);
+    tmem_dealloc<kAcc * BLOCK_N>(tmem_base);
   }
 }
 
@@ -393,7 +413,7 @@ int b2_halo3x3_try_create(const b2seg_tapgemm_desc* d, b2seg_op** out) {
   const int nm = d->ngemm;
   const int kchunks = (d->cin + 63) / 64;
   const int a_stage = ((wt + 2) * (ht + 2) * 128 + 1023) / 1024 * 1024;
-  const int bar_bytes = (2 * kMaxAStages + 2 * kMaxBSlots + 4) * 8 + 16;
+  const int bar_bytes = (2 * kMaxAStages + 2 * kMaxBSlots + 2 * kAcc) * 8 + 16;
   // choose BLOCK_N and the weight mode
   int bn = 0, resident = 0, a_stages = 0, b_slots = 0;
   const int cands[3] = {128, 64, 32};
@@ -461,6 +481,12 @@ int b2_halo3x3_try_create(const b2seg_tapgemm_desc* d, b2seg_op** out) {
   p.accumulate = d->accumulate;
   p.stat_rows = b2seg_tapgemm_stat_rows(d->on, d->oh, d->ow);
   p.resident = resident; p.a_stages = a_stages; p.b_slots = b_slots;
+  {
+    const char* e = getenv("B2SEG_PROBE");
+    p.probe = e ? atoi(e) : 0;
+    const char* st = getenv("B2SEG_ASTAGES");
+    if (st && atoi(st) >= 1 && atoi(st) <= p.a_stages) p.a_stages = atoi(st);
+  }
   p.a_stage_bytes = a_stage;
   p.b_off = a_stages * a_stage;
   p.bar_off = p.b_off + b_slots * bn * 128;

@@ -16,6 +16,12 @@ struct b2seg_op {
 
 struct b2seg_seq {
   std::vector<b2seg_op*> ops;
+  // CUDA-graph replay: the op list is captured once on a private stream (PyTorch's default stream
+  // is the legacy stream, which cannot be captured) and launched into the caller's stream.
+  cudaGraphExec_t exec = nullptr;
+  cudaGraph_t graph = nullptr;
+  cudaStream_t capture_stream = nullptr;
+  bool capture_failed = false;
 };
 
 // NHWC bf16 view -> rank-4 TMA descriptor with box (64ch, wt, ht, nt), 128B swizzle.

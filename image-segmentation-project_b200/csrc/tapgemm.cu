@@ -475,14 +475,64 @@ extern "C" int b2seg_seq_append(b2seg_seq* seq, b2seg_op* op) {
   seq->ops.push_back(op);
   return B2SEG_OK;
 }
+namespace {
+bool graphs_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B2SEG_GRAPH");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v != 0;
+}
+// Capture the op list into an executable graph.  Any failure (e.g. a driver that cannot capture
+// programmatic-dependent launches) leaves the sequence on the direct-launch path.
+void seq_try_capture(b2seg_seq* seq) {
+  seq->capture_failed = true;  // cleared on success
+  if (cudaStreamCreateWithFlags(&seq->capture_stream, cudaStreamNonBlocking) != cudaSuccess) return;
+  if (cudaStreamBeginCapture(seq->capture_stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+    cudaGetLastError();
+    return;
+  }
+  int rc = B2SEG_OK;
+  for (b2seg_op* op : seq->ops) {
+    rc = op->run(seq->capture_stream);
+    if (rc != B2SEG_OK) break;
+  }
+  cudaGraph_t g = nullptr;
+  cudaError_t e = cudaStreamEndCapture(seq->capture_stream, &g);
+  if (rc != B2SEG_OK || e != cudaSuccess || !g) {
+    if (g) cudaGraphDestroy(g);
+    cudaGetLastError();
+    return;
+  }
+  cudaGraphExec_t ex = nullptr;
+  if (cudaGraphInstantiate(&ex, g, 0) != cudaSuccess) {
+    cudaGraphDestroy(g);
+    cudaGetLastError();
+    return;
+  }
+  seq->graph = g;
+  seq->exec = ex;
+  seq->capture_failed = false;
+}
+}  // namespace
+
 extern "C" int b2seg_seq_run(b2seg_seq* seq, void* stream) {
   B2_REQUIRE(seq, "seq_run: null");
+  if (graphs_enabled() && seq->ops.size() >= 4) {
+    if (!seq->exec && !seq->capture_failed) seq_try_capture(seq);
+    if (seq->exec) {
+      B2_CHECK_CUDA(cudaGraphLaunch(seq->exec, (cudaStream_t)stream));
+      return B2SEG_OK;
+    }
+  }
   for (b2seg_op* op : seq->ops) {
     int rc = op->run((cudaStream_t)stream);
     if (rc != B2SEG_OK) return rc;
   }
   return B2SEG_OK;
 }
+extern "C" int b2seg_seq_is_graph(const b2seg_seq* seq) { return seq && seq->exec ? 1 : 0; }
 extern "C" int b2seg_seq_run_timed(b2seg_seq* seq, void* stream, float* ms, int n_ops) {
   B2_REQUIRE(seq && ms, "seq_run_timed: null");
   B2_REQUIRE(n_ops == (int)seq->ops.size(), "seq_run_timed: n_ops %d != %d", n_ops,
@@ -510,6 +560,11 @@ extern "C" int b2seg_seq_launches(const b2seg_seq* seq) {
   return n;
 }
 extern "C" int b2seg_seq_destroy(b2seg_seq* seq) {
+  if (seq) {
+    if (seq->exec) cudaGraphExecDestroy(seq->exec);
+    if (seq->graph) cudaGraphDestroy(seq->graph);
+    if (seq->capture_stream) cudaStreamDestroy(seq->capture_stream);
+  }
   delete seq;
   return B2SEG_OK;
 }

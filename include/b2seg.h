@@ -157,7 +157,10 @@ int b2seg_op_destroy(b2seg_op* op);
 int b2seg_op_launches(const b2seg_op* op);
 int b2seg_seq_create(b2seg_seq** out);
 int b2seg_seq_append(b2seg_seq* seq, b2seg_op* op); /* does not take ownership */
+/* Replays the ops in order.  Sequences of >= 4 ops are captured into a CUDA graph on first use
+ * (one graph launch per replay; B2SEG_GRAPH=0 in the environment keeps direct launches). */
 int b2seg_seq_run(b2seg_seq* seq, void* stream);
+int b2seg_seq_is_graph(const b2seg_seq* seq); /* 1 once the sequence replays as a CUDA graph */
 int b2seg_seq_launches(const b2seg_seq* seq);
 /* Replays the sequence with a CUDA event pair around every op, synchronises the stream and
  * writes each op's elapsed milliseconds to ms_per_op[0..n_ops) (profiling aid for bench.py's
