@@ -7,10 +7,12 @@
 // fixed-point scheme (coordinates in 1/32 px, 15-bit bilinear weights, constant
 // / reflect / reflect101 borders).
 //
-// One CTA produces a 32x32 destination tile.  It first computes the source
-// footprint of the tile, stages that footprint (with the border rule already
-// applied) in shared memory with coalesced loads, and then gathers from shared
-// memory.  Footprints that do not fit fall back to direct global gathers.
+// Warps: one CTA produces a 32x32 destination tile of several planes.  It computes the
+// source footprint of the tile, stages it (border rule already applied) in shared memory
+// with coalesced 32-bit loads and gathers from shared memory; each thread emits 4 adjacent
+// pixels as one 32-bit store.  Footprints that do not fit fall back to direct global gathers.
+// Permutations: 16-byte chunk moves (flips) and register/shared-memory 64x64 byte-tile
+// transposes (rot90 / transpose); odd sizes take the scalar tile kernel.
 #include "common.cuh"
 
 namespace {
@@ -69,6 +71,68 @@ __global__ void __launch_bounds__(256)
     const int di = di0 + r, dj = dj0 + tx;
     if (di < dh && dj < dw) d[(size_t)di * dw + dj] = tile[tx][r];
   }
+}
+
+// ---- vectorised permutations (the common case: 16-byte aligned planes, sides % 64 == 0) -----
+__device__ __forceinline__ uint32_t brev4(uint32_t v) { return __byte_perm(v, 0, 0x0123); }
+__device__ __forceinline__ uint4 rev16(uint4 v) {
+  return make_uint4(brev4(v.w), brev4(v.z), brev4(v.y), brev4(v.x));
+}
+
+// Flips move whole 16-byte chunks: vflip copies chunk (i, q) from row h-1-i, hflip / rot180 read
+// the mirrored chunk and reverse its bytes in registers.  Pure streaming: 16 B in, 16 B out.
+template <typename IDX>
+__global__ void __launch_bounds__(256)
+    flip16_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, int h, int wq, long long total_,
+                  int mode /*0 h, 1 v, 2 rot180*/) {
+  const IDX total = (IDX)total_, stride = (IDX)gridDim.x * 256;
+  const IDX uwq = (IDX)wq, uh = (IDX)h;
+  for (IDX idx = (IDX)blockIdx.x * 256 + threadIdx.x; idx < total; idx += stride) {
+    const IDX row = idx / uwq, q = idx - row * uwq;
+    const IDX plane = row / uh, i = row - plane * uh;
+    const IDX si = mode == 0 ? i : uh - 1 - i;
+    const IDX sq = mode == 1 ? q : uwq - 1 - q;
+    uint4 v = __ldcs(src + ((size_t)plane * uh + si) * uwq + sq);
+    if (mode != 1) v = rev16(v);
+    __stcs(dst + idx, v);
+  }
+}
+
+// Transposing family on 64x64 byte tiles.  Each thread loads a 4x4 byte block (four coalesced
+// 32-bit loads), transposes it in registers (8 PRMT) and parks it in shared memory as words of
+// the transposed tile; the tile is then written as 16-byte chunks of destination rows.
+//   transpose : dst(i,j) = src(j,i)
+//   rot90 k=1 : dst(i,j) = src(j, w-1-i)   -> rows of the transposed tile land in reverse order
+//   rot90 k=3 : dst(i,j) = src(h-1-j, i)   -> each row of the transposed tile is byte-reversed
+__global__ void __launch_bounds__(256)
+    transpose64_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int h, int w,
+                       int mode /*3 rot90 k=1, 4 rot90 k=3, 5 transpose*/) {
+  __shared__ uint32_t T[64][17];
+  const int t = threadIdx.x;
+  const size_t plane_off = (size_t)blockIdx.z * h * w;
+  const int r0 = blockIdx.y * 64, c0 = blockIdx.x * 64;  // source tile origin
+  {
+    const int l = t & 15, g = t >> 4;
+    const uint8_t* s = src + plane_off + (size_t)(r0 + 4 * g) * w + c0 + 4 * l;
+    const uint32_t a0 = __ldcs(reinterpret_cast<const uint32_t*>(s));
+    const uint32_t a1 = __ldcs(reinterpret_cast<const uint32_t*>(s + w));
+    const uint32_t a2 = __ldcs(reinterpret_cast<const uint32_t*>(s + 2 * (size_t)w));
+    const uint32_t a3 = __ldcs(reinterpret_cast<const uint32_t*>(s + 3 * (size_t)w));
+    const uint32_t t0 = __byte_perm(a0, a1, 0x5140), t1 = __byte_perm(a2, a3, 0x5140);
+    const uint32_t t2 = __byte_perm(a0, a1, 0x7362), t3 = __byte_perm(a2, a3, 0x7362);
+    T[4 * l + 0][g] = __byte_perm(t0, t1, 0x5410);  // source column 4l+0, rows 4g..4g+3
+    T[4 * l + 1][g] = __byte_perm(t0, t1, 0x7632);
+    T[4 * l + 2][g] = __byte_perm(t2, t3, 0x5410);
+    T[4 * l + 3][g] = __byte_perm(t2, t3, 0x7632);
+  }
+  __syncthreads();
+  const int c = t >> 2, q = t & 3;  // transposed-tile row (= source column), 16-byte quarter
+  uint4 v = make_uint4(T[c][4 * q], T[c][4 * q + 1], T[c][4 * q + 2], T[c][4 * q + 3]);
+  size_t drow, dcol;  // destination is [w][h]
+  if (mode == 5) { drow = c0 + c; dcol = r0 + 16 * q; }
+  else if (mode == 3) { drow = w - 1 - (c0 + c); dcol = r0 + 16 * q; }
+  else { drow = c0 + c; dcol = h - r0 - 16 * q - 16; v = rev16(v); }
+  __stcs(reinterpret_cast<uint4*>(dst + plane_off + drow * h + dcol), v);
 }
 
 // ---- cv2 border rule (borderInterpolate) ------------------------------------------
@@ -143,95 +207,196 @@ __device__ __forceinline__ int fetch_global(const uint8_t* s, int h, int w, int 
   return s[(size_t)yy * w + xx];
 }
 
+// Affine coordinates of pixel (x,y) from the per-tile integer tables (exactly the values
+// src_coord computes: ad/bd depend only on x, X0/Y0 only on y).
+__device__ __forceinline__ void affine_from_tables(int interp, int adx, int bdx, int X0y, int Y0y,
+                                                   int& sx, int& sy, int& fx, int& fy) {
+  if (interp == B2SEG_INTERP_NEAREST) {
+    sx = (X0y + adx) >> 10;
+    sy = (Y0y + bdx) >> 10;
+    fx = fy = 0;
+  } else {
+    const int X = (X0y + adx) >> 5, Y = (Y0y + bdx) >> 5;
+    sx = X >> 5;
+    sy = Y >> 5;
+    fx = X & 31;
+    fy = Y & 31;
+  }
+  sx = max(-32768, min(32767, sx));
+  sy = max(-32768, min(32767, sy));
+}
+
+constexpr int FPITCH = FOOT + 8;  // bytes; multiple of 4 so footprint rows take 32-bit stores
+
+// One CTA = one 32x32 destination tile of `pz` consecutive planes (all planes of a call share the
+// transform, so source coordinates are computed once and kept in registers).  Thread = 4
+// horizontally adjacent pixels -> one 32-bit store.  Affine coordinates come from four 32-entry
+// integer tables (the double-precision products are evaluated once per tile row / column, not per
+// pixel); the source footprint of an affine tile is the bounding box of its four corners.
 __global__ void __launch_bounds__(256)
-    warp_u8_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, WarpArgs a) {
-  __shared__ uint8_t foot[FOOT][FOOT + 4];
+    warp_u8_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, WarpArgs a,
+                   int planes, int pz, int vec_ok) {
+  __shared__ __align__(16) uint8_t foot[FOOT][FPITCH];
+  __shared__ int s_ad[TILE], s_bd[TILE], s_X0[TILE], s_Y0[TILE];
   __shared__ int s_box[4];
   const int h = a.h, w = a.w;
-  const uint8_t* s = src + (size_t)blockIdx.z * h * w;
-  uint8_t* d = dst + (size_t)blockIdx.z * h * w;
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int x = blockIdx.x * TILE + tx;
+  const int tid = threadIdx.x;
+  const int x0 = blockIdx.x * TILE, y0 = blockIdx.y * TILE;
+  const int r = tid >> 3, xg = (tid & 7) * 4;
+  const int y = y0 + r, x = x0 + xg;
   const bool lin = a.interp == B2SEG_INTERP_LINEAR;
+  const bool affine = a.map_x == nullptr;
 
   int sx[4], sy[4], fx[4], fy[4];
-  int mnx = INT_MAX, mny = INT_MAX, mxx = INT_MIN, mxy = INT_MIN;
-#pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    const int y = blockIdx.y * TILE + ty + 8 * k;
-    if (x < w && y < h) {
-      src_coord(a, x, y, sx[k], sy[k], fx[k], fy[k]);
-      if (a.border == B2SEG_BORDER_CONSTANT) {
-        // anything at or beyond one pixel outside reads only the constant
-        sx[k] = max(-2, min(w, sx[k]));
-        sy[k] = max(-2, min(h, sy[k]));
-      }
-      mnx = min(mnx, sx[k]); mxx = max(mxx, sx[k]);
-      mny = min(mny, sy[k]); mxy = max(mxy, sy[k]);
-    }
-  }
-  // block-wide footprint
-  if (threadIdx.x == 0) { s_box[0] = INT_MAX; s_box[1] = INT_MAX; s_box[2] = INT_MIN; s_box[3] = INT_MIN; }
-  __syncthreads();
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    mnx = min(mnx, __shfl_xor_sync(0xffffffffu, mnx, o));
-    mny = min(mny, __shfl_xor_sync(0xffffffffu, mny, o));
-    mxx = max(mxx, __shfl_xor_sync(0xffffffffu, mxx, o));
-    mxy = max(mxy, __shfl_xor_sync(0xffffffffu, mxy, o));
-  }
-  if (tx == 0) {
-    atomicMin(&s_box[0], mnx); atomicMin(&s_box[1], mny);
-    atomicMax(&s_box[2], mxx); atomicMax(&s_box[3], mxy);
-  }
-  __syncthreads();
-  const int bx0 = s_box[0], by0 = s_box[1];
-  const int bw = s_box[2] - bx0 + (lin ? 2 : 1), bh = s_box[3] - by0 + (lin ? 2 : 1);
-  const bool staged = s_box[0] != INT_MAX && bw <= FOOT && bh <= FOOT && bw > 0 && bh > 0;
-
-  if (staged) {
-    // coalesced footprint load with the border rule applied once per source pixel
-    for (int r = ty; r < bh; r += 8) {
-      const int yy = border_index(by0 + r, h, a.border);
-      for (int c = tx; c < bw; c += 32) {
-        const int xx = border_index(bx0 + c, w, a.border);
-        foot[r][c] = (xx < 0 || yy < 0) ? (uint8_t)a.cval : s[(size_t)yy * w + xx];
-      }
+  int bx0, by0, bx1, by1;  // inclusive box of the integer source coordinates
+  if (affine) {
+    if (tid < TILE) {
+      const double xd = (double)(x0 + tid);
+      s_ad[tid] = __double2int_rn(__dmul_rn(__dmul_rn(a.m[0], xd), 1024.0));
+      s_bd[tid] = __double2int_rn(__dmul_rn(__dmul_rn(a.m[3], xd), 1024.0));
+    } else if (tid < 2 * TILE) {
+      const double yd = (double)(y0 + tid - TILE);
+      const int round_delta = a.interp == B2SEG_INTERP_NEAREST ? 512 : 16;
+      s_X0[tid - TILE] =
+          __double2int_rn(__dmul_rn(__dadd_rn(__dmul_rn(a.m[1], yd), a.m[2]), 1024.0)) + round_delta;
+      s_Y0[tid - TILE] =
+          __double2int_rn(__dmul_rn(__dadd_rn(__dmul_rn(a.m[4], yd), a.m[5]), 1024.0)) + round_delta;
     }
     __syncthreads();
-  }
 #pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    const int y = blockIdx.y * TILE + ty + 8 * k;
-    if (x >= w || y >= h) continue;
-    int v00, v01 = 0, v10 = 0, v11 = 0;
-    if (staged) {
-      const int lx = sx[k] - bx0, ly = sy[k] - by0;
-      v00 = foot[ly][lx];
-      if (lin) { v01 = foot[ly][lx + 1]; v10 = foot[ly + 1][lx]; v11 = foot[ly + 1][lx + 1]; }
-    } else {
-      v00 = fetch_global(s, h, w, sx[k], sy[k], a.border, a.cval);
-      if (lin) {
-        v01 = fetch_global(s, h, w, sx[k] + 1, sy[k], a.border, a.cval);
-        v10 = fetch_global(s, h, w, sx[k], sy[k] + 1, a.border, a.cval);
-        v11 = fetch_global(s, h, w, sx[k] + 1, sy[k] + 1, a.border, a.cval);
+    for (int e = 0; e < 4; ++e)
+      affine_from_tables(a.interp, s_ad[xg + e], s_bd[xg + e], s_X0[r], s_Y0[r], sx[e], sy[e], fx[e], fy[e]);
+    // corners of the valid part of the tile bound every pixel's coordinate (monotone in x and y)
+    const int cx1 = min(TILE - 1, w - 1 - x0), cy1 = min(TILE - 1, h - 1 - y0);
+    bx0 = by0 = INT_MAX; bx1 = by1 = INT_MIN;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const int cx = (c & 1) ? cx1 : 0, cy = (c & 2) ? cy1 : 0;
+      int qx, qy, q0, q1;
+      affine_from_tables(a.interp, s_ad[cx], s_bd[cx], s_X0[cy], s_Y0[cy], qx, qy, q0, q1);
+      bx0 = min(bx0, qx); bx1 = max(bx1, qx);
+      by0 = min(by0, qy); by1 = max(by1, qy);
+    }
+  } else {
+    int mnx = INT_MAX, mny = INT_MAX, mxx = INT_MIN, mxy = INT_MIN;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      if (x + e < w && y < h) {
+        src_coord(a, x + e, y, sx[e], sy[e], fx[e], fy[e]);
+        mnx = min(mnx, sx[e]); mxx = max(mxx, sx[e]);
+        mny = min(mny, sy[e]); mxy = max(mxy, sy[e]);
+      } else {
+        sx[e] = sy[e] = fx[e] = fy[e] = 0;
       }
     }
-    int out = v00;
-    if (lin) {
-      // cv2 BilinearTab_i: (32-fy)(32-fx)*32 etc., sum 32768; FixedPtCast<15>
-      const int w00 = (32 - fy[k]) * (32 - fx[k]) * 32, w01 = (32 - fy[k]) * fx[k] * 32;
-      const int w10 = fy[k] * (32 - fx[k]) * 32, w11 = fy[k] * fx[k] * 32;
-      out = (v00 * w00 + v01 * w01 + v10 * w10 + v11 * w11 + (1 << 14)) >> 15;
-      out = max(0, min(255, out));
+    if (tid == 0) { s_box[0] = INT_MAX; s_box[1] = INT_MAX; s_box[2] = INT_MIN; s_box[3] = INT_MIN; }
+    __syncthreads();
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      mnx = min(mnx, __shfl_xor_sync(0xffffffffu, mnx, o));
+      mny = min(mny, __shfl_xor_sync(0xffffffffu, mny, o));
+      mxx = max(mxx, __shfl_xor_sync(0xffffffffu, mxx, o));
+      mxy = max(mxy, __shfl_xor_sync(0xffffffffu, mxy, o));
     }
-    d[(size_t)y * w + x] = (uint8_t)out;
+    if ((tid & 31) == 0) {
+      atomicMin(&s_box[0], mnx); atomicMin(&s_box[1], mny);
+      atomicMax(&s_box[2], mxx); atomicMax(&s_box[3], mxy);
+    }
+    __syncthreads();
+    bx0 = s_box[0]; by0 = s_box[1]; bx1 = s_box[2]; by1 = s_box[3];
+  }
+  if (a.border == B2SEG_BORDER_CONSTANT) {
+    // anything at or beyond one pixel outside the image reads only the constant
+    bx0 = max(-2, min(w, bx0)); bx1 = max(-2, min(w, bx1));
+    by0 = max(-2, min(h, by0)); by1 = max(-2, min(h, by1));
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      sx[e] = max(-2, min(w, sx[e]));
+      sy[e] = max(-2, min(h, sy[e]));
+    }
+  }
+  const int bxa = bx0 & ~3;  // footprint columns start on a 4-byte boundary of the source row
+  const int bw = bx1 + (lin ? 1 : 0) - bxa + 1, bh = by1 + (lin ? 1 : 0) - by0 + 1;
+  const int bwords = (bw + 3) >> 2;
+  const bool staged = bx0 != INT_MAX && bw > 0 && bh > 0 && bwords * 4 <= FPITCH && bh <= FOOT;
+  const bool valid_row = y < h;
+
+  const int p_begin = blockIdx.z * pz, p_end = min(planes, p_begin + pz);
+  for (int plane = p_begin; plane < p_end; ++plane) {
+    const uint8_t* s = src + (size_t)plane * h * w;
+    uint8_t* d = dst + (size_t)plane * h * w;
+    if (staged) {
+      if (plane != p_begin) __syncthreads();  // previous plane's gathers are done
+      // coalesced footprint load, border rule applied once per source byte
+      for (int idx = tid; idx < bh * bwords; idx += 256) {
+        const int fr = idx / bwords, fc = idx - fr * bwords;
+        const int gy = by0 + fr, gx = bxa + 4 * fc;
+        uint32_t word;
+        if (vec_ok && (unsigned)gy < (unsigned)h && gx >= 0 && gx + 3 < w) {
+          word = __ldg(reinterpret_cast<const uint32_t*>(s + (size_t)gy * w + gx));
+        } else {
+          const int yy = border_index(gy, h, a.border);
+          word = 0;
+#pragma unroll
+          for (int b = 0; b < 4; ++b) {
+            const int xx = border_index(gx + b, w, a.border);
+            const uint32_t v = (xx < 0 || yy < 0) ? (uint32_t)a.cval : (uint32_t)s[(size_t)yy * w + xx];
+            word |= v << (8 * b);
+          }
+        }
+        reinterpret_cast<uint32_t*>(&foot[fr][0])[fc] = word;
+      }
+      __syncthreads();
+    }
+    if (!valid_row) continue;
+    uint32_t packed = 0;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      if (x + e >= w) continue;
+      int v00, v01 = 0, v10 = 0, v11 = 0;
+      if (staged) {
+        const int lx = sx[e] - bxa, ly = sy[e] - by0;
+        v00 = foot[ly][lx];
+        if (lin) { v01 = foot[ly][lx + 1]; v10 = foot[ly + 1][lx]; v11 = foot[ly + 1][lx + 1]; }
+      } else {
+        v00 = fetch_global(s, h, w, sx[e], sy[e], a.border, a.cval);
+        if (lin) {
+          v01 = fetch_global(s, h, w, sx[e] + 1, sy[e], a.border, a.cval);
+          v10 = fetch_global(s, h, w, sx[e], sy[e] + 1, a.border, a.cval);
+          v11 = fetch_global(s, h, w, sx[e] + 1, sy[e] + 1, a.border, a.cval);
+        }
+      }
+      int out = v00;
+      if (lin) {
+        // cv2 BilinearTab_i: (32-fy)(32-fx)*32 etc., sum 32768; FixedPtCast<15>
+        const int w00 = (32 - fy[e]) * (32 - fx[e]) * 32, w01 = (32 - fy[e]) * fx[e] * 32;
+        const int w10 = fy[e] * (32 - fx[e]) * 32, w11 = fy[e] * fx[e] * 32;
+        out = (v00 * w00 + v01 * w01 + v10 * w10 + v11 * w11 + (1 << 14)) >> 15;
+        out = max(0, min(255, out));
+      }
+      packed |= (uint32_t)out << (8 * e);
+    }
+    if (vec_ok && x + 3 < w) {
+      *reinterpret_cast<uint32_t*>(d + (size_t)y * w + x) = packed;
+    } else {
+#pragma unroll
+      for (int e = 0; e < 4; ++e)
+        if (x + e < w) d[(size_t)y * w + x + e] = (uint8_t)(packed >> (8 * e));
+    }
   }
 }
 
 int launch_warp(const uint8_t* src, uint8_t* dst, int planes, const WarpArgs& a, void* stream) {
-  dim3 grid((a.w + TILE - 1) / TILE, (a.h + TILE - 1) / TILE, planes);
-  warp_u8_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, dst, a);
+  const int tx = (a.w + TILE - 1) / TILE, ty = (a.h + TILE - 1) / TILE;
+  // enough CTAs for ~8 per SM; the rest of the planes are walked inside the CTA
+  int gz = (148 * 8 + tx * ty - 1) / (tx * ty);
+  gz = gz < 1 ? 1 : (gz > planes ? planes : gz);
+  const int pz = (planes + gz - 1) / gz;
+  gz = (planes + pz - 1) / pz;
+  const int vec_ok = (a.w % 4 == 0) && (reinterpret_cast<uintptr_t>(src) % 4 == 0) &&
+                     (reinterpret_cast<uintptr_t>(dst) % 4 == 0);
+  dim3 grid(tx, ty, gz);
+  warp_u8_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, dst, a, planes, pz, vec_ok);
   B2_CHECK_CUDA(cudaGetLastError());
   return B2SEG_OK;
 }
@@ -262,6 +427,26 @@ extern "C" int b2seg_aug_permute_u8(const uint8_t* src, uint8_t* dst, int planes
       B2_REQUIRE(false, "aug_permute: unknown mode %d", mode);
   }
   const bool swap = km >= 3;
+  const bool aligned = ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0;
+  if (aligned && !swap && w % 16 == 0) {
+    const long long total = (long long)planes * h * (w / 16);
+    const long long want = (total + 255) / 256;
+    const int blocks = (int)(want < 148 * 16 ? want : 148 * 16);
+    if (total < (1ll << 31))
+      flip16_kernel<unsigned><<<blocks, 256, 0, (cudaStream_t)stream>>>(
+          reinterpret_cast<const uint4*>(src), reinterpret_cast<uint4*>(dst), h, w / 16, total, km);
+    else
+      flip16_kernel<unsigned long long><<<blocks, 256, 0, (cudaStream_t)stream>>>(
+          reinterpret_cast<const uint4*>(src), reinterpret_cast<uint4*>(dst), h, w / 16, total, km);
+    B2_CHECK_CUDA(cudaGetLastError());
+    return B2SEG_OK;
+  }
+  if (aligned && swap && w % 64 == 0 && h % 64 == 0) {
+    dim3 grid64(w / 64, h / 64, planes);
+    transpose64_kernel<<<grid64, 256, 0, (cudaStream_t)stream>>>(src, dst, h, w, km);
+    B2_CHECK_CUDA(cudaGetLastError());
+    return B2SEG_OK;
+  }
   const int dh = swap ? w : h, dw = swap ? h : w;
   dim3 grid((dw + TILE - 1) / TILE, (dh + TILE - 1) / TILE, planes);
   permute_u8_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, dst, h, w, km);

@@ -51,6 +51,41 @@ __global__ void __launch_bounds__(1024) bn_finalize_kernel(const EwArgs a) {
 }
 
 // -------------------------------------------------------------------- BN_APPLY ----
+// Per-channel constants live in registers: with C a power of two the 8-channel vector a thread
+// owns never changes along its grid-stride walk (256 % (C/8) == 0), so there is no per-element
+// index division and no per-element reload of scale/shift.
+struct BnApplyCh {
+  F8 sc, sf, rs, rf;
+};
+__device__ __forceinline__ uint4 bn_ld_raw8(const bf16* p) { return *reinterpret_cast<const uint4*>(p); }
+__device__ __forceinline__ F8 bn_unpack8(const uint4& u) {
+  F8 r;
+  float2 t;
+  t = bf2_to_f2(u.x); r.v[0] = t.x; r.v[1] = t.y;
+  t = bf2_to_f2(u.y); r.v[2] = t.x; r.v[3] = t.y;
+  t = bf2_to_f2(u.z); r.v[4] = t.x; r.v[5] = t.y;
+  t = bf2_to_f2(u.w); r.v[6] = t.x; r.v[7] = t.y;
+  return r;
+}
+__device__ __forceinline__ F8 bn_apply_one(const uint4& yraw, const uint4& rraw, bool has_res,
+                                           const BnApplyCh& ch, bool rnorm, bool relu) {
+  const F8 yv = bn_unpack8(yraw);
+  F8 v;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) v.v[j] = fmaf(yv.v[j], ch.sc.v[j], ch.sf.v[j]);
+  if (has_res) {
+    const F8 rv = bn_unpack8(rraw);
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      v.v[j] += rnorm ? fmaf(rv.v[j], ch.rs.v[j], ch.rf.v[j]) : rv.v[j];
+  }
+  if (relu) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v.v[j] = fmaxf(v.v[j], 0.0f);
+  }
+  return v;
+}
+
 __global__ void __launch_bounds__(kEwThreads) bn_apply_kernel(const EwArgs a) {
   pdl_prologue();
   const bf16* y = (const bf16*)a.p[0];
@@ -63,30 +98,55 @@ __global__ void __launch_bounds__(kEwThreads) bn_apply_kernel(const EwArgs a) {
   const long long ldy = a.i[2], ldo = a.i[3], ldr = a.i[4];
   const bool relu = a.i[5] != 0;
   const int cv = C >> 3;
+  BnApplyCh ch;
+  if (kEwThreads % cv == 0) {
+    const int ppb = kEwThreads / cv;  // pixels per block per step
+    const int c0 = (threadIdx.x % cv) * 8;
+    const long long pstep = (long long)gridDim.x * ppb;
+    ch.sc = ld_f8(bnp + c0);
+    ch.sf = ld_f8(bnp + C + c0);
+    if (res && rbnp) {
+      ch.rs = ld_f8(rbnp + c0);
+      ch.rf = ld_f8(rbnp + C + c0);
+    }
+    long long p = (long long)blockIdx.x * ppb + threadIdx.x / cv;
+    // two pixels in flight per thread: all loads of a pair are issued before the first store
+    for (; p + pstep < P; p += 2 * pstep) {
+      const long long q = p + pstep;
+      const uint4 y0 = bn_ld_raw8(y + p * ldy + c0), y1 = bn_ld_raw8(y + q * ldy + c0);
+      uint4 r0 = make_uint4(0, 0, 0, 0), r1 = r0;
+      if (res) {
+        r0 = bn_ld_raw8(res + p * ldr + c0);
+        r1 = bn_ld_raw8(res + q * ldr + c0);
+      }
+      st_bf8(out + p * ldo + c0, bn_apply_one(y0, r0, res != nullptr, ch, rbnp != nullptr, relu));
+      st_bf8(out + q * ldo + c0, bn_apply_one(y1, r1, res != nullptr, ch, rbnp != nullptr, relu));
+    }
+    if (p < P) {
+      const uint4 y0 = bn_ld_raw8(y + p * ldy + c0);
+      uint4 r0 = make_uint4(0, 0, 0, 0);
+      if (res) r0 = bn_ld_raw8(res + p * ldr + c0);
+      st_bf8(out + p * ldo + c0, bn_apply_one(y0, r0, res != nullptr, ch, rbnp != nullptr, relu));
+    }
+    return;
+  }
   const long long total = P * cv;
   for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
        idx += (long long)gridDim.x * blockDim.x) {
     const long long p = idx / cv;
     const int c0 = (int)(idx % cv) * 8;
-    F8 v = ld_bf8(y + p * ldy + c0);
-    const F8 sc = ld_f8(bnp + c0), sf = ld_f8(bnp + C + c0);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) v.v[j] = fmaf(v.v[j], sc.v[j], sf.v[j]);
+    ch.sc = ld_f8(bnp + c0);
+    ch.sf = ld_f8(bnp + C + c0);
+    const uint4 y0 = bn_ld_raw8(y + p * ldy + c0);
+    uint4 r0 = make_uint4(0, 0, 0, 0);
     if (res) {
-      F8 r = ld_bf8(res + p * ldr + c0);
+      r0 = bn_ld_raw8(res + p * ldr + c0);
       if (rbnp) {
-        const F8 rs = ld_f8(rbnp + c0), rf = ld_f8(rbnp + C + c0);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) r.v[j] = fmaf(r.v[j], rs.v[j], rf.v[j]);
+        ch.rs = ld_f8(rbnp + c0);
+        ch.rf = ld_f8(rbnp + C + c0);
       }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v.v[j] += r.v[j];
     }
-    if (relu) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v.v[j] = fmaxf(v.v[j], 0.0f);
-    }
-    st_bf8(out + p * ldo + c0, v);
+    st_bf8(out + p * ldo + c0, bn_apply_one(y0, r0, res != nullptr, ch, rbnp != nullptr, relu));
   }
 }
 
@@ -108,41 +168,67 @@ __device__ __forceinline__ BnBwdIn bn_bwd_in(const EwArgs& a) {
   s.self_mask = (int)a.i[9];
   return s;
 }
+struct BnBwdCh {
+  F8 sc, sf, mean, inv;
+};
+__device__ __forceinline__ BnBwdCh bn_bwd_ch(const BnBwdIn& s, int c0) {
+  BnBwdCh ch;
+  if (s.self_mask) {
+    ch.sc = ld_f8(s.bnp + c0);
+    ch.sf = ld_f8(s.bnp + s.C + c0);
+  }
+  ch.mean = ld_f8(s.bnp + 2 * s.C + c0);
+  ch.inv = ld_f8(s.bnp + 3 * s.C + c0);
+  return ch;
+}
+// one pixel's operands as loaded (packed bf16: 4 registers per 8 channels until they are used)
+struct BnBwdRaw {
+  uint4 d1, d2, m, y, old;
+};
+__device__ __forceinline__ BnBwdRaw bn_bwd_fetch(const BnBwdIn& s, long long p, int c0) {
+  BnBwdRaw r;
+  r.d1 = bn_ld_raw8(s.da1 + p * s.ld1 + c0);
+  if (s.da2) r.d2 = bn_ld_raw8(s.da2 + p * s.ld2 + c0);
+  if (s.act) r.m = bn_ld_raw8(s.act + p * s.lda + c0);
+  r.y = bn_ld_raw8(s.y + p * s.ldy + c0);
+  return r;
+}
 // dz = (da1 [+ da2]) * [act > 0];  yhat = (y - mean) * invstd
-__device__ __forceinline__ void bn_bwd_load(const BnBwdIn& s, long long p, int c0, F8& dz, F8& yh) {
-  dz = ld_bf8(s.da1 + p * s.ld1 + c0);
+__device__ __forceinline__ void bn_bwd_math(const BnBwdIn& s, const BnBwdCh& ch, const BnBwdRaw& r,
+                                            F8& dz, F8& yh) {
+  dz = bn_unpack8(r.d1);
   if (s.da2) {
-    const F8 d2 = ld_bf8(s.da2 + p * s.ld2 + c0);
+    const F8 d2 = bn_unpack8(r.d2);
 #pragma unroll
     for (int j = 0; j < 8; ++j) dz.v[j] += d2.v[j];
   }
   if (s.act) {
-    const F8 m = ld_bf8(s.act + p * s.lda + c0);
+    const F8 m = bn_unpack8(r.m);
 #pragma unroll
     for (int j = 0; j < 8; ++j) dz.v[j] = m.v[j] > 0.0f ? dz.v[j] : 0.0f;
   }
-  yh = ld_bf8(s.y + p * s.ldy + c0);
+  const F8 y = bn_unpack8(r.y);
   if (s.self_mask) {  // the forward pass stored bf16(relu(fma(y, scale, shift))): same arithmetic here
-    const F8 sc = ld_f8(s.bnp + c0), sf = ld_f8(s.bnp + s.C + c0);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const float act = __bfloat162float(__float2bfloat16_rn(fmaf(yh.v[j], sc.v[j], sf.v[j])));
+      const float act = __bfloat162float(__float2bfloat16_rn(fmaf(y.v[j], ch.sc.v[j], ch.sf.v[j])));
       dz.v[j] = act > 0.0f ? dz.v[j] : 0.0f;
     }
   }
-  const F8 mean = ld_f8(s.bnp + 2 * s.C + c0), inv = ld_f8(s.bnp + 3 * s.C + c0);
 #pragma unroll
-  for (int j = 0; j < 8; ++j) yh.v[j] = (yh.v[j] - mean.v[j]) * inv.v[j];
+  for (int j = 0; j < 8; ++j) yh.v[j] = (y.v[j] - ch.mean.v[j]) * ch.inv.v[j];
 }
 
 __global__ void __launch_bounds__(kEwThreads) bn_bwd_reduce_kernel(const EwArgs a) {
   pdl_prologue();
   extern __shared__ float red[];
   const BnBwdIn s = bn_bwd_in(a);
+  // ew_channel_reduce gives every thread one fixed channel vector: constants loaded once
+  const BnBwdCh ch = bn_bwd_ch(s, (int)(threadIdx.x % (s.C >> 3)) * 8);
   ew_channel_reduce<2>(0, a.i[0], s.C, (float*)a.p[5], red,
                        [&](long long p, int c0, float (&acc)[2][8]) {
                          F8 dz, yh;
-                         bn_bwd_load(s, p, c0, dz, yh);
+                         bn_bwd_math(s, ch, bn_bwd_fetch(s, p, c0), dz, yh);
 #pragma unroll
                          for (int j = 0; j < 8; ++j) {
                            acc[0][j] += dz.v[j];
@@ -179,6 +265,27 @@ __global__ void __launch_bounds__(1024) bn_bwd_finalize_kernel(const EwArgs a) {
   });
 }
 
+struct BnBwdCoef {
+  F8 c1, c2, c3;
+};
+__device__ __forceinline__ void bn_bwd_apply_store(const BnBwdIn& s, const BnBwdCh& ch, const BnBwdCoef& k,
+                                                   const BnBwdRaw& r, bool dz_acc, long long p, int c0,
+                                                   bf16* dy, long long lddy, bf16* dzo, long long lddz) {
+  F8 dz, yh, o;
+  bn_bwd_math(s, ch, r, dz, yh);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) o.v[j] = k.c1.v[j] * (dz.v[j] - k.c2.v[j] - yh.v[j] * k.c3.v[j]);
+  st_bf8(dy + p * lddy + c0, o);
+  if (dzo) {
+    if (dz_acc) {
+      const F8 old = bn_unpack8(r.old);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) dz.v[j] += old.v[j];
+    }
+    st_bf8(dzo + p * lddz + c0, dz);
+  }
+}
+
 __global__ void __launch_bounds__(kEwThreads) bn_bwd_apply_kernel(const EwArgs a) {
   pdl_prologue();
   const BnBwdIn s = bn_bwd_in(a);
@@ -186,28 +293,44 @@ __global__ void __launch_bounds__(kEwThreads) bn_bwd_apply_kernel(const EwArgs a
   bf16* dy = (bf16*)a.p[6];
   bf16* dzo = (bf16*)a.p[7];
   const long long P = a.i[0], lddy = a.i[6], lddz = a.i[7];
-  const int dz_mode = (int)a.i[8];  // 1 = store, 2 = accumulate
+  const bool dz_acc = dzo && (int)a.i[8] == 2;  // 1 = store, 2 = accumulate
   const int C = s.C, cv = C >> 3;
+  if (kEwThreads % cv == 0) {
+    const int ppb = kEwThreads / cv;
+    const int c0 = (threadIdx.x % cv) * 8;
+    const long long pstep = (long long)gridDim.x * ppb;
+    const BnBwdCh ch = bn_bwd_ch(s, c0);
+    BnBwdCoef k;
+    k.c1 = ld_f8(coef + c0); k.c2 = ld_f8(coef + C + c0); k.c3 = ld_f8(coef + 2 * C + c0);
+    long long p = (long long)blockIdx.x * ppb + threadIdx.x / cv;
+    for (; p + pstep < P; p += 2 * pstep) {
+      const long long q = p + pstep;
+      BnBwdRaw r0 = bn_bwd_fetch(s, p, c0), r1 = bn_bwd_fetch(s, q, c0);
+      if (dz_acc) {
+        r0.old = bn_ld_raw8(dzo + p * lddz + c0);
+        r1.old = bn_ld_raw8(dzo + q * lddz + c0);
+      }
+      bn_bwd_apply_store(s, ch, k, r0, dz_acc, p, c0, dy, lddy, dzo, lddz);
+      bn_bwd_apply_store(s, ch, k, r1, dz_acc, q, c0, dy, lddy, dzo, lddz);
+    }
+    if (p < P) {
+      BnBwdRaw r0 = bn_bwd_fetch(s, p, c0);
+      if (dz_acc) r0.old = bn_ld_raw8(dzo + p * lddz + c0);
+      bn_bwd_apply_store(s, ch, k, r0, dz_acc, p, c0, dy, lddy, dzo, lddz);
+    }
+    return;
+  }
   const long long total = P * cv;
   for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
        idx += (long long)gridDim.x * blockDim.x) {
     const long long p = idx / cv;
     const int c0 = (int)(idx % cv) * 8;
-    F8 dz, yh;
-    bn_bwd_load(s, p, c0, dz, yh);
-    const F8 c1 = ld_f8(coef + c0), c2 = ld_f8(coef + C + c0), c3 = ld_f8(coef + 2 * C + c0);
-    F8 o;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) o.v[j] = c1.v[j] * (dz.v[j] - c2.v[j] - yh.v[j] * c3.v[j]);
-    st_bf8(dy + p * lddy + c0, o);
-    if (dzo) {
-      if (dz_mode == 2) {
-        const F8 old = ld_bf8(dzo + p * lddz + c0);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) dz.v[j] += old.v[j];
-      }
-      st_bf8(dzo + p * lddz + c0, dz);
-    }
+    const BnBwdCh ch = bn_bwd_ch(s, c0);
+    BnBwdCoef k;
+    k.c1 = ld_f8(coef + c0); k.c2 = ld_f8(coef + C + c0); k.c3 = ld_f8(coef + 2 * C + c0);
+    BnBwdRaw r0 = bn_bwd_fetch(s, p, c0);
+    if (dz_acc) r0.old = bn_ld_raw8(dzo + p * lddz + c0);
+    bn_bwd_apply_store(s, ch, k, r0, dz_acc, p, c0, dy, lddy, dzo, lddz);
   }
 }
 

@@ -175,6 +175,7 @@ __device__ __forceinline__ void ew_channel_reduce(long long P0, long long P1, in
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[k][j] = 0.0f;
   if (lp < pl) {
+#pragma unroll 2
     for (long long p = P0 + (long long)blockIdx.x * pl + lp; p < P1; p += (long long)gridDim.x * pl)
       body(p, lc * 8, acc);
 #pragma unroll

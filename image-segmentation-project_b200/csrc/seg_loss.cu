@@ -36,9 +36,19 @@ __device__ __forceinline__ PixelTerms pixel_terms(float x, float t) {
   PixelTerms r;
   const float e = __expf(-fabsf(x));
   const float inv = __frcp_rn(1.0f + e);
-  r.p = x >= 0.0f ? inv : e * inv;
+  const float small = e * inv;  // min(p, 1-p), free of cancellation
+  r.p = x >= 0.0f ? inv : small;
   r.bce = fmaxf(x, 0.0f) - x * t + log1p_exp_neg(e);
-  r.one_m_pt = NEED_FOCAL ? 1.0f - __expf(-r.bce) : 0.0f;
+  if (NEED_FOCAL) {
+    // 1 - pt with pt = exp(-bce) (losses.py:78-80).  For hard targets pt is p or 1-p, both
+    // already in registers; only soft targets pay the extra exp.
+    const float omp = x >= 0.0f ? small : inv;  // 1 - p
+    if (t == 1.0f) r.one_m_pt = omp;
+    else if (t == 0.0f) r.one_m_pt = r.p;
+    else r.one_m_pt = 1.0f - __expf(-r.bce);
+  } else {
+    r.one_m_pt = 0.0f;
+  }
   return r;
 }
 

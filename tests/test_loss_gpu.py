@@ -72,6 +72,25 @@ def test_ragged_sizes_and_misalignment(cuda, n):
             np.testing.assert_allclose(gd.cpu().numpy(), go.numpy(), rtol=3e-4, atol=1e-8)
 
 
+def test_soft_targets(cuda):
+    """Targets strictly between 0 and 1 (label smoothing / resized masks): the focal term takes
+    its general exp(-bce) branch instead of the hard-target shortcut."""
+    import losses
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(2, 1, 40, 52, generator=g) * 3
+    t = torch.rand(2, 1, 40, 52, generator=g)
+    t[0, 0, :4] = 0.0
+    t[0, 0, 4:8] = 1.0
+    for name in ("focal", "triple_combo", "combo", "dice"):
+        crit = losses.get_loss_function({"loss_fn": name})
+        xd = x.to(cuda).requires_grad_(True)
+        val = crit(xd, t.to(cuda))
+        (gd,) = torch.autograd.grad(val, xd)
+        vo, go = seg_losses.loss_and_grad(name, x, t)
+        assert float(val) == pytest.approx(vo, rel=2e-5, abs=1e-7), name
+        np.testing.assert_allclose(gd.cpu().numpy(), go.numpy(), rtol=3e-4, atol=1e-8, err_msg=name)
+
+
 def test_metrics_match_fixture_and_counts_are_exact(cuda, loss_kat):
     import utils
     logits, target = seg_losses.kat_inputs((4, 1, 256, 256))
