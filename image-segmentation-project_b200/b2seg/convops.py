@@ -82,13 +82,16 @@ class Op:
 class Seq:
     """Ordered list of ops replayed with one C call."""
 
-    def __init__(self, ops):
+    def __init__(self, ops, side_kinds=()):
+        """`side_kinds`: kind prefixes of ops nothing later in the list depends on (weight
+        gradients); the graph replay runs them on a side branch (b2seg_seq_append_lane)."""
         self.ops = list(ops)
         h = C.c_void_p()
         L.check(L.lib().b2seg_seq_create(C.byref(h)))
         self.handle = h
         for op in self.ops:
-            L.check(L.lib().b2seg_seq_append(self.handle, op.handle))
+            lane = 1 if any(op.kind.startswith(k) for k in side_kinds) else 0
+            L.check(L.lib().b2seg_seq_append_lane(self.handle, op.handle, lane))
 
     def run(self):
         L.check(L.lib().b2seg_seq_run(self.handle, L.stream_ptr()))

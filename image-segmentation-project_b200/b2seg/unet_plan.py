@@ -324,7 +324,9 @@ class UNetPlan:
         self.tape = None
         self._finish_pack()
         self.fwd = co.Seq(self.fwd_ops)
-        self.bwd = co.Seq(self.bwd_ops) if ng else None
+        # weight-gradient GEMMs read a forward activation and a gradient that is final when they are
+        # appended, and write only their slice of gflat: they float on the graph's side branch
+        self.bwd = co.Seq(self.bwd_ops, side_kinds=("wgrad",)) if ng else None
         self.launches_fwd = self.fwd.launches
         self.launches_bwd = self.bwd.launches if ng else 0
 

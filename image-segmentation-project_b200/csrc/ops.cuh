@@ -16,6 +16,12 @@ struct b2seg_op {
 
 struct b2seg_seq {
   std::vector<b2seg_op*> ops;
+  // lane 0 = the dependent chain; lane 1 = ops whose results nothing in the sequence reads
+  // (weight gradients): in the captured graph they fork onto a side branch after the op that
+  // precedes them and join at the end, so they fill the chain's latency bubbles.
+  std::vector<int> lanes;
+  cudaStream_t side_stream = nullptr;
+  cudaEvent_t fork_event = nullptr, join_event = nullptr;
   // CUDA-graph replay: the op list is captured once on a private stream (PyTorch's default stream
   // is the legacy stream, which cannot be captured) and launched into the caller's stream.
   cudaGraphExec_t exec = nullptr;

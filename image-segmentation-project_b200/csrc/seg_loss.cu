@@ -31,25 +31,32 @@ __device__ __forceinline__ float log1p_exp_neg(float e) {
   return e < 0.015625f ? series : __logf(1.0f + e);
 }
 
-template <bool NEED_FOCAL>
+// SOFT = false is the hard-target shortcut of the focal term: pt = exp(-bce) (losses.py:78-80) is
+// p for t = 1 and 1-p for t = 0, and both are already in registers (cancellation-free), so the
+// second exp is skipped.  Callers pick SOFT per group of 8 pixels (see is_hard4).
+template <bool NEED_FOCAL, bool SOFT = true>
 __device__ __forceinline__ PixelTerms pixel_terms(float x, float t) {
   PixelTerms r;
   const float e = __expf(-fabsf(x));
   const float inv = __frcp_rn(1.0f + e);
-  const float small = e * inv;  // min(p, 1-p), free of cancellation
+  const float small = e * inv;  // min(p, 1-p)
   r.p = x >= 0.0f ? inv : small;
   r.bce = fmaxf(x, 0.0f) - x * t + log1p_exp_neg(e);
   if (NEED_FOCAL) {
-    // 1 - pt with pt = exp(-bce) (losses.py:78-80).  For hard targets pt is p or 1-p, both
-    // already in registers; only soft targets pay the extra exp.
-    const float omp = x >= 0.0f ? small : inv;  // 1 - p
-    if (t == 1.0f) r.one_m_pt = omp;
-    else if (t == 0.0f) r.one_m_pt = r.p;
-    else r.one_m_pt = 1.0f - __expf(-r.bce);
+    if (SOFT) {
+      r.one_m_pt = 1.0f - __expf(-r.bce);
+    } else {
+      const float omp = x >= 0.0f ? small : inv;  // 1 - p
+      r.one_m_pt = t == 1.0f ? omp : r.p;
+    }
   } else {
     r.one_m_pt = 0.0f;
   }
   return r;
+}
+__device__ __forceinline__ bool is_hard4(const float4& t) {
+  return (t.x == 0.0f || t.x == 1.0f) && (t.y == 0.0f || t.y == 1.0f) &&
+         (t.z == 0.0f || t.z == 1.0f) && (t.w == 0.0f || t.w == 1.0f);
 }
 
 __device__ __forceinline__ float pow_pos(float base, float g) {
@@ -57,10 +64,10 @@ __device__ __forceinline__ float pow_pos(float base, float g) {
   return exp2f(g * __log2f(base));
 }
 
-template <bool NEED_FOCAL, bool HAS_WMAP>
+template <bool NEED_FOCAL, bool HAS_WMAP, bool SOFT = true>
 __device__ __forceinline__ void accumulate(float (&acc)[kAcc], float x, float t, float w,
                                            float gamma, bool gamma_is_two) {
-  const PixelTerms q = pixel_terms<NEED_FOCAL>(x, t);
+  const PixelTerms q = pixel_terms<NEED_FOCAL, SOFT>(x, t);
   const float bce_w = HAS_WMAP ? q.bce * w : q.bce;
   acc[0] += q.p;
   acc[1] += t;
@@ -220,6 +227,15 @@ __device__ void finish_loss(const b2seg_loss_spec& s, const double* tot, double 
 }
 
 // ---- forward kernel -----------------------------------------------------------
+template <bool NEED_FOCAL, bool HAS_WMAP, bool SOFT>
+__device__ __forceinline__ void accumulate4(float (&acc)[kAcc], const float4& x, const float4& t,
+                                            const float4& w, float gamma, bool g2) {
+  accumulate<NEED_FOCAL, HAS_WMAP, SOFT>(acc, x.x, t.x, w.x, gamma, g2);
+  accumulate<NEED_FOCAL, HAS_WMAP, SOFT>(acc, x.y, t.y, w.y, gamma, g2);
+  accumulate<NEED_FOCAL, HAS_WMAP, SOFT>(acc, x.z, t.z, w.z, gamma, g2);
+  accumulate<NEED_FOCAL, HAS_WMAP, SOFT>(acc, x.w, t.w, w.w, gamma, g2);
+}
+
 template <bool NEED_FOCAL, bool HAS_WMAP, bool VEC4>
 __global__ void __launch_bounds__(kThreads)
     seg_loss_fwd_kernel(const float* __restrict__ x, const float* __restrict__ t,
@@ -248,14 +264,13 @@ __global__ void __launch_bounds__(kThreads)
         wa = ldg_stream_f4(w4 + i);
         wb = ldg_stream_f4(w4 + i + nthreads);
       }
-      accumulate<NEED_FOCAL, HAS_WMAP>(acc, xa.x, ta.x, wa.x, gamma, g2);
-      accumulate<NEED_FOCAL, HAS_WMAP>(acc, xa.y, ta.y, wa.y, gamma, g2);
-      accumulate<NEED_FOCAL, HAS_WMAP>(acc, xa.z, ta.z, wa.z, gamma, g2);
-      accumulate<NEED_FOCAL, HAS_WMAP>(acc, xa.w, ta.w, wa.w, gamma, g2);
-      accumulate<NEED_FOCAL, HAS_WMAP>(acc, xb.x, tb.x, wb.x, gamma, g2);
-      accumulate<NEED_FOCAL, HAS_WMAP>(acc, xb.y, tb.y, wb.y, gamma, g2);
-      accumulate<NEED_FOCAL, HAS_WMAP>(acc, xb.z, tb.z, wb.z, gamma, g2);
-      accumulate<NEED_FOCAL, HAS_WMAP>(acc, xb.w, tb.w, wb.w, gamma, g2);
+      if (NEED_FOCAL && is_hard4(ta) && is_hard4(tb)) {
+        accumulate4<NEED_FOCAL, HAS_WMAP, false>(acc, xa, ta, wa, gamma, g2);
+        accumulate4<NEED_FOCAL, HAS_WMAP, false>(acc, xb, tb, wb, gamma, g2);
+      } else {
+        accumulate4<NEED_FOCAL, HAS_WMAP, true>(acc, xa, ta, wa, gamma, g2);
+        accumulate4<NEED_FOCAL, HAS_WMAP, true>(acc, xb, tb, wb, gamma, g2);
+      }
     }
     for (; i < n4; i += nthreads) {
       const float4 xa = ldg_stream_f4(x4 + i);
@@ -281,11 +296,11 @@ __global__ void __launch_bounds__(kThreads)
 }
 
 // ---- backward kernel ----------------------------------------------------------
-template <bool NEED_FOCAL, bool HAS_WMAP>
+template <bool NEED_FOCAL, bool HAS_WMAP, bool SOFT = true>
 __device__ __forceinline__ float pixel_grad(float x, float t, float w, float A, float B, float W0,
                                             float W1, float F, float Wm, float gamma,
                                             bool gamma_is_two, float go) {
-  const PixelTerms q = pixel_terms<NEED_FOCAL>(x, t);
+  const PixelTerms q = pixel_terms<NEED_FOCAL, SOFT>(x, t);
   const float d = q.p - t;
   float g = (fmaf(A, t, B)) * q.p * (1.0f - q.p);
   float wl = fmaf(W1, t, W0);
@@ -307,20 +322,29 @@ __device__ __forceinline__ float pixel_grad(float x, float t, float w, float A, 
   return g * go;
 }
 
+struct BwdCoef {
+  float A, B, W0, W1, F, gamma, Wm, go;
+  bool g2;
+};
+template <bool NEED_FOCAL, bool HAS_WMAP, bool SOFT>
+__device__ __forceinline__ float4 pixel_grad4(const float4& x, const float4& t, const float4& w,
+                                              const BwdCoef& c) {
+  float4 g;
+  g.x = pixel_grad<NEED_FOCAL, HAS_WMAP, SOFT>(x.x, t.x, w.x, c.A, c.B, c.W0, c.W1, c.F, c.Wm, c.gamma, c.g2, c.go);
+  g.y = pixel_grad<NEED_FOCAL, HAS_WMAP, SOFT>(x.y, t.y, w.y, c.A, c.B, c.W0, c.W1, c.F, c.Wm, c.gamma, c.g2, c.go);
+  g.z = pixel_grad<NEED_FOCAL, HAS_WMAP, SOFT>(x.z, t.z, w.z, c.A, c.B, c.W0, c.W1, c.F, c.Wm, c.gamma, c.g2, c.go);
+  g.w = pixel_grad<NEED_FOCAL, HAS_WMAP, SOFT>(x.w, t.w, w.w, c.A, c.B, c.W0, c.W1, c.F, c.Wm, c.gamma, c.g2, c.go);
+  return g;
+}
+
 template <bool NEED_FOCAL, bool HAS_WMAP, bool VEC4>
-__global__ void __launch_bounds__(kThreads)
-    seg_loss_bwd_kernel(const float* __restrict__ x, const float* __restrict__ t,
-                        const float* __restrict__ wm, long long n,
-                        const float* __restrict__ coef, const float* __restrict__ grad_out,
-                        float* __restrict__ gx) {
-  const float A = coef[0], B = coef[1], W0 = coef[2], W1 = coef[3], F = coef[4], gamma = coef[5],
-              Wm = coef[6];
-  const float go = grad_out ? *grad_out : 1.0f;
-  const bool g2 = gamma == 2.0f;
+__device__ __forceinline__ void seg_loss_bwd_body(const float* __restrict__ x, const float* __restrict__ t,
+                                                  const float* __restrict__ wm, long long n,
+                                                  const BwdCoef& c, float* __restrict__ gx) {
   const long long tid = (long long)blockIdx.x * kThreads + threadIdx.x;
   const long long nthreads = (long long)gridDim.x * kThreads;
 #define B2_PG(xx, tt, ww) \
-  pixel_grad<NEED_FOCAL, HAS_WMAP>(xx, tt, ww, A, B, W0, W1, F, Wm, gamma, g2, go)
+  pixel_grad<NEED_FOCAL, HAS_WMAP, true>(xx, tt, ww, c.A, c.B, c.W0, c.W1, c.F, c.Wm, c.gamma, c.g2, c.go)
   if (VEC4) {
     const long long n4 = n >> 2;
     const float4* x4 = reinterpret_cast<const float4*>(x);
@@ -337,14 +361,13 @@ __global__ void __launch_bounds__(kThreads)
         wb = ldg_stream_f4(w4 + i + nthreads);
       }
       float4 ga, gb;
-      ga.x = B2_PG(xa.x, ta.x, wa.x);
-      ga.y = B2_PG(xa.y, ta.y, wa.y);
-      ga.z = B2_PG(xa.z, ta.z, wa.z);
-      ga.w = B2_PG(xa.w, ta.w, wa.w);
-      gb.x = B2_PG(xb.x, tb.x, wb.x);
-      gb.y = B2_PG(xb.y, tb.y, wb.y);
-      gb.z = B2_PG(xb.z, tb.z, wb.z);
-      gb.w = B2_PG(xb.w, tb.w, wb.w);
+      if (NEED_FOCAL && is_hard4(ta) && is_hard4(tb)) {
+        ga = pixel_grad4<NEED_FOCAL, HAS_WMAP, false>(xa, ta, wa, c);
+        gb = pixel_grad4<NEED_FOCAL, HAS_WMAP, false>(xb, tb, wb, c);
+      } else {
+        ga = pixel_grad4<NEED_FOCAL, HAS_WMAP, true>(xa, ta, wa, c);
+        gb = pixel_grad4<NEED_FOCAL, HAS_WMAP, true>(xb, tb, wb, c);
+      }
       stg_stream_f4(g4 + i, ga);
       stg_stream_f4(g4 + i + nthreads, gb);
     }
@@ -353,12 +376,7 @@ __global__ void __launch_bounds__(kThreads)
       const float4 ta = ldg_stream_f4(t4 + i);
       float4 wa = make_float4(1.f, 1.f, 1.f, 1.f);
       if (HAS_WMAP) wa = ldg_stream_f4(w4 + i);
-      float4 ga;
-      ga.x = B2_PG(xa.x, ta.x, wa.x);
-      ga.y = B2_PG(xa.y, ta.y, wa.y);
-      ga.z = B2_PG(xa.z, ta.z, wa.z);
-      ga.w = B2_PG(xa.w, ta.w, wa.w);
-      stg_stream_f4(g4 + i, ga);
+      stg_stream_f4(g4 + i, pixel_grad4<NEED_FOCAL, HAS_WMAP, true>(xa, ta, wa, c));
     }
     for (long long j = (n4 << 2) + tid; j < n; j += nthreads)
       gx[j] = B2_PG(x[j], t[j], HAS_WMAP ? wm[j] : 1.0f);
@@ -367,6 +385,25 @@ __global__ void __launch_bounds__(kThreads)
       gx[j] = B2_PG(x[j], t[j], HAS_WMAP ? wm[j] : 1.0f);
   }
 #undef B2_PG
+}
+
+// The focal coefficient is only known on the device (the forward kernel wrote it), so the
+// kernel branches once, uniformly, between the focal and the focal-free instantiation.
+template <bool NEED_FOCAL_UNUSED, bool HAS_WMAP, bool VEC4>
+__global__ void __launch_bounds__(kThreads)
+    seg_loss_bwd_kernel(const float* __restrict__ x, const float* __restrict__ t,
+                        const float* __restrict__ wm, long long n,
+                        const float* __restrict__ coef, const float* __restrict__ grad_out,
+                        float* __restrict__ gx) {
+  BwdCoef c;
+  c.A = coef[0]; c.B = coef[1]; c.W0 = coef[2]; c.W1 = coef[3]; c.F = coef[4]; c.gamma = coef[5];
+  c.Wm = coef[6];
+  c.go = grad_out ? *grad_out : 1.0f;
+  c.g2 = c.gamma == 2.0f;
+  if (c.F == 0.0f)
+    seg_loss_bwd_body<false, HAS_WMAP, VEC4>(x, t, wm, n, c, gx);
+  else
+    seg_loss_bwd_body<true, HAS_WMAP, VEC4>(x, t, wm, n, c, gx);
 }
 
 // ---- metrics from probabilities (utils.py:120-151) --------------------------------

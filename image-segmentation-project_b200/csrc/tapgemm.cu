@@ -470,10 +470,16 @@ extern "C" int b2seg_seq_create(b2seg_seq** out) {
   B2_REQUIRE(*out, "seq_create: out of host memory");
   return B2SEG_OK;
 }
-extern "C" int b2seg_seq_append(b2seg_seq* seq, b2seg_op* op) {
+extern "C" int b2seg_seq_append_lane(b2seg_seq* seq, b2seg_op* op, int lane) {
   B2_REQUIRE(seq && op, "seq_append: null");
+  B2_REQUIRE(lane == 0 || lane == 1, "seq_append: lane %d (0 = chain, 1 = side branch)", lane);
+  B2_REQUIRE(!seq->exec, "seq_append: sequence already captured");
   seq->ops.push_back(op);
+  seq->lanes.push_back(lane);
   return B2SEG_OK;
+}
+extern "C" int b2seg_seq_append(b2seg_seq* seq, b2seg_op* op) {
+  return b2seg_seq_append_lane(seq, op, 0);
 }
 namespace {
 bool graphs_enabled() {
@@ -486,34 +492,78 @@ bool graphs_enabled() {
 }
 // Capture the op list into an executable graph.  Any failure (e.g. a driver that cannot capture
 // programmatic-dependent launches) leaves the sequence on the direct-launch path.
-void seq_try_capture(b2seg_seq* seq) {
-  seq->capture_failed = true;  // cleared on success
-  if (cudaStreamCreateWithFlags(&seq->capture_stream, cudaStreamNonBlocking) != cudaSuccess) return;
+bool side_lane_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B2SEG_SIDE");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v != 0;
+}
+bool seq_capture_once(b2seg_seq* seq, bool use_lanes) {
   if (cudaStreamBeginCapture(seq->capture_stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
     cudaGetLastError();
-    return;
+    return false;
   }
   int rc = B2SEG_OK;
-  for (b2seg_op* op : seq->ops) {
-    rc = op->run(seq->capture_stream);
-    if (rc != B2SEG_OK) break;
+  bool side_used = false, forked = false;  // forked: side branch already waits on the latest chain op
+  for (size_t i = 0; i < seq->ops.size() && rc == B2SEG_OK; ++i) {
+    if (use_lanes && seq->lanes[i] == 1) {
+      if (!forked) {
+        if (cudaEventRecord(seq->fork_event, seq->capture_stream) != cudaSuccess ||
+            cudaStreamWaitEvent(seq->side_stream, seq->fork_event, 0) != cudaSuccess) {
+          rc = B2SEG_ECUDA;
+          break;
+        }
+        forked = side_used = true;
+      }
+      rc = seq->ops[i]->run(seq->side_stream);
+    } else {
+      rc = seq->ops[i]->run(seq->capture_stream);
+      forked = false;
+    }
+  }
+  if (side_used && rc == B2SEG_OK) {
+    if (cudaEventRecord(seq->join_event, seq->side_stream) != cudaSuccess ||
+        cudaStreamWaitEvent(seq->capture_stream, seq->join_event, 0) != cudaSuccess)
+      rc = B2SEG_ECUDA;
   }
   cudaGraph_t g = nullptr;
   cudaError_t e = cudaStreamEndCapture(seq->capture_stream, &g);
   if (rc != B2SEG_OK || e != cudaSuccess || !g) {
     if (g) cudaGraphDestroy(g);
     cudaGetLastError();
-    return;
+    return false;
   }
   cudaGraphExec_t ex = nullptr;
   if (cudaGraphInstantiate(&ex, g, 0) != cudaSuccess) {
     cudaGraphDestroy(g);
     cudaGetLastError();
-    return;
+    return false;
   }
   seq->graph = g;
   seq->exec = ex;
-  seq->capture_failed = false;
+  return true;
+}
+// Capture the op list into an executable graph.  Any failure (e.g. a driver that cannot capture
+// programmatic-dependent launches) leaves the sequence on the direct-launch path.
+void seq_try_capture(b2seg_seq* seq) {
+  seq->capture_failed = true;  // cleared on success
+  if (cudaStreamCreateWithFlags(&seq->capture_stream, cudaStreamNonBlocking) != cudaSuccess) return;
+  bool lanes = false;
+  if (side_lane_enabled())
+    for (int l : seq->lanes) lanes = lanes || l == 1;
+  if (lanes) {
+    lanes = cudaStreamCreateWithFlags(&seq->side_stream, cudaStreamNonBlocking) == cudaSuccess &&
+            cudaEventCreateWithFlags(&seq->fork_event, cudaEventDisableTiming) == cudaSuccess &&
+            cudaEventCreateWithFlags(&seq->join_event, cudaEventDisableTiming) == cudaSuccess;
+    if (!lanes) cudaGetLastError();
+  }
+  if (lanes && seq_capture_once(seq, true)) {
+    seq->capture_failed = false;
+    return;
+  }
+  if (seq_capture_once(seq, false)) seq->capture_failed = false;
 }
 }  // namespace
 
@@ -564,6 +614,9 @@ extern "C" int b2seg_seq_destroy(b2seg_seq* seq) {
     if (seq->exec) cudaGraphExecDestroy(seq->exec);
     if (seq->graph) cudaGraphDestroy(seq->graph);
     if (seq->capture_stream) cudaStreamDestroy(seq->capture_stream);
+    if (seq->side_stream) cudaStreamDestroy(seq->side_stream);
+    if (seq->fork_event) cudaEventDestroy(seq->fork_event);
+    if (seq->join_event) cudaEventDestroy(seq->join_event);
   }
   delete seq;
   return B2SEG_OK;

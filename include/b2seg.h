@@ -157,6 +157,12 @@ int b2seg_op_destroy(b2seg_op* op);
 int b2seg_op_launches(const b2seg_op* op);
 int b2seg_seq_create(b2seg_seq** out);
 int b2seg_seq_append(b2seg_seq* seq, b2seg_op* op); /* does not take ownership */
+/* lane 0 = the dependent chain (same as b2seg_seq_append).  lane 1 = an op whose outputs no later
+ * op of the sequence reads and whose inputs no later op overwrites (weight gradients,
+ * convolution_backward's grad_weight half at train.py:48): in the CUDA-graph replay it runs on a
+ * side branch forked after the op appended before it and joined at the end of the sequence;
+ * lane-1 ops keep their relative order.  Direct (non-graph) replays ignore lanes. */
+int b2seg_seq_append_lane(b2seg_seq* seq, b2seg_op* op, int lane);
 /* Replays the ops in order.  Sequences of >= 4 ops are captured into a CUDA graph on first use
  * (one graph launch per replay; B2SEG_GRAPH=0 in the environment keeps direct launches). */
 int b2seg_seq_run(b2seg_seq* seq, void* stream);
