@@ -54,6 +54,7 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-kernel-timing", action="store_true")
+    ap.add_argument("--torch-adam", action="store_true", help="stock torch.optim.Adam instead of FusedAdam")
     a = ap.parse_args()
     a.warmup = max(a.warmup, 3) if a.impl == "b200" else a.warmup
     return a
@@ -220,7 +221,10 @@ def run_b200(a):
     model = advanced_models.UNetWithBackbone(1, a.backbone, pretrained=False,
                                              use_attention=not a.no_attention).to(dev)
     crit = losses.get_loss_function({"loss_fn": a.loss})
-    opt = torch.optim.Adam(model.parameters(), lr=1e-3, weight_decay=1e-5)
+    from b2seg.optim import FusedAdam, LAUNCHES_PER_GROUP
+    # the optimizer train.quick_train / cross_validation build: a torch.optim.Adam subclass whose
+    # step() is one multi-tensor kernel launch (--torch-adam times the stock optimizer instead)
+    opt = (torch.optim.Adam if a.torch_adam else FusedAdam)(model.parameters(), lr=1e-3, weight_decay=1e-5)
     if a.mode == "dp" and world > 1:
         from b2seg import dataparallel
         dataparallel.attach(model, world)
@@ -272,7 +276,8 @@ def run_b200(a):
 
     plan = model._plan_for(dev_i[0], True)
     from b2seg import lossfn
-    launches_step = plan.launches_fwd + plan.launches_bwd + lossfn.LAUNCHES_FWD + lossfn.LAUNCHES_BWD
+    launches_step = (plan.launches_fwd + plan.launches_bwd + lossfn.LAUNCHES_FWD + lossfn.LAUNCHES_BWD +
+                     (0 if a.torch_adam else LAUNCHES_PER_GROUP))
     imgs = a.batch * world * a.steps
     peaks = _peaks()
     rec = {

@@ -111,6 +111,8 @@ _SIGS = {
     "b2seg_aug_permute_u8": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "b2seg_aug_warp_affine_u8": (C.c_int, [_vp, _vp, _i, _i, _i, C.POINTER(C.c_double), _i, _i, _i, _vp]),
     "b2seg_aug_remap_u8": (C.c_int, [_vp, _vp, _i, _i, _i, _vp, _vp, _i, _i, _i, _vp]),
+    "b2seg_adam_step": (C.c_int, [_vp, _i, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float,
+                                  C.c_double, _vp]),
     "b2seg_op_run": (C.c_int, [_vp, _vp]),
     "b2seg_op_destroy": (C.c_int, [_vp]),
     "b2seg_op_launches": (C.c_int, [_vp]),

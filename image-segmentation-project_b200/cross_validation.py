@@ -19,6 +19,7 @@ import torch
 from sklearn.model_selection import KFold, train_test_split
 
 from b2seg import shard
+from b2seg.optim import FusedAdam
 from dataset import load_original_data
 from losses import get_loss_function
 from train import train_model
@@ -85,8 +86,8 @@ class CrossValidator:
         model = model_class(n_classes=1, backbone=config['backbone'], pretrained=config['pretrained'],
                             use_attention=config['use_attention']).to(device)
         criterion = get_loss_function(config)
-        optimizer = torch.optim.Adam(model.parameters(), lr=config['learning_rate'],
-                                     weight_decay=config.get('weight_decay', 1e-5))
+        optimizer = FusedAdam(model.parameters(), lr=config['learning_rate'],  # a torch.optim.Adam
+                              weight_decay=config.get('weight_decay', 1e-5))
         scheduler = torch.optim.lr_scheduler.ReduceLROnPlateau(optimizer, mode='max', factor=0.5,
                                                                patience=3, min_lr=1e-6)
         quiet = dict(config, verbose=False, save_plots=False)

@@ -90,7 +90,10 @@ class CellAugmenter:
 
     def __init__(self, augmentations_per_image=3, seed=None):
         self.augmentations_per_image = augmentations_per_image
-        self.temp_dir = "temp_augmentation"
+        # one directory per process: folds / grid configs run one per GPU (b2seg.shard) and each
+        # rank writes and cleans up its own augmented copies
+        rank = os.environ.get("RANK") if int(os.environ.get("WORLD_SIZE", "1")) > 1 else None
+        self.temp_dir = "temp_augmentation" if rank is None else f"temp_augmentation_rank{rank}"
         self.rng = np.random.default_rng(seed)
 
     # -- one augmented (image, mask) pair, uint8 numpy in / out

@@ -145,6 +145,27 @@ int b2seg_aug_remap_u8(const uint8_t* src, uint8_t* dst, int planes, int h, int 
                        int border_value, void* stream);
 
 /* ======================================================================== *
+ *  2b. Optimizer step (replaces torch.optim.Adam.step, train.py:49; the    *
+ *      optimizer the reference builds at train.py:331-335 and               *
+ *      cross_validation.py:93-97).                                          *
+ * ======================================================================== */
+/* One chunk of one parameter: n <= 2^31-1 consecutive fp32 elements of the parameter, its
+ * gradient and its two moment buffers.  The table lives in DEVICE memory. */
+typedef struct b2seg_adam_chunk {
+  float* p;
+  const float* g;
+  float* m; /* exp_avg */
+  float* v; /* exp_avg_sq */
+  int32_t n;
+  int32_t pad;
+} b2seg_adam_chunk;
+
+/* Adam (amsgrad = maximize = false) with L2 weight decay on every chunk, one launch of `nchunks`
+ * CTAs.  `step` is the 1-based step count t the bias corrections 1 - beta^t use. */
+int b2seg_adam_step(const b2seg_adam_chunk* chunks /*device*/, int nchunks, float lr, float beta1,
+                    float beta2, float eps, float weight_decay, double step, void* stream);
+
+/* ======================================================================== *
  *  3. Planned ops: created once per (pointers, shapes), replayed per step.  *
  *     TMA descriptors are encoded at creation, so run() is launch-only and  *
  *     CUDA-graph capturable.                                                 *

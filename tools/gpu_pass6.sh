@@ -1,0 +1,9 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 1500 python -m pytest tests -q -m gpu -x > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
+for FLAG in "--torch-adam" ""; do
+  timeout 900 python bench.py --no-cpu-baseline --steps 30 $FLAG > gpurun_out/bench_b64_adam$FLAG.json 2> gpurun_out/bench_b64_adam$FLAG.err; echo "bench '$FLAG' rc=$?"; tail -2 gpurun_out/bench_b64_adam$FLAG.err
+  python -c "
+import json;d=json.load(open('gpurun_out/bench_b64_adam$FLAG.json'));print('$FLAG value',d['value'],'ms',d['ms_per_step'],'e2e',d['e2e']['value'],'loss',d['final_loss'])"
+done
+python tools/step_segments.py 64 256 2>&1 | tail -10
