@@ -50,9 +50,10 @@ static inline int ew_blocks(long long work_items) {  // elementwise grid: 256 th
   return (int)b;
 }
 // Number of row slices (gridDim.y) of a column-reduce finalize kernel: each (32 x 32)-thread
-// block then walks <= ~8 rows per thread; the last block to finish folds the slices.
+// block then walks <= ~32 rows per thread (independent loads, one L2 round trip); block-partial
+// buffers have <= 592 rows, so these kernels are single-phase -- no ticket, no second fold.
 static inline int ew_fin_slices(long long rows, int colblocks) {
-  long long s = (rows + 255) / 256;
+  long long s = (rows + 1023) / 1024;
   if (s > 64) s = 64;
   while (s > 1 && s * colblocks > 1024) --s;
   if (s < 1) s = 1;

@@ -67,5 +67,5 @@ def test_training_reduces_loss_and_learns_masks(cuda):
         loss, stats = train_mod.train_step(model, imgs, masks, opt, crit)
         hist.append((float(loss), lossfn.metrics_dict(stats.cpu())["iou"]))
     assert all(np.isfinite(l) for l, _ in hist)
-    assert hist[-1][0] < 0.8 * hist[0][0], hist[::5]
-    assert hist[-1][1] > hist[0][1] + 0.1, hist[::5]
+    assert hist[-1][0] < 0.9 * hist[0][0], hist[::5]
+    assert hist[-1][1] > max(0.5, hist[0][1] + 0.3), hist[::5]
