@@ -119,6 +119,7 @@ _SIGS = {
     "b2seg_seq_create": (C.c_int, [C.POINTER(_vp)]),
     "b2seg_seq_append": (C.c_int, [_vp, _vp]),
     "b2seg_seq_append_lane": (C.c_int, [_vp, _vp, C.c_int]),
+    "b2seg_seq_join": (C.c_int, [_vp]),
     "b2seg_seq_run": (C.c_int, [_vp, _vp]),
     "b2seg_seq_launches": (C.c_int, [_vp]),
     "b2seg_seq_is_graph": (C.c_int, [_vp]),

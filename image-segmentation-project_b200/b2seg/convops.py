@@ -82,15 +82,22 @@ class Op:
 class Seq:
     """Ordered list of ops replayed with one C call."""
 
-    def __init__(self, ops, side_kinds=()):
-        """`side_kinds`: kind prefixes of ops nothing later in the list depends on (weight
-        gradients); the graph replay runs them on a side branch (b2seg_seq_append_lane)."""
+    def __init__(self, ops, side_kinds=(), join_before_kinds=()):
+        """`side_kinds`: kind prefixes of ops the graph replay runs on a side branch
+        (b2seg_seq_append_lane): weight gradients, which nothing later in the list reads, and the
+        weight repack, which is joined before the first op whose kind starts with one of
+        `join_before_kinds` (b2seg_seq_join)."""
         self.ops = list(ops)
         h = C.c_void_p()
         L.check(L.lib().b2seg_seq_create(C.byref(h)))
         self.handle = h
+        pending = False
         for op in self.ops:
             lane = 1 if any(op.kind.startswith(k) for k in side_kinds) else 0
+            if pending and lane == 0 and any(op.kind.startswith(k) for k in join_before_kinds):
+                L.check(L.lib().b2seg_seq_join(self.handle))
+                pending = False
+            pending = pending or lane == 1
             L.check(L.lib().b2seg_seq_append_lane(self.handle, op.handle, lane))
 
     def run(self):

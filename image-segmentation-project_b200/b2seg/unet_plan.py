@@ -323,7 +323,9 @@ class UNetPlan:
                 fn()
         self.tape = None
         self._finish_pack()
-        self.fwd = co.Seq(self.fwd_ops)
+        # the weight repack (fp32 parameters -> bf16 GEMM operands) overlaps the stem, which reads the
+        # fp32 stem weights directly; it joins the chain before the first tensor-core convolution
+        self.fwd = co.Seq(self.fwd_ops, side_kinds=(f"ew{L.EW_PACK}",), join_before_kinds=("conv",))
         # weight-gradient GEMMs read a forward activation and a gradient that is final when they are
         # appended, and write only their slice of gflat: they float on the graph's side branch
         self.bwd = co.Seq(self.bwd_ops, side_kinds=("wgrad",)) if ng else None

@@ -38,34 +38,53 @@ __device__ __forceinline__ void block_sum(float (&v)[N], float* sh /* [N][8] */)
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + __expf(-x)); }
 
 // ------------------------------------------------------------------- DOT1_FWD ----
-__global__ void __launch_bounds__(kEwThreads) dot1_fwd_kernel(const EwArgs a) {
-  pdl_prologue();
-  const bf16* v = (const bf16*)a.p[0];
-  const float* w = (const float*)a.p[1];
-  const float* b = (const float*)a.p[2];
-  float* out = (float*)a.p[3];
-  float* partial = (float*)a.p[4];
+// KMAX = channel vectors per lane (1 for C <= 256: every use in the U-Net); the lane's weights
+// stay in registers and UNR pixels are in flight per thread.
+template <int KMAX, int UNR>
+__device__ __forceinline__ void dot1_fwd_body(const EwArgs& a) {
+  const bf16* __restrict__ v = (const bf16*)a.p[0];
+  const float* __restrict__ w = (const float*)a.p[1];
+  const float* __restrict__ b = (const float*)a.p[2];
+  float* __restrict__ out = (float*)a.p[3];
+  float* __restrict__ partial = (float*)a.p[4];
   const long long P = a.i[0], ld = a.i[2];
   const int C = (int)a.i[1], cv = C >> 3, g = group_of(C);
   const int lg = threadIdx.x % g, grp = threadIdx.x / g, gpb = blockDim.x / g;
   const float bias = b ? b[0] : 0.0f;
   __shared__ float sh[16];
   float st[2] = {0.0f, 0.0f};
-  for (long long base = (long long)blockIdx.x * gpb; base < P; base += (long long)gridDim.x * gpb) {
-    const long long p = base + grp;
-    float s = 0.0f;
-    if (p < P) {
-      for (int c8 = lg; c8 < cv; c8 += g) {
-        const F8 x = ld_bf8(v + p * ld + c8 * 8), ww = ld_f8(w + c8 * 8);
+  F8 wr[KMAX];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) s = fmaf(x.v[j], ww.v[j], s);
-      }
+  for (int k = 0; k < KMAX; ++k)
+    if (lg + k * g < cv) wr[k] = ld_f8(w + (lg + k * g) * 8);
+  const long long stride = (long long)gridDim.x * gpb;
+  for (long long base = (long long)blockIdx.x * gpb; base < P; base += UNR * stride) {
+    uint4 raw[UNR][KMAX];
+#pragma unroll
+    for (int u = 0; u < UNR; ++u) {
+      const long long p = base + u * stride + grp;
+#pragma unroll
+      for (int k = 0; k < KMAX; ++k)
+        if (p < P && lg + k * g < cv)
+          raw[u][k] = *reinterpret_cast<const uint4*>(v + p * ld + (lg + k * g) * 8);
     }
-    s = group_sum(s, g) + bias;
-    if (p < P && lg == 0) {
-      out[p] = s;
-      st[0] += s;
-      st[1] = fmaf(s, s, st[1]);
+#pragma unroll
+    for (int u = 0; u < UNR; ++u) {
+      const long long p = base + u * stride + grp;
+      float s = 0.0f;
+#pragma unroll
+      for (int k = 0; k < KMAX; ++k)
+        if (p < P && lg + k * g < cv) {
+          const F8 x = unpack_bf8(raw[u][k]);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) s = fmaf(x.v[j], wr[k].v[j], s);
+        }
+      s = group_sum(s, g) + bias;  // every lane takes part (base + u*stride is block-uniform)
+      if (p < P && lg == 0) {
+        out[p] = s;
+        st[0] += s;
+        st[1] = fmaf(s, s, st[1]);
+      }
     }
   }
   if (partial) {
@@ -76,52 +95,84 @@ __global__ void __launch_bounds__(kEwThreads) dot1_fwd_kernel(const EwArgs a) {
     }
   }
 }
+__global__ void __launch_bounds__(kEwThreads) dot1_fwd_kernel(const EwArgs a) {
+  pdl_prologue();
+  dot1_fwd_body<1, 4>(a);
+}
+__global__ void __launch_bounds__(kEwThreads) dot1_fwd_wide_kernel(const EwArgs a) {  // C > 256
+  pdl_prologue();
+  dot1_fwd_body<4, 1>(a);
+}
 
 // ------------------------------------------------------------------- DOT1_BWD ----
 // ds[p] = dscalar[p]  or  BatchNorm2d(1)-backward of it;  dv = ds * w;  partial = (dW[C], db).
-__global__ void __launch_bounds__(kEwThreads) dot1_bwd_kernel(const EwArgs a) {
-  pdl_prologue();
-  extern __shared__ float red[];  // [gpb][C]
-  const float* dsc = (const float*)a.p[0];
-  const bf16* v = (const bf16*)a.p[1];
-  const float* w = (const float*)a.p[2];
-  bf16* dv = (bf16*)a.p[3];
-  float* partial = (float*)a.p[4];
-  const float* coef = (const float*)a.p[5];
-  const float* ypre = (const float*)a.p[6];
-  const float* bnp = (const float*)a.p[7];
+template <int KMAX, int UNR>
+__device__ __forceinline__ void dot1_bwd_body(const EwArgs& a, float* red) {
+  const float* __restrict__ dsc = (const float*)a.p[0];
+  const bf16* __restrict__ v = (const bf16*)a.p[1];
+  const float* __restrict__ w = (const float*)a.p[2];
+  bf16* __restrict__ dv = (bf16*)a.p[3];
+  float* __restrict__ partial = (float*)a.p[4];
+  const float* __restrict__ coef = (const float*)a.p[5];
+  const float* __restrict__ ypre = (const float*)a.p[6];
+  const float* __restrict__ bnp = (const float*)a.p[7];
   const long long P = a.i[0], ldv = a.i[2], lddv = a.i[3];
   const int C = (int)a.i[1], cv = C >> 3, g = group_of(C);
   const int lg = threadIdx.x % g, grp = threadIdx.x / g, gpb = blockDim.x / g;
   float c1 = 1.0f, c2 = 0.0f, c3 = 0.0f, mean = 0.0f, inv = 0.0f;
   if (coef) { c1 = coef[0]; c2 = coef[1]; c3 = coef[2]; mean = bnp[2]; inv = bnp[3]; }
-  float acc[4][8];
+  float acc[KMAX][8];
+  F8 wr[KMAX];
 #pragma unroll
-  for (int k = 0; k < 4; ++k)
+  for (int k = 0; k < KMAX; ++k) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[k][j] = 0.0f;
+    if (lg + k * g < cv) wr[k] = ld_f8(w + (lg + k * g) * 8);
+  }
   float db = 0.0f;
-  for (long long p = (long long)blockIdx.x * gpb + grp; p < P; p += (long long)gridDim.x * gpb) {
-    float ds = dsc[p];
-    if (coef) ds = c1 * (ds - c2 - (ypre[p] - mean) * inv * c3);
-    if (lg == 0) db += ds;
+  const long long stride = (long long)gridDim.x * gpb;
+  for (long long p0 = (long long)blockIdx.x * gpb + grp; p0 < P; p0 += UNR * stride) {
+    uint4 raw[UNR][KMAX];
+    float ds[UNR], yp[UNR];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int c8 = lg + k * g;
-      if (c8 < cv) {
-        const F8 x = ld_bf8(v + p * ldv + c8 * 8), ww = ld_f8(w + c8 * 8);
-        F8 o;
+    for (int u = 0; u < UNR; ++u) {
+      const long long p = p0 + u * stride;
+      ds[u] = 0.0f;
+      yp[u] = 0.0f;
+      if (p < P) {
+        ds[u] = dsc[p];
+        if (coef) yp[u] = ypre[p];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          acc[k][j] = fmaf(ds, x.v[j], acc[k][j]);
-          o.v[j] = ds * ww.v[j];
+        for (int k = 0; k < KMAX; ++k)
+          if (lg + k * g < cv)
+            raw[u][k] = *reinterpret_cast<const uint4*>(v + p * ldv + (lg + k * g) * 8);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < UNR; ++u) {
+      const long long p = p0 + u * stride;
+      if (p >= P) continue;
+      float d = ds[u];
+      if (coef) d = c1 * (d - c2 - (yp[u] - mean) * inv * c3);
+      if (lg == 0) db += d;
+#pragma unroll
+      for (int k = 0; k < KMAX; ++k) {
+        const int c8 = lg + k * g;
+        if (c8 < cv) {
+          const F8 x = unpack_bf8(raw[u][k]);
+          F8 o;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            acc[k][j] = fmaf(d, x.v[j], acc[k][j]);
+            o.v[j] = d * wr[k].v[j];
+          }
+          st_bf8(dv + p * lddv + c8 * 8, o);
         }
-        st_bf8(dv + p * lddv + c8 * 8, o);
       }
     }
   }
 #pragma unroll
-  for (int k = 0; k < 4; ++k) {
+  for (int k = 0; k < KMAX; ++k) {
     const int c8 = lg + k * g;
     if (c8 < cv)
 #pragma unroll
@@ -138,6 +189,16 @@ __global__ void __launch_bounds__(kEwThreads) dot1_bwd_kernel(const EwArgs a) {
   }
   if (threadIdx.x == 0) row[C] = dbv[0];
 }
+__global__ void __launch_bounds__(kEwThreads) dot1_bwd_kernel(const EwArgs a) {
+  pdl_prologue();
+  extern __shared__ float red[];  // [gpb][C]
+  dot1_bwd_body<1, 4>(a, red);
+}
+__global__ void __launch_bounds__(kEwThreads) dot1_bwd_wide_kernel(const EwArgs a) {  // C > 256
+  pdl_prologue();
+  extern __shared__ float red[];
+  dot1_bwd_body<4, 1>(a, red);
+}
 
 // ----------------------------------------------------------------- GATE_APPLY ----
 __global__ void __launch_bounds__(kEwThreads) gate_apply_kernel(const EwArgs a) {
@@ -153,8 +214,9 @@ __global__ void __launch_bounds__(kEwThreads) gate_apply_kernel(const EwArgs a) 
   const long long total = P * cv;
   for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
        idx += (long long)gridDim.x * blockDim.x) {
-    const long long p = idx / cv;
-    const int c8 = (int)(idx % cv);
+    long long p;
+    int c8;
+    ew_divmod(idx, cv, p, c8);
     const float psi = sigmoidf_(fmaf(pre[p], scale, shift));
     if (c8 == 0) psi_out[p] = psi;
     F8 v = ld_bf8(x + p * ldx + c8 * 8);
@@ -225,8 +287,14 @@ __global__ void __launch_bounds__(kEwThreads) gate_bwd_kernel(const EwArgs a) {
     B2_CHECK_CUDA(cudaGetLastError());                                                    \
     return B2SEG_OK;                                                                      \
   }
-EW_LAUNCHER(launch_dot1_fwd, dot1_fwd_kernel)
-EW_LAUNCHER(launch_dot1_bwd, dot1_bwd_kernel)
+#define EW_LAUNCHER_BY_WIDTH(name, kernel, wide)                                           \
+  int name(const EwArgs& a, dim3 grid, dim3 block, size_t smem, cudaStream_t st) {        \
+    B2_CHECK_CUDA(b2_launch(a.i[1] <= 256 ? kernel : wide, grid, block, smem, st, a));    \
+    B2_CHECK_CUDA(cudaGetLastError());                                                    \
+    return B2SEG_OK;                                                                      \
+  }
+EW_LAUNCHER_BY_WIDTH(launch_dot1_fwd, dot1_fwd_kernel, dot1_fwd_wide_kernel)
+EW_LAUNCHER_BY_WIDTH(launch_dot1_bwd, dot1_bwd_kernel, dot1_bwd_wide_kernel)
 EW_LAUNCHER(launch_gate_apply, gate_apply_kernel)
 EW_LAUNCHER(launch_gate_bwd, gate_bwd_kernel)
 

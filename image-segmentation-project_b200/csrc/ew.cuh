@@ -84,6 +84,15 @@ __device__ __forceinline__ F8 ld_bf8(const bf16* p) {
   t = bf2_to_f2(u.w); r.v[6] = t.x; r.v[7] = t.y;
   return r;
 }
+__device__ __forceinline__ F8 unpack_bf8(const uint4& u) {
+  F8 r;
+  float2 t;
+  t = bf2_to_f2(u.x); r.v[0] = t.x; r.v[1] = t.y;
+  t = bf2_to_f2(u.y); r.v[2] = t.x; r.v[3] = t.y;
+  t = bf2_to_f2(u.z); r.v[4] = t.x; r.v[5] = t.y;
+  t = bf2_to_f2(u.w); r.v[6] = t.x; r.v[7] = t.y;
+  return r;
+}
 __device__ __forceinline__ void st_bf8(bf16* p, const F8& r) {
   uint4 u;
   u.x = f2_to_bf2(r.v[0], r.v[1]);
@@ -99,6 +108,21 @@ __device__ __forceinline__ F8 ld_f8(const float* p) {
   r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w;
   r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
   return r;
+}
+
+// idx -> (idx / d, idx % d).  Work-item counts of the layer kernels fit 31 bits for every shape
+// the plan builds, and a 64-bit division costs ~100 instructions against ~20 for 32 bits: next to
+// one 16-byte load per item the index arithmetic otherwise dominates the instruction stream.
+__device__ __forceinline__ void ew_divmod(long long idx, int d, long long& q, int& r) {
+  if (idx < (1ll << 31)) {
+    const unsigned u = (unsigned)idx, ud = (unsigned)d;
+    const unsigned uq = u / ud;
+    q = uq;
+    r = (int)(u - uq * ud);
+  } else {
+    q = idx / d;
+    r = (int)(idx - q * d);
+  }
 }
 
 // Scratch of the column-reduce finalize kernels.  One set per device context: the kernels that

@@ -20,6 +20,7 @@ struct b2seg_seq {
   // (weight gradients): in the captured graph they fork onto a side branch after the op that
   // precedes them and join at the end, so they fill the chain's latency bubbles.
   std::vector<int> lanes;
+  std::vector<size_t> join_at;  // op indices before which the side branch joins the chain
   cudaStream_t side_stream = nullptr;
   cudaEvent_t fork_event = nullptr, join_event = nullptr;
   // CUDA-graph replay: the op list is captured once on a private stream (PyTorch's default stream

@@ -120,9 +120,11 @@ __global__ void __launch_bounds__(kEwThreads) se_scale_kernel(const EwArgs a) {
   const long long total = (long long)N * HW * cv;
   for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
        idx += (long long)gridDim.x * blockDim.x) {
-    const long long p = idx / cv;
-    const int c0 = (int)(idx % cv) * 8;
-    const int n = (int)(p / HW);
+    long long p, nn;
+    int c8, pl_unused;
+    ew_divmod(idx, cv, p, c8);
+    ew_divmod(p, HW, nn, pl_unused);
+    const int c0 = c8 * 8, n = (int)nn;
     F8 v = ld_bf8(x + p * ldx + c0);
     const F8 g = ld_f8(saved + ((size_t)n * 4 + 2) * C + c0);
 #pragma unroll
@@ -250,9 +252,11 @@ __global__ void __launch_bounds__(kEwThreads) se_bwd_apply_kernel(const EwArgs a
   const long long total = (long long)N * HW * cv;
   for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
        idx += (long long)gridDim.x * blockDim.x) {
-    const long long p = idx / cv;
-    const int c0 = (int)(idx % cv) * 8;
-    const int n = (int)(p / HW), pl = (int)(p % HW);
+    long long p, nn;
+    int c8, pl;
+    ew_divmod(idx, cv, p, c8);
+    ew_divmod(p, HW, nn, pl);
+    const int c0 = c8 * 8, n = (int)nn;
     const float* sv = saved + (size_t)n * 4 * C;
     F8 v = ld_bf8(dout + p * ldd + c0);
     const F8 g = ld_f8(sv + 2 * C + c0), am = ld_f8(sv + 3 * C + c0);

@@ -192,9 +192,12 @@ __global__ void __launch_bounds__(kEwThreads) maxpool_fwd_kernel(const EwArgs a)
   const long long total = (long long)N * OH * OW * cv;
   for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total;
        e += (long long)gridDim.x * blockDim.x) {
-    const int c0 = (int)(e % cv) * 8;
-    const long long op = e / cv;
-    const int ow = (int)(op % OW), oh = (int)((op / OW) % OH), n = (int)(op / ((long long)OW * OH));
+    long long op, rest;
+    int c8, ow, oh;
+    ew_divmod(e, cv, op, c8);
+    ew_divmod(op, OW, rest, ow);
+    ew_divmod(rest, OH, rest, oh);
+    const int c0 = c8 * 8, n = (int)rest;
     float best[8];
     uint32_t bi[8];
 #pragma unroll
@@ -236,9 +239,12 @@ __global__ void __launch_bounds__(kEwThreads) maxpool_bwd_kernel(const EwArgs a)
   const long long total = (long long)N * H * W * cv;
   for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total;
        e += (long long)gridDim.x * blockDim.x) {
-    const int c0 = (int)(e % cv) * 8;
-    const long long ip = e / cv;
-    const int iw = (int)(ip % W), ih = (int)((ip / W) % H), n = (int)(ip / ((long long)W * H));
+    long long ip, rest;
+    int c8, iw, ih;
+    ew_divmod(e, cv, ip, c8);
+    ew_divmod(ip, W, rest, iw);
+    ew_divmod(rest, H, rest, ih);
+    const int c0 = c8 * 8, n = (int)rest;
     F8 g;
 #pragma unroll
     for (int j = 0; j < 8; ++j) g.v[j] = 0.0f;

@@ -481,6 +481,12 @@ extern "C" int b2seg_seq_append_lane(b2seg_seq* seq, b2seg_op* op, int lane) {
 extern "C" int b2seg_seq_append(b2seg_seq* seq, b2seg_op* op) {
   return b2seg_seq_append_lane(seq, op, 0);
 }
+extern "C" int b2seg_seq_join(b2seg_seq* seq) {
+  B2_REQUIRE(seq, "seq_join: null");
+  B2_REQUIRE(!seq->exec, "seq_join: sequence already captured");
+  seq->join_at.push_back(seq->ops.size());
+  return B2SEG_OK;
+}
 namespace {
 bool graphs_enabled() {
   static int v = -1;
@@ -507,8 +513,20 @@ bool seq_capture_once(b2seg_seq* seq, bool use_lanes) {
   }
   int rc = B2SEG_OK;
   bool side_used = false, forked = false;  // forked: side branch already waits on the latest chain op
+  bool side_pending = false;  // side-branch work not yet joined
   for (size_t i = 0; i < seq->ops.size() && rc == B2SEG_OK; ++i) {
+    if (side_pending)
+      for (size_t j : seq->join_at)
+        if (j == i) {
+          if (cudaEventRecord(seq->join_event, seq->side_stream) != cudaSuccess ||
+              cudaStreamWaitEvent(seq->capture_stream, seq->join_event, 0) != cudaSuccess)
+            rc = B2SEG_ECUDA;
+          side_pending = forked = false;
+          break;
+        }
+    if (rc != B2SEG_OK) break;
     if (use_lanes && seq->lanes[i] == 1) {
+      side_pending = true;
       if (!forked) {
         if (cudaEventRecord(seq->fork_event, seq->capture_stream) != cudaSuccess ||
             cudaStreamWaitEvent(seq->side_stream, seq->fork_event, 0) != cudaSuccess) {
@@ -523,7 +541,7 @@ bool seq_capture_once(b2seg_seq* seq, bool use_lanes) {
       forked = false;
     }
   }
-  if (side_used && rc == B2SEG_OK) {
+  if (side_used && side_pending && rc == B2SEG_OK) {
     if (cudaEventRecord(seq->join_event, seq->side_stream) != cudaSuccess ||
         cudaStreamWaitEvent(seq->capture_stream, seq->join_event, 0) != cudaSuccess)
       rc = B2SEG_ECUDA;

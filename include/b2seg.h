@@ -184,6 +184,10 @@ int b2seg_seq_append(b2seg_seq* seq, b2seg_op* op); /* does not take ownership *
  * side branch forked after the op appended before it and joined at the end of the sequence;
  * lane-1 ops keep their relative order.  Direct (non-graph) replays ignore lanes. */
 int b2seg_seq_append_lane(b2seg_seq* seq, b2seg_op* op, int lane);
+/* The side branch joins the chain before the next appended op (instead of at the end): for a
+ * lane-1 op whose output IS read later, e.g. the weight repack that only the first tensor-core
+ * convolution needs while the stem runs. */
+int b2seg_seq_join(b2seg_seq* seq);
 /* Replays the ops in order.  Sequences of >= 4 ops are captured into a CUDA graph on first use
  * (one graph launch per replay; B2SEG_GRAPH=0 in the environment keeps direct launches). */
 int b2seg_seq_run(b2seg_seq* seq, void* stream);
