@@ -227,7 +227,7 @@ def run_b200(a):
     opt = (torch.optim.Adam if a.torch_adam else FusedAdam)(model.parameters(), lr=1e-3, weight_decay=1e-5)
     if a.mode == "dp" and world > 1:
         from b2seg import dataparallel
-        dataparallel.attach(model, world)
+        dataparallel.attach(model, world, criterion=crit)  # global-batch loss, summed gradients
     model.train()
 
     # synthetic pool: POOL distinct batches, pinned on the host and resident on the device

@@ -106,6 +106,7 @@ _SIGS = {
     "b2seg_device_info": (C.c_int, [C.c_char_p, _i, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "b2seg_seg_reduce_workspace_bytes": (_sz, []),
     "b2seg_seg_loss_fwd": (C.c_int, [_vp, _vp, _vp, _i64, C.POINTER(LossSpec), _vp, _vp, _vp, _vp, _vp]),
+    "b2seg_seg_loss_finish": (C.c_int, [C.POINTER(LossSpec), _i64, _vp, _vp, _vp, _vp]),
     "b2seg_seg_loss_bwd": (C.c_int, [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp]),
     "b2seg_seg_metrics_from_probs": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _vp]),
     "b2seg_aug_permute_u8": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),

@@ -7,14 +7,21 @@ term is ~0.2 ms and launch latency dominates, which is why there is one bucket, 
 BatchNorm stays per replica, as in the reference (it has no SyncBN).
 
 The reference has no data-parallel path at all; this is the B200 addition
-`north_star` asks for.  Gradients are averaged, matching a mean-reduced loss over the global
-batch for the shard-decomposable losses (BCE, focal); Dice/Tversky terms normalise per replica.
+`north_star` asks for.  Two modes:
+  * `attach(model)`: every replica evaluates its loss on its own shard and the gradients are
+    AVERAGED -- exact for the shard-decomposable losses (BCE, focal) with equal shards; Dice /
+    Tversky terms then normalise per replica.
+  * `attach(model, criterion=crit)`: the fused loss all-reduces its eight sums and the pixel count
+    (72 bytes) between its reduction and its evaluation (lossfn.loss_forward(group=...)), so the
+    loss value, the confusion counts and the per-pixel gradient are those of the GLOBAL batch and
+    the replica gradients are SUMMED -- the single-process semantics of every closed-form loss
+    (losses.py:21-27, 99-107 normalise by whole-batch totals).
 """
 import torch
 import torch.distributed as dist
 
 
-def attach(model, world_size=None, group=None):
+def attach(model, world_size=None, group=None, criterion=None):
     """Install the flat-gradient all-reduce on `model` and make all replicas start identical."""
     world = world_size or dist.get_world_size(group)
     if world <= 1:
@@ -22,16 +29,24 @@ def attach(model, world_size=None, group=None):
     with torch.no_grad():
         for t in list(model.parameters()) + list(model.buffers()):
             dist.broadcast(t, src=0, group=group)
+    global_loss = criterion is not None
+    if global_loss:
+        if not hasattr(criterion, "dp_group"):
+            raise TypeError("criterion must be one of the fused losses of losses.py")
+        criterion.dp_group = group if group is not None else dist.group.WORLD
     inv = 1.0 / world
 
     def hook(gflat):
         dist.all_reduce(gflat, op=dist.ReduceOp.SUM, group=group)
-        gflat.mul_(inv)
+        if not global_loss:
+            gflat.mul_(inv)
 
     model._grad_hook = hook
     return model
 
 
-def detach(model):
+def detach(model, criterion=None):
     model._grad_hook = None
+    if criterion is not None:
+        criterion.dp_group = None
     return model

@@ -51,8 +51,12 @@ def _flat_f32(t: torch.Tensor) -> torch.Tensor:
     return t.contiguous()
 
 
-def loss_forward(logits, target, spec: L.LossSpec, weight_map=None):
-    """Returns (loss[0-dim f32], stats[16 f64], coef[8 f32]) — all device tensors."""
+def loss_forward(logits, target, spec: L.LossSpec, weight_map=None, group=None):
+    """Returns (loss[0-dim f32], stats[16 f64], coef[8 f32]) — all device tensors.
+    `group`: a torch.distributed process group of data-parallel replicas; the eight sums and the
+    pixel count are all-reduced between the reduction and the loss evaluation, so the value and
+    the gradient coefficients are those of the GLOBAL batch (exact single-process semantics for
+    Dice / Tversky, whose ratios do not decompose over shards)."""
     L.require_cuda(logits, target, weight_map)
     x, t = _flat_f32(logits), _flat_f32(target)
     if x.numel() != t.numel():
@@ -67,6 +71,11 @@ def loss_forward(logits, target, spec: L.LossSpec, weight_map=None):
         x.data_ptr(), t.data_ptr(), wm.data_ptr() if wm is not None else None, x.numel(),
         C.byref(spec), _Scratch.get(dev).data_ptr(), out.data_ptr(), small.data_ptr(),
         small.data_ptr() + 4, L.stream_ptr()))
+    if group is not None:
+        import torch.distributed as dist
+        dist.all_reduce(out[:L.S_N + 1], op=dist.ReduceOp.SUM, group=group)
+        L.check(L.lib().b2seg_seg_loss_finish(C.byref(spec), 0, out.data_ptr(), small.data_ptr(),
+                                              small.data_ptr() + 4, L.stream_ptr()))
     return small[0], out, small[1:], (x, t, wm)
 
 
@@ -84,8 +93,8 @@ class FusedSegLoss(torch.autograd.Function):
     """loss, stats = FusedSegLoss.apply(logits, target, spec, weight_map)"""
 
     @staticmethod
-    def forward(ctx, logits, target, spec, weight_map=None):
-        loss, stats, coef, saved = loss_forward(logits, target, spec, weight_map)
+    def forward(ctx, logits, target, spec, weight_map=None, group=None):
+        loss, stats, coef, saved = loss_forward(logits, target, spec, weight_map, group)
         ctx.saved = saved
         ctx.coef = coef
         ctx.shape = logits.shape
@@ -95,7 +104,7 @@ class FusedSegLoss(torch.autograd.Function):
     @staticmethod
     def backward(ctx, grad_loss, _grad_stats):
         g = loss_backward(ctx.saved, ctx.coef, grad_loss, ctx.shape)
-        return g, None, None, None
+        return g, None, None, None, None
 
 
 def metrics_from_probs(probs, target) -> torch.Tensor:

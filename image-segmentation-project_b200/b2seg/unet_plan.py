@@ -199,7 +199,7 @@ class UNetPlan:
         self.B(eo.ew(L.EW_BN_BWD_FINALIZE,
                      p=[self.part, self.params[prefix + ".weight"], bnp, self.gview(prefix + ".weight"),
                         self.gview(prefix + ".bias"), coef, dbias],
-                     i=[rows, C_, P, 0, 1 if self.training else 0]))
+                     i=[rows, C_, P, 0, 1 if self.training else 0, 1]))  # i5: partial holds sum dz*y
         self.B(eo.ew(L.EW_BN_BWD_APPLY, p=pp + [coef, dy, dz],
                      i=ii + [dy.sw, dz.sw if dz else 0, 2 if dz_acc else 1, 1 if self_mask else 0]))
 

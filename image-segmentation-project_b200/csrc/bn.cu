@@ -168,19 +168,6 @@ __device__ __forceinline__ BnBwdIn bn_bwd_in(const EwArgs& a) {
   s.self_mask = (int)a.i[9];
   return s;
 }
-struct BnBwdCh {
-  F8 sc, sf, mean, inv;
-};
-__device__ __forceinline__ BnBwdCh bn_bwd_ch(const BnBwdIn& s, int c0) {
-  BnBwdCh ch;
-  if (s.self_mask) {
-    ch.sc = ld_f8(s.bnp + c0);
-    ch.sf = ld_f8(s.bnp + s.C + c0);
-  }
-  ch.mean = ld_f8(s.bnp + 2 * s.C + c0);
-  ch.inv = ld_f8(s.bnp + 3 * s.C + c0);
-  return ch;
-}
 // one pixel's operands as loaded (packed bf16: 4 registers per 8 channels until they are used)
 struct BnBwdRaw {
   uint4 d1, d2, m, y, old;
@@ -193,9 +180,9 @@ __device__ __forceinline__ BnBwdRaw bn_bwd_fetch(const BnBwdIn& s, long long p, 
   r.y = bn_ld_raw8(s.y + p * s.ldy + c0);
   return r;
 }
-// dz = (da1 [+ da2]) * [act > 0];  yhat = (y - mean) * invstd
-__device__ __forceinline__ void bn_bwd_math(const BnBwdIn& s, const BnBwdCh& ch, const BnBwdRaw& r,
-                                            F8& dz, F8& yh) {
+// dz = (da1 [+ da2]) * [a > 0] and the raw pre-BN value y of one pixel's 8 channels.
+__device__ __forceinline__ void bn_bwd_dz(const BnBwdIn& s, const F8& sc, const F8& sf, const BnBwdRaw& r,
+                                          F8& dz, F8& y) {
   dz = bn_unpack8(r.d1);
   if (s.da2) {
     const F8 d2 = bn_unpack8(r.d2);
@@ -207,32 +194,38 @@ __device__ __forceinline__ void bn_bwd_math(const BnBwdIn& s, const BnBwdCh& ch,
 #pragma unroll
     for (int j = 0; j < 8; ++j) dz.v[j] = m.v[j] > 0.0f ? dz.v[j] : 0.0f;
   }
-  const F8 y = bn_unpack8(r.y);
+  y = bn_unpack8(r.y);
   if (s.self_mask) {  // the forward pass stored bf16(relu(fma(y, scale, shift))): same arithmetic here
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const float act = __bfloat162float(__float2bfloat16_rn(fmaf(y.v[j], ch.sc.v[j], ch.sf.v[j])));
+      const float act = __bfloat162float(__float2bfloat16_rn(fmaf(y.v[j], sc.v[j], sf.v[j])));
       dz.v[j] = act > 0.0f ? dz.v[j] : 0.0f;
     }
   }
-#pragma unroll
-  for (int j = 0; j < 8; ++j) yh.v[j] = (y.v[j] - ch.mean.v[j]) * ch.inv.v[j];
 }
 
+// Block partials of (sum dz, sum dz*y).  The normalised form sum dz*yhat = invstd * (sum dz*y -
+// mean * sum dz) is taken in fp64 by BN_BWD_FINALIZE (i5 = 1): the streaming loop then carries no
+// per-channel mean / invstd (16 registers less, more loads in flight).
 __global__ void __launch_bounds__(kEwThreads) bn_bwd_reduce_kernel(const EwArgs a) {
   pdl_prologue();
   extern __shared__ float red[];
   const BnBwdIn s = bn_bwd_in(a);
   // ew_channel_reduce gives every thread one fixed channel vector: constants loaded once
-  const BnBwdCh ch = bn_bwd_ch(s, (int)(threadIdx.x % (s.C >> 3)) * 8);
+  const int c0t = (int)(threadIdx.x % (s.C >> 3)) * 8;
+  F8 sc, sf;
+  if (s.self_mask) {
+    sc = ld_f8(s.bnp + c0t);
+    sf = ld_f8(s.bnp + s.C + c0t);
+  }
   ew_channel_reduce<2>(0, a.i[0], s.C, (float*)a.p[5], red,
                        [&](long long p, int c0, float (&acc)[2][8]) {
-                         F8 dz, yh;
-                         bn_bwd_math(s, ch, bn_bwd_fetch(s, p, c0), dz, yh);
+                         F8 dz, y;
+                         bn_bwd_dz(s, sc, sf, bn_bwd_fetch(s, p, c0), dz, y);
 #pragma unroll
                          for (int j = 0; j < 8; ++j) {
                            acc[0][j] += dz.v[j];
-                           acc[1][j] = fmaf(dz.v[j], yh.v[j], acc[1][j]);
+                           acc[1][j] = fmaf(dz.v[j], y.v[j], acc[1][j]);
                          }
                        });
 }
@@ -248,9 +241,11 @@ __global__ void __launch_bounds__(1024) bn_bwd_finalize_kernel(const EwArgs a) {
   float* dbias = (float*)a.p[6];
   const int rows = (int)a.i[0], C = (int)a.i[1];
   const double count = (double)a.i[2];
-  const bool accumulate = a.i[3] != 0, training = a.i[4] != 0;
+  const bool accumulate = a.i[3] != 0, training = a.i[4] != 0, raw_q = a.i[5] != 0;
   ew_rows_reduce<2>(partial, rows, 2 * (long long)C, C, C, [&](int c, const double* v) {
-    const double s = v[0], q = v[1];
+    const double s = v[0];
+    // raw_q: the second accumulator is sum dz*y; sum dz*yhat = invstd * (sum dz*y - mean * sum dz)
+    const double q = raw_q ? (double)bnp[3 * C + c] * (v[1] - (double)bnp[2 * C + c] * s) : v[1];
     const float g = gamma ? gamma[c] : 1.0f;
     const float c1 = g * bnp[3 * C + c];
     if (dgamma) dgamma[c] = accumulate ? dgamma[c] + (float)q : (float)q;
@@ -265,16 +260,36 @@ __global__ void __launch_bounds__(1024) bn_bwd_finalize_kernel(const EwArgs a) {
   });
 }
 
-struct BnBwdCoef {
-  F8 c1, c2, c3;
+// dy = c1*(dz - c2 - yhat*c3) with yhat = (y - mean)*invstd, folded per channel into
+// dy = A*dz + B*y + D:  A = c1,  B = -c1*c3*invstd,  D = c1*(c3*invstd*mean - c2).
+struct BnBwdLin {
+  F8 A, B, D, sc, sf;
 };
-__device__ __forceinline__ void bn_bwd_apply_store(const BnBwdIn& s, const BnBwdCh& ch, const BnBwdCoef& k,
-                                                   const BnBwdRaw& r, bool dz_acc, long long p, int c0,
-                                                   bf16* dy, long long lddy, bf16* dzo, long long lddz) {
-  F8 dz, yh, o;
-  bn_bwd_math(s, ch, r, dz, yh);
+__device__ __forceinline__ BnBwdLin bn_bwd_lin(const BnBwdIn& s, const float* coef, int c0) {
+  BnBwdLin k;
+  const int C = s.C;
+  const F8 c1 = ld_f8(coef + c0), c2 = ld_f8(coef + C + c0), c3 = ld_f8(coef + 2 * C + c0);
+  const F8 mean = ld_f8(s.bnp + 2 * C + c0), inv = ld_f8(s.bnp + 3 * C + c0);
 #pragma unroll
-  for (int j = 0; j < 8; ++j) o.v[j] = k.c1.v[j] * (dz.v[j] - k.c2.v[j] - yh.v[j] * k.c3.v[j]);
+  for (int j = 0; j < 8; ++j) {
+    const float t = c3.v[j] * inv.v[j];
+    k.A.v[j] = c1.v[j];
+    k.B.v[j] = -c1.v[j] * t;
+    k.D.v[j] = c1.v[j] * (t * mean.v[j] - c2.v[j]);
+  }
+  if (s.self_mask) {
+    k.sc = ld_f8(s.bnp + c0);
+    k.sf = ld_f8(s.bnp + C + c0);
+  }
+  return k;
+}
+__device__ __forceinline__ void bn_bwd_apply_store(const BnBwdIn& s, const BnBwdLin& k, const BnBwdRaw& r,
+                                                   bool dz_acc, long long p, int c0, bf16* dy,
+                                                   long long lddy, bf16* dzo, long long lddz) {
+  F8 dz, y, o;
+  bn_bwd_dz(s, k.sc, k.sf, r, dz, y);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) o.v[j] = fmaf(k.A.v[j], dz.v[j], fmaf(k.B.v[j], y.v[j], k.D.v[j]));
   st_bf8(dy + p * lddy + c0, o);
   if (dzo) {
     if (dz_acc) {
@@ -299,38 +314,38 @@ __global__ void __launch_bounds__(kEwThreads) bn_bwd_apply_kernel(const EwArgs a
     const int ppb = kEwThreads / cv;
     const int c0 = (threadIdx.x % cv) * 8;
     const long long pstep = (long long)gridDim.x * ppb;
-    const BnBwdCh ch = bn_bwd_ch(s, c0);
-    BnBwdCoef k;
-    k.c1 = ld_f8(coef + c0); k.c2 = ld_f8(coef + C + c0); k.c3 = ld_f8(coef + 2 * C + c0);
+    const BnBwdLin k = bn_bwd_lin(s, coef, c0);
     long long p = (long long)blockIdx.x * ppb + threadIdx.x / cv;
-    for (; p + pstep < P; p += 2 * pstep) {
-      const long long q = p + pstep;
-      BnBwdRaw r0 = bn_bwd_fetch(s, p, c0), r1 = bn_bwd_fetch(s, q, c0);
-      if (dz_acc) {
-        r0.old = bn_ld_raw8(dzo + p * lddz + c0);
-        r1.old = bn_ld_raw8(dzo + q * lddz + c0);
+    constexpr int U = 3;  // pixels in flight per thread
+    for (; p + (U - 1) * pstep < P; p += U * pstep) {
+      BnBwdRaw r[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        r[u] = bn_bwd_fetch(s, p + u * pstep, c0);
+        if (dz_acc) r[u].old = bn_ld_raw8(dzo + (p + u * pstep) * lddz + c0);
       }
-      bn_bwd_apply_store(s, ch, k, r0, dz_acc, p, c0, dy, lddy, dzo, lddz);
-      bn_bwd_apply_store(s, ch, k, r1, dz_acc, q, c0, dy, lddy, dzo, lddz);
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        bn_bwd_apply_store(s, k, r[u], dz_acc, p + u * pstep, c0, dy, lddy, dzo, lddz);
     }
-    if (p < P) {
+    for (; p < P; p += pstep) {
       BnBwdRaw r0 = bn_bwd_fetch(s, p, c0);
       if (dz_acc) r0.old = bn_ld_raw8(dzo + p * lddz + c0);
-      bn_bwd_apply_store(s, ch, k, r0, dz_acc, p, c0, dy, lddy, dzo, lddz);
+      bn_bwd_apply_store(s, k, r0, dz_acc, p, c0, dy, lddy, dzo, lddz);
     }
     return;
   }
   const long long total = P * cv;
   for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
        idx += (long long)gridDim.x * blockDim.x) {
-    const long long p = idx / cv;
-    const int c0 = (int)(idx % cv) * 8;
-    const BnBwdCh ch = bn_bwd_ch(s, c0);
-    BnBwdCoef k;
-    k.c1 = ld_f8(coef + c0); k.c2 = ld_f8(coef + C + c0); k.c3 = ld_f8(coef + 2 * C + c0);
+    long long p;
+    int c8;
+    ew_divmod(idx, cv, p, c8);
+    const int c0 = c8 * 8;
+    const BnBwdLin k = bn_bwd_lin(s, coef, c0);
     BnBwdRaw r0 = bn_bwd_fetch(s, p, c0);
     if (dz_acc) r0.old = bn_ld_raw8(dzo + p * lddz + c0);
-    bn_bwd_apply_store(s, ch, k, r0, dz_acc, p, c0, dy, lddy, dzo, lddz);
+    bn_bwd_apply_store(s, k, r0, dz_acc, p, c0, dy, lddy, dzo, lddz);
   }
 }
 

@@ -515,15 +515,40 @@ extern "C" int b2seg_seg_loss_bwd(const float* logits, const float* target,
                    (!wmap || aligned16(weight_map));
   const int blocks = pick_blocks(n, 8);
   cudaStream_t st = (cudaStream_t)stream;
-  // The focal branch is selected on the host from nothing but pointers, so the
-  // general kernel is always used: F == 0 makes the focal term vanish and costs
-  // only ALU in an HBM-bound pass.
+  // The focal coefficient lives on the device: the kernel branches once, uniformly, between its
+  // focal and focal-free bodies (the first template argument is unused).
 #define LAUNCH(W, V)                                                                        \
   seg_loss_bwd_kernel<true, W, V><<<blocks, kThreads, 0, st>>>(logits, target, weight_map, n, \
                                                                coef, grad_out, grad_logits)
   if (wmap) { if (vec) LAUNCH(true, true); else LAUNCH(true, false); }
   else      { if (vec) LAUNCH(false, true); else LAUNCH(false, false); }
 #undef LAUNCH
+  B2_CHECK_CUDA(cudaGetLastError());
+  return B2SEG_OK;
+}
+
+// Loss value and gradient coefficients from given sums (stats[0..7]) of `n` pixels: the second
+// half of the forward kernel as its own launch, for sums that were combined across data-parallel
+// replicas after the local reduction (Dice / Tversky normalise by global-batch totals).
+namespace {
+__global__ void seg_loss_finish_kernel(LossSpecDev spec, double n, double* stats, float* loss_out,
+                                       float* coef) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    double tot[kAcc];
+    for (int i = 0; i < kAcc; ++i) tot[i] = stats[i];
+    if (n <= 0.0) n = stats[B2SEG_S_N];  // pixel count summed on the device with the other sums
+    finish_loss(spec.s, tot, n, stats, loss_out, coef);
+  }
+}
+}  // namespace
+
+extern "C" int b2seg_seg_loss_finish(const b2seg_loss_spec* spec, int64_t n_total, double* stats,
+                                     float* loss_out, float* coef, void* stream) {
+  B2_REQUIRE(spec && stats && loss_out && coef, "seg_loss_finish: null argument");
+  B2_REQUIRE(n_total >= 0, "seg_loss_finish: n must be >= 0 (got %lld)", (long long)n_total);
+  LossSpecDev sd;
+  sd.s = *spec;
+  seg_loss_finish_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(sd, (double)n_total, stats, loss_out, coef);
   B2_CHECK_CUDA(cudaGetLastError());
   return B2SEG_OK;
 }

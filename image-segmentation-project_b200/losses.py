@@ -28,6 +28,7 @@ class _FusedLoss(nn.Module):
         super().__init__()
         self.last_stats = None
         self.last_logits_ref = None
+        self.dp_group = None  # set by b2seg.dataparallel.attach: global-batch loss across replicas
 
     def _spec(self):
         raise NotImplementedError
@@ -36,7 +37,8 @@ class _FusedLoss(nn.Module):
         return None
 
     def forward(self, pred, target):
-        loss, stats = lossfn.FusedSegLoss.apply(pred, target, self._spec(), self._weight_map(pred, target))
+        loss, stats = lossfn.FusedSegLoss.apply(pred, target, self._spec(), self._weight_map(pred, target),
+                                                self.dp_group)
         self.last_stats = stats
         self.last_logits_ref = pred
         return loss

@@ -106,6 +106,15 @@ int b2seg_seg_loss_bwd(const float* logits, const float* target, const float* we
                        int64_t n, const float* coef, const float* grad_out, float* grad_logits,
                        void* stream);
 
+/* Second half of b2seg_seg_loss_fwd as its own launch: loss, gradient coefficients and the
+ * confusion block from the eight sums in stats[0..7] over n_total pixels.  Data-parallel replicas
+ * all-reduce stats[0..8] (sums and pixel count) after their local forward and call this with
+ * n_total = 0 (= take the count from stats[B2SEG_S_N]; no host round trip), so
+ * Dice / Tversky / balanced-BCE terms see the whole batch exactly as the single-process
+ * reference does (losses.py:21-27, 99-107). */
+int b2seg_seg_loss_finish(const b2seg_loss_spec* spec, int64_t n_total, double* stats /*in/out [16]*/,
+                          float* loss_out, float* coef /*[8]*/, void* stream);
+
 /* calculate_metrics(pred, target) of utils.py:120-151: `probs` are
  * probabilities; fills stats[S_PB, S_PB_T, S_T, S_N, S_TP..S_TN]. */
 int b2seg_seg_metrics_from_probs(const float* probs, const float* target, int64_t n,
@@ -306,7 +315,8 @@ enum {
    * p0 y bf16  p1 bnp  p2 out bf16  p3 res bf16|NULL  p4 res bnp|NULL
    * i0 P  i1 C  i2 ld_y  i3 ld_out  i4 ld_res  i5 relu */
   B2SEG_EW_BN_APPLY = 2,
-  /* BatchNorm backward phase 1: dz = (da1 [+ da2]) * [a > 0]; block partials of (dz, dz*yhat).
+  /* BatchNorm backward phase 1: dz = (da1 [+ da2]) * [a > 0]; block partials of (dz, dz*y) -- the
+   * RAW pre-BN y; BN_BWD_FINALIZE with i5 = 1 turns them into (sum dz, sum dz*yhat).
    * p0 da1 bf16  p1 da2 bf16|NULL  p2 a bf16|NULL (ReLU mask source)  p3 y bf16 (pre-BN)  p4 bnp
    * p5 out partial f32 [rows][2][C], rows = b2seg_ew_partial_rows(kind, P, C)
    * i0 P  i1 C  i2 ld_da1  i3 ld_da2  i4 ld_a  i5 ld_y
@@ -315,7 +325,8 @@ enum {
   B2SEG_EW_BN_BWD_REDUCE = 3,
   /* p0 partial  p1 gamma|NULL  p2 bnp  p3 dgamma f32|NULL  p4 dbeta f32|NULL  p5 out coef f32 [3][C]
    * p6 dbias f32|NULL (gradient of a conv bias feeding this BN: 0 with batch statistics)
-   * i0 rows  i1 C  i2 count  i3 accumulate into dgamma/dbeta/dbias  i4 training */
+   * i0 rows  i1 C  i2 count  i3 accumulate into dgamma/dbeta/dbias  i4 training
+   * i5 the second accumulator of `partial` is sum dz*y (BN_BWD_REDUCE), not sum dz*yhat */
   B2SEG_EW_BN_BWD_FINALIZE = 4,
   /* phase 2: dy = c1*(dz - c2 - yhat*c3) -> bf16; optionally also emits dz (residual branch).
    * p0..p4 as BN_BWD_REDUCE  p5 coef  p6 dy bf16  p7 dz bf16|NULL

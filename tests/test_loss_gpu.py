@@ -91,6 +91,40 @@ def test_soft_targets(cuda):
         np.testing.assert_allclose(gd.cpu().numpy(), go.numpy(), rtol=3e-4, atol=1e-8, err_msg=name)
 
 
+def test_global_batch_loss_across_replicas(cuda):
+    """Data-parallel exactness: each replica reduces its shard, the eight sums and
+    the pixel count are added (what the NCCL all-reduce does) and b2seg_seg_loss_finish evaluates
+    the loss on the totals -- value, confusion counts and per-pixel gradient must equal the
+    single-process loss on the whole batch, for losses whose ratios do not decompose over shards."""
+    import ctypes as C
+    import losses
+    from b2seg import lossfn, _lib as L
+    logits, target = seg_losses.kat_inputs((4, 1, 64, 96))
+    x, t = logits.to(cuda), target.to(cuda)
+    shards = [(x[:1], t[:1]), (x[1:], t[1:])]  # unequal shards: the pixel count is summed too
+    for name in ("dice", "tversky_recall", "combo", "balanced_bce", "focal", "sensitivity_specificity"):
+        spec = losses.get_loss_function({"loss_fn": name})._spec()
+        full_loss, full_stats, full_coef, saved = lossfn.loss_forward(x, t, spec)
+        g_full = lossfn.loss_backward(saved, full_coef, None, x.shape)
+        parts = [lossfn.loss_forward(xs, ts, spec) for xs, ts in shards]
+        tot = torch.zeros(L.STATS_LEN, dtype=torch.float64, device=cuda)
+        tot[:L.S_N + 1] = sum(p[1][:L.S_N + 1] for p in parts)
+        small = torch.empty(1 + L.COEF_LEN, dtype=torch.float32, device=cuda)
+        L.check(L.lib().b2seg_seg_loss_finish(C.byref(spec), 0, tot.data_ptr(), small.data_ptr(),
+                                              small.data_ptr() + 4, L.stream_ptr()))
+        assert float(small[0]) == pytest.approx(float(full_loss), rel=1e-6), name
+        assert float(tot[L.S_N]) == x.numel()
+        for i in (L.S_TP, L.S_FP, L.S_FN, L.S_TN):
+            assert float(tot[i]) == float(full_stats[i]), (name, i)
+        g_parts = torch.cat([lossfn.loss_backward(p[3], small[1:], None, xs.shape)
+                             for p, (xs, _) in zip(parts, shards)])
+        torch.testing.assert_close(g_parts, g_full, rtol=1e-5, atol=1e-10)
+        # the same loss evaluated per shard and averaged is NOT the global loss for ratio losses
+        if name == "dice":
+            per_shard = sum(float(p[0]) for p in parts) / 2
+            assert abs(per_shard - float(full_loss)) > 1e-4
+
+
 def test_metrics_match_fixture_and_counts_are_exact(cuda, loss_kat):
     import utils
     logits, target = seg_losses.kat_inputs((4, 1, 256, 256))
