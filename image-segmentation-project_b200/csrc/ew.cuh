@@ -39,12 +39,16 @@ static inline int ew_rows(long long P, int C) {
   const long long per = (long long)ew_pl(C) * 8;
   long long r = (P + per - 1) / per;
   if (r < 1) r = 1;
-  if (r > B2SEG_EW_MAX_PARTIAL_ROWS) r = B2SEG_EW_MAX_PARTIAL_ROWS;
+  // one block per partial row: at most 3 resident 256-thread blocks per SM (76-101 registers),
+  // so more rows than 3 x SMs would run as a second, mostly empty wave
+  long long cap = 3ll * b2_num_sms();
+  if (cap > B2SEG_EW_MAX_PARTIAL_ROWS) cap = B2SEG_EW_MAX_PARTIAL_ROWS;
+  if (r > cap) r = cap;
   return (int)r;
 }
 static inline int ew_blocks(long long work_items) {  // elementwise grid: 256 threads, grid-stride
   long long b = (work_items + kEwThreads - 1) / kEwThreads;
-  const long long cap = (long long)b2_num_sms() * 16;
+  const long long cap = (long long)b2_num_sms() * 12;  // whole waves at 2, 3, 4 or 6 blocks per SM
   if (b > cap) b = cap;
   if (b < 1) b = 1;
   return (int)b;

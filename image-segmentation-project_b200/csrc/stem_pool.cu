@@ -4,6 +4,8 @@
 // K = 49 is too thin for a tensor-core tile and the layer is bandwidth/latency bound, so it is a
 // direct convolution on the CUDA cores: a block computes an 8x16 brick of output pixels from a
 // 21x37 input patch staged in shared memory; each thread owns one pixel x 32 channels.
+#include <stdlib.h>
+
 #include "ew.cuh"
 
 namespace {
@@ -297,6 +299,13 @@ extern "C" int b2seg_stem_wgrad_rows(int n, int h, int w) {
   return stem_blocks(n, h, w);
 }
 
+// stem_tc.cu: the same convolution on tcgen05 (B2SEG_STEM_TC=0 keeps the CUDA-core kernel)
+int launch_stem_tc_fwd(const EwArgs& a, dim3 grid, dim3 block, size_t smem, cudaStream_t st);
+static bool stem_tc_enabled() {
+  const char* e = getenv("B2SEG_STEM_TC");
+  return !(e && e[0] == '0');
+}
+
 int ew_plan_stem(const b2seg_ew_desc* d, EwPlan* pl) {
   const int64_t* i = d->i;
   void* const* p = d->p;
@@ -308,7 +317,8 @@ int ew_plan_stem(const b2seg_ew_desc* d, EwPlan* pl) {
       B2_REQUIRE(p[0] && p[1] && p[2], "stem: null argument");
       B2_REQUIRE(i[0] >= 1 && i[1] >= 2 && i[2] >= 2 && i[1] % 2 == 0 && i[2] % 2 == 0,
                  "stem: image %lldx%lld must have even height and width", i[1], i[2]);
-      pl->fn = d->kind == B2SEG_EW_STEM_FWD ? launch_stem_fwd : launch_stem_wgrad;
+      pl->fn = d->kind == B2SEG_EW_STEM_FWD ? (stem_tc_enabled() ? launch_stem_tc_fwd : launch_stem_fwd)
+                                            : launch_stem_wgrad;
       pl->grid = dim3(stem_blocks((int)i[0], (int)i[1], (int)i[2]));
       pl->block = dim3(256);
       return B2SEG_OK;
