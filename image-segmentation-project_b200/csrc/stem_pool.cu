@@ -301,6 +301,7 @@ extern "C" int b2seg_stem_wgrad_rows(int n, int h, int w) {
 
 // stem_tc.cu: the same convolution on tcgen05 (B2SEG_STEM_TC=0 keeps the CUDA-core kernel)
 int launch_stem_tc_fwd(const EwArgs& a, dim3 grid, dim3 block, size_t smem, cudaStream_t st);
+int launch_stem_tc_wgrad(const EwArgs& a, dim3 grid, dim3 block, size_t smem, cudaStream_t st);
 static bool stem_tc_enabled() {
   const char* e = getenv("B2SEG_STEM_TC");
   return !(e && e[0] == '0');
@@ -318,7 +319,7 @@ int ew_plan_stem(const b2seg_ew_desc* d, EwPlan* pl) {
       B2_REQUIRE(i[0] >= 1 && i[1] >= 2 && i[2] >= 2 && i[1] % 2 == 0 && i[2] % 2 == 0,
                  "stem: image %lldx%lld must have even height and width", i[1], i[2]);
       pl->fn = d->kind == B2SEG_EW_STEM_FWD ? (stem_tc_enabled() ? launch_stem_tc_fwd : launch_stem_fwd)
-                                            : launch_stem_wgrad;
+                                            : (stem_tc_enabled() ? launch_stem_tc_wgrad : launch_stem_wgrad);
       pl->grid = dim3(stem_blocks((int)i[0], (int)i[1], (int)i[2]));
       pl->block = dim3(256);
       return B2SEG_OK;

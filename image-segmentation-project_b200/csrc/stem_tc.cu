@@ -196,12 +196,144 @@ __global__ void __launch_bounds__(128, 4) stem_tc_fwd_kernel(const EwArgs a) {
   }
 }
 
+// ---- weight gradient ------------------------------------------------------------------------
+// dW[c][tap] = sum_pix dy[pix][c] * x[2*oh-3+kh, 2*ow-3+kw]:  D[tap][c] += A^T B with the pixels as
+// K.  Both operands are MN-major tiles of 128 pixel rows x 128 B: A = the same im2col rows as the
+// forward kernel (taps along M), B = the dy rows of the brick (channels along N), copied from
+// global memory into the swizzled layout by the thread that owns the pixel.  The MMA is 128 rows
+// tall; the second 64-row block of A is pointed at the B tile (LBO = 16 KB) and its products are
+// never read.  The accumulator stays in TMEM across all bricks of the CTA; one fp32 partial row
+// [64][49] per CTA goes to the workspace COLSUM_FINALIZE reduces (same contract as stem_pool.cu).
+__global__ void __launch_bounds__(128, 4) stem_tc_wgrad_kernel(const EwArgs a) {
+  pdl_trigger();
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~(uintptr_t)1023);
+  uint8_t* As = smem;
+  uint8_t* Bs = smem + TC_A_BYTES;  // 128 pixel rows x 64 channels
+  float* patch = reinterpret_cast<float*>(Bs + TC_A_BYTES);
+  uint64_t* mma_bar = reinterpret_cast<uint64_t*>(patch + TC_PH * TC_PWP);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mma_bar + 1);
+  const float* __restrict__ x = (const float*)a.p[0];
+  const bf16* __restrict__ dy = (const bf16*)a.p[1];
+  float* __restrict__ ws = (float*)a.p[2];
+  const int N = (int)a.i[0], H = (int)a.i[1], W = (int)a.i[2];
+  const int OH = H / 2, OW = W / 2;
+  const int tilesH = (OH + TC_TH - 1) / TC_TH, tilesW = (OW + TC_TW - 1) / TC_TW;
+  const long long tiles = (long long)N * tilesH * tilesW;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+
+  if (t == 0) {
+    mbar_init(mma_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) tmem_alloc<64>(tmem_slot);
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  pdl_wait();
+
+  constexpr uint32_t idesc = umma_idesc_bf16(128, 64, 1, 1);
+  const uint64_t adesc = umma_smem_desc(smem_u32(As), TC_A_BYTES, 1024);
+  const uint64_t bdesc = umma_smem_desc(smem_u32(Bs), TC_A_BYTES, 1024);
+  const int ty = t / TC_TW, tx = t % TC_TW;
+  uint32_t phase = 0;
+  bool first = true;
+  float pre[TC_PER_THREAD];
+  long long tile = blockIdx.x;
+  if (tile < tiles) stem_fetch(pre, x, stem_tile(tile, tilesW, tilesH), H, W);
+  for (; tile < tiles; tile += gridDim.x) {
+    const StemTile s = stem_tile(tile, tilesW, tilesH);
+    stem_stash(pre, patch);
+    __syncthreads();
+    if (tile + gridDim.x < tiles)
+      stem_fetch(pre, x, stem_tile(tile + gridDim.x, tilesW, tilesH), H, W);
+    const int oh = s.oh0 + ty, ow = s.ow0 + tx;
+    const bool ok = oh < OH && ow < OW;
+    uint4 dyr[8];
+    {
+      const uint4* src = reinterpret_cast<const uint4*>(dy + (((size_t)s.n * OH + oh) * OW + ow) * 64);
+#pragma unroll
+      for (int c = 0; c < 8; ++c) dyr[c] = ok ? __ldg(src + c) : make_uint4(0u, 0u, 0u, 0u);
+    }
+    {
+      uint32_t words[32];
+      const float* p0 = patch + (2 * ty) * TC_PWP + 2 * tx;
+#pragma unroll
+      for (int i = 0; i < 24; ++i) {
+        const int k0 = 2 * i, k1 = 2 * i + 1;
+        words[i] = f2_to_bf2(p0[(k0 / 7) * TC_PWP + (k0 % 7)], p0[(k1 / 7) * TC_PWP + (k1 % 7)]);
+      }
+      words[24] = f2_to_bf2(p0[6 * TC_PWP + 6], 0.0f);
+#pragma unroll
+      for (int i = 25; i < 32; ++i) words[i] = 0u;
+      store_swizzled_row(As, t, words);
+    }
+    {
+      uint8_t* row = Bs + t * 128;
+#pragma unroll
+      for (int c = 0; c < 8; ++c) *reinterpret_cast<uint4*>(row + ((c ^ (t & 7)) << 4)) = dyr[c];
+    }
+    fence_proxy_async_smem();
+    __syncthreads();
+    if (warp == 0) {
+      tcgen05_fence_after();
+      if (elect_one_sync()) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k)  // 16 pixel rows (2 KB) per MMA
+          umma_bf16_ss(tmem, adesc + (uint64_t)(k * 128), bdesc + (uint64_t)(k * 128), idesc,
+                       (first && k == 0) ? 0u : 1u);
+        tcgen05_commit(mma_bar);
+      }
+      __syncwarp();
+    }
+    first = false;
+    mbar_wait(mma_bar, phase);  // operands may be overwritten once the MMAs have read them
+    phase ^= 1u;
+  }
+  tcgen05_fence_after();
+  float* row = ws + (size_t)blockIdx.x * 3136;
+  const int tap = warp * 32 + lane;  // TMEM lane = accumulator row = tap
+  if (warp < 2) {
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      float v[32];
+      if (!first) {
+        tmem_ld_32x32b_x32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(c * 32), v);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = 0.0f;
+      }
+      if (tap < 49) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) row[(c * 32 + j) * 49 + tap] = v[j];
+      }
+    }
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tcgen05_fence_after();
+    tmem_dealloc<64>(tmem);
+  }
+}
+
 }  // namespace
 
 int launch_stem_tc_fwd(const EwArgs& a, dim3 grid, dim3 block, size_t smem, cudaStream_t st) {
   (void)block;
   (void)smem;
   B2_CHECK_CUDA(b2_launch(stem_tc_fwd_kernel, grid, dim3(128), (size_t)TC_SMEM, st, a));
+  B2_CHECK_CUDA(cudaGetLastError());
+  return B2SEG_OK;
+}
+
+int launch_stem_tc_wgrad(const EwArgs& a, dim3 grid, dim3 block, size_t smem, cudaStream_t st) {
+  (void)block;
+  (void)smem;
+  B2_CHECK_CUDA(b2_launch(stem_tc_wgrad_kernel, grid, dim3(128),
+                          (size_t)(2 * TC_A_BYTES + TC_PH * TC_PWP * 4 + 64 + 1024), st, a));
   B2_CHECK_CUDA(cudaGetLastError());
   return B2SEG_OK;
 }
