@@ -151,9 +151,22 @@ __device__ __forceinline__ void ew_rows_reduce(const float* partial, int rows, l
 #pragma unroll
   for (int k = 0; k < NACC; ++k) acc[k] = 0.0;
   if (c < ncols && partial != nullptr) {
-    for (int r = s * 32 + ty; r < rows; r += 32 * S) {
+    // the loads of a batch of rows are issued together (one L2 round trip per 8 rows, not per row);
+    // the fp64 additions keep the row order, so the result does not depend on the batching
+    const int step = 32 * S;
+    for (int r = s * 32 + ty; r < rows; r += 8 * step) {
+      float v[8][NACC];
 #pragma unroll
-      for (int k = 0; k < NACC; ++k) acc[k] += (double)partial[(size_t)r * rstride + k * koff + c];
+      for (int u = 0; u < 8; ++u) {
+        const int rr = r + u * step;
+#pragma unroll
+        for (int k = 0; k < NACC; ++k)
+          v[u][k] = rr < rows ? __ldg(partial + (size_t)rr * rstride + k * koff + c) : 0.0f;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+#pragma unroll
+        for (int k = 0; k < NACC; ++k) acc[k] += (double)v[u][k];
     }
   }
 #pragma unroll
