@@ -12,8 +12,9 @@ backward, optimizer.step() -- the reference's inner loop, train.py:38-60.
 
 Printed JSON (one line, rank 0):
   value        images/s, whole job, inputs resident in HBM, CUDA events, max over ranks
-  e2e          same metric through train.train_step with HOST (pinned) batches copied in and the
-               loss + confusion counts read back every step
+  e2e          same metric through train.train_step with HOST (pinned) batches fed by
+               train.DevicePrefetcher (H2D on a side stream, double buffered) and the loss +
+               confusion counts read back every step
   roofline     dominant kernel class (tcgen05 conv GEMMs): algorithmic FLOPs / event-timed duration
   cpu_baseline the oracle port of the reference step on this box's host cores (rank 0, N=1)
 Multi-GPU (`--mode folds`, default): every rank trains its own model on its own data -- the
@@ -137,6 +138,19 @@ def _peaks():
                 "hbm": d.get("hbm_gbs"), "source": "measured (MEASURED_PEAKS.json, sustained bf16)"}
     return {"tensor": 1400.0, "tensor_burst": 1590.0, "hbm": 6650.0,
             "source": "fallback (B200_PROFILING.md: 1.59 PF burst / ~1.4 PF sustained, 6.65 TB/s)"}
+
+
+def _recorded_traffic(a):
+    """DRAM bytes per step of the tcgen05 conv kernels from the committed ncu capture of this exact
+    workload (profiles/r01_dram_step_families.json, made by tools/dram_summary.py from
+    `ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum`); None for any other workload."""
+    path = os.path.join(ROOT, "profiles", "r01_dram_step_families.json")
+    if not (a.batch == 64 and a.size == 256 and a.backbone == "resnet34" and not a.no_attention
+            and os.path.exists(path)):
+        return None
+    fam = json.load(open(path))["families"]
+    return float(sum(fam[k]["rd"] + fam[k]["wr"] for k in ("halo3x3_kernel", "tapgemm_kernel", "wgrad_kernel")
+                     if k in fam))
 
 
 def _dist_setup(a):
@@ -312,7 +326,8 @@ def run_b200(a):
         rec["roofline"] = {
             "bound": "tensor", "kernel": "tapgemm_kernel / wgrad_kernel (tcgen05 conv fprop, dgrad, wgrad)",
             "achieved": ach, "peak": peaks["tensor"], "unit": "TFLOP/s", "frac": ach / peaks["tensor"],
-            "traffic": None, "peak_source": peaks["source"],
+            "traffic": _recorded_traffic(a), "traffic_unit": "DRAM bytes per step over these launches (ncu)",
+            "peak_source": peaks["source"],
             "launches_per_step": kb["tensor_launches"],
             "flops_per_step": kb["tensor_flops"], "ms_per_step": kb["tensor_ms"],
             "share_of_step": kb["tensor_ms"] / kb["total_ms"],
