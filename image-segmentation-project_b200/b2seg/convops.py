@@ -62,6 +62,7 @@ class Op:
         self.kind = kind
         self.flops = float(flops)  # algorithmic 2*M*N*K of a tensor-core op (bench roofline)
         self.desc = ""
+        self.side = False  # True: nothing later in the sequence reads its output (see Seq)
 
     def run(self):
         L.check(L.lib().b2seg_op_run(self.handle, L.stream_ptr()))
@@ -83,7 +84,8 @@ class Seq:
     """Ordered list of ops replayed with one C call."""
 
     def __init__(self, ops, side_kinds=(), join_before_kinds=()):
-        """`side_kinds`: kind prefixes of ops the graph replay runs on a side branch
+        """`side_kinds`: kind prefixes of ops (plus every op with `op.side` set) the graph replay
+        runs on a side branch
         (b2seg_seq_append_lane): weight gradients, which nothing later in the list reads, and the
         weight repack, which is joined before the first op whose kind starts with one of
         `join_before_kinds` (b2seg_seq_join)."""
@@ -93,7 +95,7 @@ class Seq:
         self.handle = h
         pending = False
         for op in self.ops:
-            lane = 1 if any(op.kind.startswith(k) for k in side_kinds) else 0
+            lane = 1 if op.side or any(op.kind.startswith(k) for k in side_kinds) else 0
             if pending and lane == 0 and any(op.kind.startswith(k) for k in join_before_kinds):
                 L.check(L.lib().b2seg_seq_join(self.handle))
                 pending = False

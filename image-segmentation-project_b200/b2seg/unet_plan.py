@@ -85,6 +85,7 @@ class UNetPlan:
         # shared block-partial scratch (BatchNorm backward, column sums, 1-channel convs): every
         # use is consumed by the op that follows it on the stream
         self.part = self._alloc((L.EW_MAX_PARTIAL_ROWS * 2 * 2048 + 1024,), F32)
+        self.part_side = None
         self.x_in = self._alloc((N, H, W), F32)
         self.logits = self._alloc((N, 1, H, W), F32)
         if self.need_grad:
@@ -213,8 +214,14 @@ class UNetPlan:
         """grad[gname][c] = sum over pixels of x[:, c] (ConvTranspose2d bias gradient)."""
         P = x.n * x.h * x.w
         rows = eo.partial_rows(L.EW_COLSUM, P, x.c)
-        self.B(eo.ew(L.EW_COLSUM, p=[x, self.part], i=[P, x.c, x.sw]))
-        self.B(eo.ew(L.EW_COLSUM_FINALIZE, p=[self.part, self.gview(gname)], i=[rows, x.c, 0, x.c]))
+        # a parameter gradient: both ops ride the side branch with the weight gradients (which run
+        # in order among themselves), on partial rows of their own
+        if self.part_side is None:
+            self.part_side = self._alloc((L.EW_MAX_PARTIAL_ROWS * 2048 + 1024,), F32)
+        for op in (eo.ew(L.EW_COLSUM, p=[x, self.part_side], i=[P, x.c, x.sw]),
+                   eo.ew(L.EW_COLSUM_FINALIZE, p=[self.part_side, self.gview(gname)], i=[rows, x.c, 0, x.c])):
+            op.side = True
+            self.B(op)
 
     # ------------------------------------------------------------ network walk ----
     def _build(self):

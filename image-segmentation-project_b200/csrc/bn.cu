@@ -380,10 +380,68 @@ __global__ void __launch_bounds__(1024) colsum_finalize_kernel(const EwArgs a) {
 // out[t][a][b] = bf16(in[a*sa + b*sb + t*st]).  One block per 32(a) x 32(b) x T tile (job.start =
 // first tile of the job): the tile is read along whichever of a / b is contiguous with the taps
 // in the parameter (coalesced), transposed through shared memory and written along b.
+// Every layout the plan asks for has st == 1 and the taps innermost (inner stride == T), so a
+// tile is 32 contiguous runs of 32*T floats; for T = 1, 4, 9 (1x1, 2x2, 3x3 kernels) the index
+// arithmetic is compile-time and the store packs two bf16 per thread.
 constexpr int kPackT = 9;
+constexpr int kPackTS = 32 * 33 + 4;  // tap stride in shared memory: bank = 4t + a + b
+
+template <int T>
+__device__ __forceinline__ void pack_tile_fast(const b2seg_pack_job& j, int a0, int b0, float* sm) {
+  constexpr int RUN = 32 * T;
+  const bool inner_b = j.sb < j.sa;
+  const long long so = inner_b ? j.sa : j.sb;
+  const float* __restrict__ in = j.in + (long long)a0 * j.sa + (long long)b0 * j.sb;
+  const int outer_n = inner_b ? j.A - a0 : j.B - b0;
+  const int run_n = (inner_b ? j.B - b0 : j.A - a0) * T;  // valid floats of a run (may exceed RUN)
+#pragma unroll 4
+  for (int e = threadIdx.x; e < 32 * RUN; e += kEwThreads) {
+    const int u = e / RUN, r = e % RUN, v = r / T, t = r % T;
+    const float val = (u < outer_n && r < run_n) ? __ldg(in + (long long)u * so + r) : 0.0f;
+    const int la = inner_b ? u : v, lb = inner_b ? v : u;
+    sm[t * kPackTS + la * 33 + lb] = val;
+  }
+  __syncthreads();
+  bf16* __restrict__ out = (bf16*)j.out;
+  const bool pairs = (j.B & 1) == 0 && (reinterpret_cast<uintptr_t>(out) & 3) == 0;
+#pragma unroll 2
+  for (int e = threadIdx.x; e < T * 512; e += kEwThreads) {
+    const int lb = (e & 15) * 2, la = (e >> 4) & 31, t = e >> 9;
+    if (a0 + la >= j.A || b0 + lb >= j.B) continue;
+    const float* src = sm + t * kPackTS + la * 33 + lb;
+    bf16* dst = out + ((long long)t * j.A + a0 + la) * j.B + b0 + lb;
+    if (pairs) {  // B even and b0 + lb even: lb + 1 is in range and dst is 4-byte aligned
+      *reinterpret_cast<uint32_t*>(dst) = f2_to_bf2(src[0], src[1]);
+    } else {
+      dst[0] = __float2bfloat16_rn(src[0]);
+      if (b0 + lb + 1 < j.B) dst[1] = __float2bfloat16_rn(src[1]);
+    }
+  }
+}
+
+__device__ __forceinline__ void pack_tile_generic(const b2seg_pack_job& j, int a0, int b0, float* sm) {
+  const bool inner_b = j.sb < j.sa;
+  const int T = j.T, runlen = 32 * T;
+  for (int e = threadIdx.x; e < 32 * runlen; e += blockDim.x) {
+    const int u = e / runlen, r = e % runlen, v = r / T, t = r % T;
+    const int la = inner_b ? u : v, lb = inner_b ? v : u;
+    float val = 0.0f;
+    if (a0 + la < j.A && b0 + lb < j.B)
+      val = j.in[(long long)(a0 + la) * j.sa + (long long)(b0 + lb) * j.sb + (long long)t * j.st];
+    sm[t * kPackTS + la * 33 + lb] = val;
+  }
+  __syncthreads();
+  bf16* out = (bf16*)j.out;
+  for (int e = threadIdx.x; e < T * 1024; e += blockDim.x) {
+    const int lb = e & 31, la = (e >> 5) & 31, t = e >> 10;
+    if (a0 + la < j.A && b0 + lb < j.B)
+      out[((long long)t * j.A + a0 + la) * j.B + b0 + lb] = __float2bfloat16_rn(sm[t * kPackTS + la * 33 + lb]);
+  }
+}
+
 __global__ void __launch_bounds__(kEwThreads) pack_kernel(const EwArgs a) {
   pdl_prologue();
-  __shared__ float sm[kPackT * (32 * 33 + 1)];
+  __shared__ float sm[kPackT * kPackTS];
   const b2seg_pack_job* jobs = (const b2seg_pack_job*)a.p[0];
   const int njobs = (int)a.i[0];
   const long long tile = blockIdx.x;
@@ -396,23 +454,11 @@ __global__ void __launch_bounds__(kEwThreads) pack_kernel(const EwArgs a) {
   const int tilesB = (j.B + 31) / 32;
   const int lt = (int)(tile - j.start);
   const int a0 = (lt / tilesB) * 32, b0 = (lt % tilesB) * 32;
-  const bool inner_b = j.sb < j.sa;
-  const int T = j.T, runlen = 32 * T;
-  for (int e = threadIdx.x; e < 32 * runlen; e += blockDim.x) {
-    const int u = e / runlen, r = e % runlen, v = r / T, t = r % T;
-    const int la = inner_b ? u : v, lb = inner_b ? v : u;
-    float val = 0.0f;
-    if (a0 + la < j.A && b0 + lb < j.B)
-      val = j.in[(long long)(a0 + la) * j.sa + (long long)(b0 + lb) * j.sb + (long long)t * j.st];
-    sm[t * (32 * 33 + 1) + la * 33 + lb] = val;
-  }
-  __syncthreads();
-  bf16* out = (bf16*)j.out;
-  for (int e = threadIdx.x; e < T * 1024; e += blockDim.x) {
-    const int lb = e & 31, la = (e >> 5) & 31, t = e >> 10;
-    if (a0 + la < j.A && b0 + lb < j.B)
-      out[((long long)t * j.A + a0 + la) * j.B + b0 + lb] = __float2bfloat16_rn(sm[t * (32 * 33 + 1) + la * 33 + lb]);
-  }
+  const bool fast = j.st == 1 && (j.sb < j.sa ? j.sb : j.sa) == j.T;
+  if (fast && j.T == 9) pack_tile_fast<9>(j, a0, b0, sm);
+  else if (fast && j.T == 4) pack_tile_fast<4>(j, a0, b0, sm);
+  else if (fast && j.T == 1) pack_tile_fast<1>(j, a0, b0, sm);
+  else pack_tile_generic(j, a0, b0, sm);
 }
 
 __global__ void __launch_bounds__(kEwThreads) fill_kernel(const EwArgs a) {

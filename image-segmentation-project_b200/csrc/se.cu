@@ -210,30 +210,56 @@ __global__ void __launch_bounds__(kEwThreads) se_mlp_bwd_sample_kernel(const EwA
 
 __global__ void __launch_bounds__(kEwThreads) se_mlp_bwd_weight_kernel(const EwArgs a) {
   pdl_prologue();
-  const float* part = (const float*)a.p[0];
-  const float* saved = (const float*)a.p[3];
-  const float* hidden = (const float*)a.p[4];
+  const float* __restrict__ part = (const float*)a.p[0];
+  const float* __restrict__ saved = (const float*)a.p[3];
+  const float* __restrict__ hidden = (const float*)a.p[4];
   float* dW1 = (float*)a.p[5];
   float* dW2 = (float*)a.p[6];
   const int N = (int)a.i[0], C = (int)a.i[2], Ch = (int)a.i[3], rows = (int)a.i[4];
   const bool accumulate = a.i[5] != 0;
-  const float* ds = part + (size_t)N * rows * C;
-  const float* dh = part + (size_t)2 * N * rows * C;
+  const float* __restrict__ ds = part + (size_t)N * rows * C;
+  const float* __restrict__ dh = part + (size_t)2 * N * rows * C;
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  // the loads of 8 samples are issued together; the fma chain keeps the sample order
   if (e < C * Ch) {  // dW2[c][h] = sum_n ds[n][c] * (hid_a[n][h] + hid_m[n][h])
     const int c = e / Ch, h = e % Ch;
     float s = 0.0f;
-    for (int n = 0; n < N; ++n)
-      s = fmaf(ds[(size_t)n * C + c], hidden[(size_t)n * 2 * Ch + h] + hidden[(size_t)n * 2 * Ch + Ch + h], s);
+    for (int n0 = 0; n0 < N; n0 += 8) {
+      float x[8], y[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int n = n0 + u;
+        const bool ok = n < N;
+        x[u] = ok ? __ldg(ds + (size_t)n * C + c) : 0.0f;
+        y[u] = ok ? __ldg(hidden + (size_t)n * 2 * Ch + h) + __ldg(hidden + (size_t)n * 2 * Ch + Ch + h) : 0.0f;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if (n0 + u < N) s = fmaf(x[u], y[u], s);
+    }
     dW2[e] = accumulate ? dW2[e] + s : s;
   } else if (e < 2 * C * Ch) {  // dW1[h][c] = sum_n dha[n][h]*avg[n][c] + dhm[n][h]*max[n][c]
     const int e1 = e - C * Ch;
     const int h = e1 / C, c = e1 % C;
     float s = 0.0f;
-    for (int n = 0; n < N; ++n) {
-      const float* sv = saved + (size_t)n * 4 * C;
-      s = fmaf(dh[(size_t)n * 2 * Ch + h], sv[c], s);
-      s = fmaf(dh[(size_t)n * 2 * Ch + Ch + h], sv[C + c], s);
+    for (int n0 = 0; n0 < N; n0 += 8) {
+      float da[8], dm[8], va[8], vm[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int n = n0 + u;
+        const bool ok = n < N;
+        const float* sv = saved + (size_t)n * 4 * C;
+        da[u] = ok ? __ldg(dh + (size_t)n * 2 * Ch + h) : 0.0f;
+        dm[u] = ok ? __ldg(dh + (size_t)n * 2 * Ch + Ch + h) : 0.0f;
+        va[u] = ok ? __ldg(sv + c) : 0.0f;
+        vm[u] = ok ? __ldg(sv + C + c) : 0.0f;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if (n0 + u < N) {
+          s = fmaf(da[u], va[u], s);
+          s = fmaf(dm[u], vm[u], s);
+        }
     }
     dW1[e1] = accumulate ? dW1[e1] + s : s;
   }

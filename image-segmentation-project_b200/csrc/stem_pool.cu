@@ -247,24 +247,34 @@ __global__ void __launch_bounds__(kEwThreads) maxpool_bwd_kernel(const EwArgs a)
     ew_divmod(ip, W, rest, iw);
     ew_divmod(rest, H, rest, ih);
     const int c0 = c8 * 8, n = (int)rest;
+    // windows oh with 2*oh-1 <= ih <= 2*oh+1: row ih is tap 1 of window ih/2 when even, tap 2 of
+    // window (ih-1)/2 and tap 0 of window (ih+1)/2 when odd (same along w): 1, 2 or 4 windows.
+    // All their loads are issued together (predicated), then compared: one L2 round trip, not four.
+    const int oh0 = ih >> 1, ow0 = iw >> 1;
+    const bool vh = (ih & 1) && oh0 + 1 < OH, vw = (iw & 1) && ow0 + 1 < OW;
+    const uint32_t kh0 = (ih & 1) ? 2u : 1u, kw0 = (iw & 1) ? 2u : 1u;  // second window: tap 0
+    uint2 pk[4];
+    uint4 dr[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const bool ok = ((q & 2) == 0 || vh) && ((q & 1) == 0 || vw);
+      const long long op = ((long long)n * OH + oh0 + (q >> 1)) * OW + ow0 + (q & 1);
+      pk[q] = ok ? *reinterpret_cast<const uint2*>(idx + op * C + c0) : make_uint2(~0u, ~0u);
+      dr[q] = ok ? *reinterpret_cast<const uint4*>(dout + op * lddo + c0) : make_uint4(0u, 0u, 0u, 0u);
+    }
     F8 g;
 #pragma unroll
     for (int j = 0; j < 8; ++j) g.v[j] = 0.0f;
-    // windows oh with 2*oh-1 <= ih <= 2*oh+1
-    for (int oh = ih >> 1; oh <= ((ih + 1) >> 1); ++oh) {
-      if (oh >= OH) continue;
-      const uint32_t kh = (uint32_t)(ih - (2 * oh - 1));
-      for (int ow = iw >> 1; ow <= ((iw + 1) >> 1); ++ow) {
-        if (ow >= OW) continue;
-        const uint32_t k = kh * 3 + (uint32_t)(iw - (2 * ow - 1));
-        const long long op = ((long long)n * OH + oh) * OW + ow;
-        const uint2 pk = *reinterpret_cast<const uint2*>(idx + op * C + c0);
-        const F8 d = ld_bf8(dout + op * lddo + c0);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const uint32_t word = j < 4 ? pk.x : pk.y;
-          if (((word >> ((j & 3) * 8)) & 0xffu) == k) g.v[j] += d.v[j];
-        }
+    for (int q = 0; q < 4; ++q) {
+      const uint32_t k = ((q & 2) ? 0u : kh0) * 3u + ((q & 1) ? 0u : kw0);
+      const uint32_t kk = k * 0x01010101u;
+      const uint32_t m0 = __vcmpeq4(pk[q].x, kk), m1 = __vcmpeq4(pk[q].y, kk);
+      const F8 d = unpack_bf8(dr[q]);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const uint32_t m = j < 4 ? m0 : m1;
+        if (m & (1u << ((j & 3) * 8))) g.v[j] += d.v[j];
       }
     }
     bf16* dst = dx + ip * lddx + c0;

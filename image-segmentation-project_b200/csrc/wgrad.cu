@@ -193,8 +193,19 @@ __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const __grid_constant
     const int j = j0 + jj;
     float acc = 0.0f;
     if (j < p.b_channels) {
+      // eight splits' loads in flight per round trip; the additions keep the split order
       const float* src = p.ws + ((size_t)pair * 128 + row) * p.ncols_pad + j;
-      for (int s = g; s < p.nsplit; s += kRedG) acc += __ldg(src + (size_t)s * split_stride);
+      for (int s = g; s < p.nsplit; s += 8 * kRedG) {
+        float v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int ss = s + u * kRedG;
+          v[u] = ss < p.nsplit ? __ldg(src + (size_t)ss * split_stride) : 0.0f;
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+          if (s + u * kRedG < p.nsplit) acc += v[u];
+      }
     }
     sm[g][jj][i * p.ntaps + tap] = acc;
   }
