@@ -22,6 +22,7 @@ cross-validation-fold / grid-config sharding of north_star, no data-path collect
 scaling).  `--mode dp`: one model, per-rank batch, flat-gradient NCCL all-reduce per step.
 """
 import argparse
+import gc
 import json
 import os
 import subprocess
@@ -276,6 +277,11 @@ def run_b200(a):
 
     for i in range(a.warmup):
         step_resident(i)
+    run_e2e(2)
+    # the plan holds ~10^5 long-lived Python objects: keep the cyclic collector from walking them
+    # inside a timed region (a full collection costs tens of ms, several steps' worth)
+    gc.collect()
+    gc.freeze()
     _barrier(world)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local) as clk:

@@ -392,7 +392,10 @@ extern "C" int b2seg_tapgemm_create(const b2seg_tapgemm_desc* d, b2seg_op** out)
 
   const int nm = d->ngemm;
   int bn;
-  if (nm % 128 == 0 && (long long)p.mtiles * (nm / 128) >= b2_num_sms()) bn = 128;
+  // N = 128 tiles once they fill most of the SMs (B2SEG_TG_BN128_MIN = minimum tile count)
+  long long bn128_min = b2_num_sms();
+  if (const char* e = getenv("B2SEG_TG_BN128_MIN")) bn128_min = atoll(e);
+  if (nm % 128 == 0 && (long long)p.mtiles * (nm / 128) >= bn128_min) bn = 128;
   else if (nm % 64 == 0) bn = 64;
   else bn = 32;
   op->block_n = bn;

@@ -66,6 +66,7 @@ class DevicePrefetcher:
         side = torch.cuda.Stream(self.device)
         side.wait_stream(torch.cuda.current_stream(self.device))
         self._bufs, self._done = [{}, {}], [None, None]
+        events = [torch.cuda.Event(), torch.cuda.Event()]  # re-recorded: no per-batch allocation
         it = iter(self.loader)
         k = 0
         try:
@@ -81,9 +82,8 @@ class DevicePrefetcher:
             except StopIteration:
                 staged = None
             yield ready
-            ev = torch.cuda.Event()
-            ev.record(torch.cuda.current_stream(self.device))
-            self._done[k & 1] = ev
+            events[k & 1].record(torch.cuda.current_stream(self.device))
+            self._done[k & 1] = events[k & 1]
             k += 1
 
 

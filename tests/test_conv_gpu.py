@@ -99,6 +99,30 @@ def test_conv_fprop_dgrad_wgrad(cuda, n, h, w, cin, cout, k, stride):
     np.testing.assert_allclose(gw.cpu().numpy(), gw_ref.numpy(), rtol=2e-3, atol=2e-4 * scale)
 
 
+@pytest.mark.parametrize("mode", ["0", "2"])  # 0 = generic kernel only, 2 = halo kernel wherever it fits
+@pytest.mark.parametrize("n,h,w,cin,cout", [(2, 16, 16, 64, 64), (3, 32, 24, 128, 192), (2, 20, 40, 96, 32),
+                                            (1, 64, 64, 256, 128)])
+def test_wgrad3x3_halo_and_generic_agree_with_reference(cuda, monkeypatch, mode, n, h, w, cin, cout):
+    """Both 3x3 stride-1 weight-gradient kernels (wgrad.cu: per-tap loads vs one halo brick per
+    chunk) against torch.nn.grad.conv2d_weight, including accumulate mode."""
+    from b2seg import convops as co
+    monkeypatch.setenv("B2SEG_WGRAD_HALO", mode)
+    g = torch.Generator().manual_seed(n + h + w + cin + cout)
+    x = _rb(torch.randn(n, cin, h, w, generator=g))
+    dy = _rb(torch.randn(n, cout, h, w, generator=g))
+    gw_ref = torch.nn.grad.conv2d_weight(x, (cout, cin, 3, 3), dy, 1, 1)
+    xd, dyd = _nhwc(x).to(cuda), _nhwc(dy).to(cuda)
+    gw = torch.full((cout, cin, 3, 3), 7.0, dtype=torch.float32, device=cuda)
+    ws = torch.empty(co.wgrad_workspace_bytes(cin, cout, 9, n, h, w) // 4 + 4, dtype=torch.float32, device=cuda)
+    co.conv_wgrad(co.View(xd), co.View(dyd), 3, 1, gw, ws).run()
+    torch.cuda.synchronize()
+    scale = float(gw_ref.abs().max())
+    np.testing.assert_allclose(gw.cpu().numpy(), gw_ref.numpy(), rtol=2e-3, atol=2e-4 * scale)
+    co.conv_wgrad(co.View(xd), co.View(dyd), 3, 1, gw, ws, accumulate=True).run()
+    torch.cuda.synchronize()
+    np.testing.assert_allclose(gw.cpu().numpy(), 2 * gw_ref.numpy(), rtol=2e-3, atol=4e-4 * scale)
+
+
 @pytest.mark.parametrize("n,h,w,cin,cout,skip", [(2, 8, 8, 128, 64, 64), (1, 16, 24, 32, 16, 0),
                                                   (4, 4, 4, 512, 256, 256), (2, 64, 64, 64, 32, 64)])
 def test_conv_transpose_into_concat_slice(cuda, n, h, w, cin, cout, skip):
