@@ -326,6 +326,10 @@ def run_b200(a):
         "clocks": clk.summary(),
         "final_loss": final_loss,
     }
+    if a.mode == "dp" and world > 1:
+        # the per-kernel replay below runs on rank 0 alone: take the collectives (gradient hook,
+        # global-batch loss sums) off the model first, on every rank
+        dataparallel.detach(model, crit)
     if rank == 0 and not a.no_kernel_timing:
         kb = _kernel_breakdown(model, crit, dev_i[0], dev_m[0])
         ach = kb["tensor_flops"] / (kb["tensor_ms"] * 1e-3) / 1e12
