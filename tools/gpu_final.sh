@@ -14,6 +14,7 @@ timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/b
 timeout 600 python tools/hbm_bench.py > gpurun_out/hbm_kernels.json 2> gpurun_out/hbm_kernels.err; echo "hbm rc=$?"; tail -3 gpurun_out/hbm_kernels.err
 timeout 300 python tools/step_segments.py 64 256 > gpurun_out/step_segments_b64.txt 2>&1; grep -E "graph|full" gpurun_out/step_segments_b64.txt
 timeout 600 python tools/op_times.py 64 256 > gpurun_out/op_times_b64.txt 2>&1; echo "op_times rc=$?"
+timeout 300 python tools/graph_costs.py 64 256 > gpurun_out/graph_costs_b64.txt 2>&1; echo "graph_costs rc=$?"
 ARGS="--steps 2 --warmup 3 --no-kernel-timing --no-cpu-baseline"
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv \
     --log-file gpurun_out/launches.csv python bench.py $ARGS > gpurun_out/ncu_launch.log 2>&1
@@ -26,5 +27,5 @@ B="python bench.py --steps 1 --warmup 3 --no-kernel-timing --no-cpu-baseline"
 cap() { timeout 900 ncu --set full --clock-control none --import-source on --profile-from-start off -k regex:"$1" -c $2 -f -o /tmp/$3 $B > gpurun_out/ncu_$3.log 2>&1; echo "$3 rc=$?"; ncu -i /tmp/$3.ncu-rep --page raw --csv > gpurun_out/ncu_raw_$3.csv 2>/dev/null; }
 cap "stem_tc|maxpool" 4 stemtc
 cap "bn_bwd_reduce|bn_bwd_apply|bn_apply" 9 bn
-cap "tapgemm_kernel|wgrad_kernel" 24 conv
+cap "halo3x3_kernel|wgrad_halo_kernel|wgrad_kernel" 24 conv
 ls -la gpurun_out | head -60
