@@ -162,9 +162,6 @@ def _dist_setup(a):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        # NCCL_DEBUG=VERSION makes NCCL print its banner on stdout, where the one JSON line belongs
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     elif a.gpus > 1:
@@ -357,7 +354,7 @@ def run_b200(a):
         dist.barrier()
         dist.destroy_process_group()
     if rank == 0:
-        print(json.dumps(rec))
+        _emit(rec)
 
 
 # ------------------------------------------------ CPU baseline / reference arm ----
@@ -429,11 +426,31 @@ def run_reference(a):
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(rec))
+    _emit(rec)
+
+
+_RESULT_OUT = None
+
+
+def _claim_stdout():
+    """stdout carries exactly ONE JSON line.  Libraries write there too (NCCL prints its version
+    banner on stdout at init), so the real stdout is set aside for the result and file
+    descriptor 1 is pointed at stderr for everything else."""
+    global _RESULT_OUT
+    sys.stdout.flush()
+    _RESULT_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+def _emit(rec):
+    out = _RESULT_OUT or sys.stdout
+    out.write(json.dumps(rec) + "\n")
+    out.flush()
 
 
 def main():
     a = parse_args()
+    _claim_stdout()
     if a.impl == "reference":
         run_reference(a)
     else:
