@@ -204,19 +204,23 @@ __global__ void __launch_bounds__(kEwThreads) maxpool_fwd_kernel(const EwArgs a)
     uint32_t bi[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) { best[j] = -INFINITY; bi[j] = 0; }
+    // the nine window loads are issued together (predicated at the borders), then scanned in order
+    uint4 raw[9];
+    bool ok[9];
 #pragma unroll
-    for (int kh = 0; kh < 3; ++kh) {
-      const int ih = 2 * oh - 1 + kh;
-      if (ih < 0 || ih >= H) continue;
+    for (int q = 0; q < 9; ++q) {
+      const int ih = 2 * oh - 1 + q / 3, iw = 2 * ow - 1 + q % 3;
+      ok[q] = ih >= 0 && ih < H && iw >= 0 && iw < W;
+      raw[q] = ok[q] ? *reinterpret_cast<const uint4*>(x + (((long long)n * H + ih) * W + iw) * ldx + c0)
+                     : make_uint4(0u, 0u, 0u, 0u);
+    }
 #pragma unroll
-      for (int kw = 0; kw < 3; ++kw) {
-        const int iw = 2 * ow - 1 + kw;
-        if (iw < 0 || iw >= W) continue;
-        const F8 v = ld_bf8(x + (((long long)n * H + ih) * W + iw) * ldx + c0);
+    for (int q = 0; q < 9; ++q) {
+      if (!ok[q]) continue;
+      const F8 v = unpack_bf8(raw[q]);
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if (v.v[j] > best[j] || v.v[j] != v.v[j]) { best[j] = v.v[j]; bi[j] = kh * 3 + kw; }
-      }
+      for (int j = 0; j < 8; ++j)
+        if (v.v[j] > best[j] || v.v[j] != v.v[j]) { best[j] = v.v[j]; bi[j] = q; }
     }
     F8 o;
 #pragma unroll
