@@ -268,7 +268,11 @@ int b2seg_tapgemm_stat_rows(int on, int oh, int ow);
  *   grad[tap.out_base + i*row_stride + j*col_stride] (+)= G[tap][i][j]   (fp32)
  * replaces the wgrad half of convolution_backward for Conv2d (a = layer input,
  * b = dY) and ConvTranspose2d (a = dY phases, b = layer input) reached from
- * loss.backward() at train.py:48. */
+ * loss.backward() at train.py:48.
+ * A 3x3 stride-1 problem (one source, the nine offsets -1..1) whose b side has at most 64
+ * channels is planned on a halo-reuse kernel that reads all nine taps out of one input brick
+ * per pixel tile; the result is the same, and b2seg_wgrad_workspace_bytes() already accounts
+ * for whichever kernel the planner picks. */
 typedef struct b2seg_wgrad_desc {
   b2seg_tensor4 a_src[4];
   int32_t na_src;
