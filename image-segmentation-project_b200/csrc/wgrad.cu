@@ -389,10 +389,11 @@ bool wgrad_halo_enabled() {
 
 // geometry of the halo-reuse kernel; false when the pixel grid is smaller than one 8 x 16 brick
 // Measured at 64 images (profiles/r01_op_times_b64*.txt, generic -> halo): 96->32 @128x128 235 -> 171 us,
-// 32->32 @128x128 158 -> 114, 128->64 @64x64 74 -> 71; but 64->64 @64x64 58 -> 65 (148-way split-K
-// reduce), and every dY wider than 64 channels loses (256->256 @16x16 39 -> 54): there the generic
-// kernel's N = 128 MMAs halve the MN-major operand reads per FLOP, which -- not L2 traffic -- is
-// what bounds these GEMMs (~120 cycles per 128x64x16 MMA in both kernels).
+// 32->32 @128x128 158 -> 114, 128->64 @64x64 74 -> 71; but 64->64 @64x64 58 -> 65 (its 148-way split-K
+// reduction becomes the long pole), and every dY wider than 64 channels loses (256->256 @16x16
+// 39 -> 54): this kernel's N = 64 MMAs run at 48 cycles each, shared-memory-operand bound, where
+// the generic kernel's N = 128 MMAs do twice the work in 64 (tools/umma_rate.cu; MN-major operands
+// cost nothing extra).
 bool wgrad_halo_geom(int a_ch, int b_ch, int pn, int ph, int pw, WgradGeom* out) {
   WgradGeom g;
   b2_pick_pixel_tile(pn, ph, pw, &g.wt, &g.ht, &g.nt);
