@@ -155,16 +155,16 @@ class UNetWithBackbone(nn.Module):
     # plans are cached per (batch, H, W, training, needs-grad); rebuilt if parameters moved
     def _plan_for(self, x, need_grad):
         key = (x.shape[0], x.shape[2], x.shape[3], self.training, bool(need_grad))
-        plan = self._plans.get(key)
+        plan = self._plans.pop(key, None)
         if plan is not None and plan.params_moved():
             self._plans.clear()
             plan = None
         if plan is None:
             max_plans = int(os.environ.get("B2SEG_MAX_PLANS", "6"))
-            while len(self._plans) >= max_plans:
+            while len(self._plans) >= max_plans:  # least recently used first (dict order = use order)
                 self._plans.pop(next(iter(self._plans)))
             plan = UNetPlan(self, x.shape[0], x.shape[2], x.shape[3], self.training, need_grad)
-            self._plans[key] = plan
+        self._plans[key] = plan  # (re-)inserted last: most recently used
         return plan
 
     def __getstate__(self):  # copy.deepcopy / pickle: plans hold device handles, rebuild lazily

@@ -31,12 +31,15 @@ def make_spec(**kw) -> L.LossSpec:
 
 
 class _Scratch:
-    """Per-device reduction workspace (zero-initialised once; kernels leave it zeroed)."""
+    """Reduction workspace (ticket counter + block partials; zero-initialised once, kernels leave it
+    zeroed), one per (device, stream): reductions in flight on different streams or from different
+    threads never share tickets or partials."""
     _by_dev = {}
 
     @classmethod
     def get(cls, device) -> torch.Tensor:
-        key = (device.type, device.index if device.index is not None else torch.cuda.current_device())
+        key = (device.type, device.index if device.index is not None else torch.cuda.current_device(),
+               int(torch.cuda.current_stream(device).cuda_stream))
         ws = cls._by_dev.get(key)
         if ws is None:
             n = L.lib().b2seg_seg_reduce_workspace_bytes()
@@ -116,7 +119,7 @@ def metrics_from_probs(probs, target) -> torch.Tensor:
     out = torch.empty(L.STATS_LEN, dtype=torch.float64, device=p.device)
     L.check(L.lib().b2seg_seg_metrics_from_probs(p.data_ptr(), t.data_ptr(), p.numel(),
                                                  _Scratch.get(p.device).data_ptr(), out.data_ptr(),
-                                                 L.stream_ptr()))
+                                                 int(torch.cuda.current_stream(device).cuda_stream)))
     return out
 
 

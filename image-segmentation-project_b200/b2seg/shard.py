@@ -13,6 +13,7 @@ function degenerates to the sequential loop of the reference.
 """
 from __future__ import annotations
 
+import datetime
 import os
 from typing import Callable, List, Sequence
 
@@ -27,21 +28,48 @@ def world() -> tuple:
     return 0, 1
 
 
+# Units of a grid can differ by hours (resnet50 vs resnet34, early stopping): the result gather
+# must not sit under NCCL's 10-minute watchdog.  It runs over a gloo (CPU) group with this timeout;
+# NCCL is kept for tensors only (the data-parallel gradient all-reduce).
+RESULT_TIMEOUT = datetime.timedelta(hours=float(os.environ.get("B2SEG_SHARD_TIMEOUT_HOURS", "48")))
+_result_group = None
+
+
 def init_from_env(backend: str | None = None) -> tuple:
     """Join the torchrun rendezvous if RANK/WORLD_SIZE are set (idempotent); bind this process
-    to its GPU.  Returns (rank, world_size)."""
+    to its GPU (LOCAL_RANK).  Returns (rank, world_size).  CrossValidator / ModelComparator call
+    this, so `torchrun --nproc-per-node N <experiment script>.py` shards without any change to
+    the script."""
     ws = int(os.environ.get("WORLD_SIZE", "1"))
-    if ws > 1 and not dist.is_initialized():
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    if ws > 1 and "RANK" in os.environ:
         local = int(os.environ.get("LOCAL_RANK", "0"))
-        if backend is None:
-            backend = "nccl" if torch.cuda.is_available() else "gloo"
-        if backend == "nccl":
-            torch.cuda.set_device(local)
-            dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-        else:
-            dist.init_process_group(backend)
+        if torch.cuda.is_available():
+            torch.cuda.set_device(local % torch.cuda.device_count())
+        if not dist.is_initialized():
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            os.environ.setdefault("MASTER_PORT", "29500")
+            if backend is None:
+                backend = "nccl" if torch.cuda.is_available() else "gloo"
+            if backend == "nccl":
+                dist.init_process_group("nccl", device_id=torch.device("cuda", torch.cuda.current_device()),
+                                        timeout=RESULT_TIMEOUT)
+            else:
+                dist.init_process_group(backend, timeout=RESULT_TIMEOUT)
     return world()
+
+
+def result_group():
+    """The process group the small python result dicts travel over: the default group when it is
+    gloo already, otherwise a gloo group created next to the NCCL one (collective: every rank
+    reaches this from run_units at the same point)."""
+    global _result_group
+    if not dist.is_initialized():
+        return None
+    if dist.get_backend() == "gloo":
+        return None  # default group
+    if _result_group is None:
+        _result_group = dist.new_group(backend="gloo", timeout=RESULT_TIMEOUT)
+    return _result_group
 
 
 def assign(n_units: int, rank: int, world_size: int, costs: Sequence[float] | None = None) -> List[int]:
@@ -83,7 +111,7 @@ def run_units(units: Sequence, fn: Callable, costs: Sequence[float] | None = Non
     if ws == 1:
         return [local[i] for i in range(len(units))]
     gathered = [None] * ws
-    dist.all_gather_object(gathered, (local, err), group=group)
+    dist.all_gather_object(gathered, (local, err), group=group if group is not None else result_group())
     merged = {}
     for r, (part, e) in enumerate(gathered):
         if e is not None:

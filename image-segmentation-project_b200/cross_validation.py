@@ -54,7 +54,9 @@ class CrossValidator:
         self.n_splits = n_splits
         self.random_state = random_state
         self.augmentations_per_image = augmentations_per_image
-        self.rank, self.world_size = shard.world()
+        # under torchrun (RANK / WORLD_SIZE / LOCAL_RANK set) this joins the rendezvous and binds the
+        # process to cuda:LOCAL_RANK; otherwise (0, 1) and the loops below run sequentially
+        self.rank, self.world_size = shard.init_from_env()
         self._announce = verbose              # every rank reports the units it ran
         self.verbose = verbose and self.rank == 0
         self.data = load_original_data(data_dir, image_type)

@@ -18,6 +18,9 @@ def get_device():
     silently training on the CPU."""
     if not torch.cuda.is_available():
         raise RuntimeError("b2seg needs a CUDA (Blackwell, sm_100a) device; there is no CPU fallback")
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1 and "LOCAL_RANK" in os.environ:
+        # one process per GPU (torchrun): this process owns cuda:LOCAL_RANK
+        torch.cuda.set_device(int(os.environ["LOCAL_RANK"]) % torch.cuda.device_count())
     device = torch.device("cuda", torch.cuda.current_device())
     print("Using CUDA device")
     return device

@@ -55,3 +55,26 @@ class OracleTrainer:
                 self.sd[k].copy_(v)
             metrics = seg_losses.confusion_metrics(torch.sigmoid(logits.detach()), masks)
         return float(loss.detach()), metrics
+
+    def evaluate_batch(self, images, masks):
+        """Validation batch (train.py:87-99): eval-mode forward (running statistics), loss,
+        metrics on sigmoid(outputs); no parameter or buffer changes."""
+        with torch.no_grad():
+            logits = uf.unet_forward(self.sd, images, backbone=self.backbone, use_attention=self.attn,
+                                     training=False)
+            loss = self._loss(logits, masks)
+            metrics = seg_losses.confusion_metrics(torch.sigmoid(logits), masks)
+        return float(loss), metrics
+
+
+def epoch_means(batch_results):
+    """The epoch dict train_epoch / evaluate return (train.py:54-68, :100-112): every per-batch
+    metric and the per-batch loss weighted by the batch size, divided by the sample count.
+    `batch_results` = [(loss float, metrics dict, batch_size)]."""
+    total = sum(bs for _, _, bs in batch_results)
+    out = {}
+    for loss, metrics, bs in batch_results:
+        for k, v in metrics.items():
+            out[k] = out.get(k, 0.0) + v * bs
+        out["loss"] = out.get("loss", 0.0) + loss * bs
+    return {k: v / total for k, v in out.items()}

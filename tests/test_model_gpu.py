@@ -14,13 +14,21 @@ Tolerances (written here because `north_star` asks for stated tolerances):
   * every stored activation:  ||ours - oracle|| / ||oracle|| <= 6e-3   (bf16 has 2^-9 = 2e-3
     relative rounding; fp32 accumulation on both sides),
   * loss on identical logits: 1e-3 relative (north_star) -- in fact ~1e-6,
-  * every parameter gradient: cosine >= 0.995 and relative L2 error <= max(8e-2, 4 x the
+  * every parameter gradient: cosine >= 0.995 and relative L2 error <= max(GRAD_FLOOR, 2 x the
     error of the oracle's own "bf16 activation-gradient" twin) -- gradients pass through
-    bf16 buffers ~60 times; tensors whose absolute error is below 2e-4 x the largest gradient
-    norm of the model pass outright (1-element BatchNorm2d(1) parameters of the gates),
-  * free-running logits vs the fp32 reference: reported, bounded loosely (<= 0.35 rel).
+    bf16 buffers ~60 times, and the twin is the same fp32 oracle with its activation gradients
+    rounded to bf16 at the product's storage points; tensors whose absolute error is below
+    1e-4 x the largest gradient norm of the model pass outright (1-element BatchNorm2d(1)
+    parameters of the gates).  The worst layer of every case is printed and written to
+    gpurun_out/parity_<case>.json,
+  * trajectory (free running, 10 optimiser steps vs the fp32 CPU oracle): loss per step within
+    TRAJ_TOL relative (test_trajectory_matches_oracle); the observed worst step is printed.
+The cases include the shapes bench.py times: C1 (4 x 256^2), 32 x 256^2 (the >= 148-CTA grids,
+resident-weight halo kernel, halo weight gradient) and one 1024^2 tile (config 5's tile size).
 """
 import copy
+import json
+import os
 
 import pytest
 import torch
@@ -53,7 +61,18 @@ CASES = [
     ("resnet50", False, 64, 2, "bce"),
     ("resnet50", True, 64, 2, "focal"),
     ("resnet34", True, 96, 1, "tversky"),   # 3x3 grid at enc4, batch 1
+    ("resnet34", True, 256, 4, "combo"),    # BASELINE config 1: batch 4 x 256^2, BCE+Dice
+    ("resnet34", True, 256, 32, "combo"),   # the planner's choices at the bench shape (>= 148 CTAs)
+    ("resnet34", False, 1024, 1, "combo"),  # one config-5 tile
 ]
+GRAD_FLOOR = 2.5e-2   # relative L2; applies where 2 x twin is smaller (see the module docstring)
+
+
+def _report(name, payload):
+    out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    if os.path.isdir(out):
+        with open(os.path.join(out, f"parity_{name}.json"), "w") as f:
+            json.dump(payload, f, indent=1)
 
 
 @pytest.mark.parametrize("backbone,attn,size,batch,loss_name", CASES)
@@ -91,6 +110,7 @@ def test_train_step_teacher_forced(cuda, backbone, attn, size, batch, loss_name)
     params = dict(model.named_parameters())
     gmax = max(float(v.norm()) for v in ref_grads.values() if v is not None)
     checked = 0
+    rows = []
     for n, p in params.items():
         rg = ref_grads[n]
         if rg is None:
@@ -101,12 +121,21 @@ def test_train_step_teacher_forced(cuda, backbone, attn, size, batch, loss_name)
             continue
         pg = p.grad.cpu()
         checked += 1
-        if float((pg.double() - rg.double()).norm()) <= 2e-4 * gmax:
+        if float((pg.double() - rg.double()).norm()) <= 1e-4 * gmax:
             continue  # small tensors (BatchNorm2d(1) of psi, ...): absolute error far below the scale
-        tol = max(8e-2, 4 * _rel(twin[n], rg))
-        assert _cos(pg, rg) >= 0.995, (n, _cos(pg, rg))
-        assert _rel(pg, rg) <= tol, (n, _rel(pg, rg), tol)
+        tw = _rel(twin[n], rg)
+        rows.append({"name": n, "rel": _rel(pg, rg), "twin": tw, "cos": _cos(pg, rg),
+                     "tol": max(GRAD_FLOOR, 2 * tw)})
     assert checked > 100
+    rows.sort(key=lambda r: -r["rel"] / r["tol"])
+    case = f"{backbone}_{'attn' if attn else 'noattn'}_{size}x{batch}_{loss_name}"
+    _report(case, {"worst_activation": worst, "loss": float(loss), "oracle_loss": ref_loss,
+                   "worst_gradients": rows[:12], "min_cos": min(r["cos"] for r in rows)})
+    print(f"\n[{case}] worst activation {worst[0]:.2e} ({worst[1]}); worst gradient "
+          f"{rows[0]['name']} rel {rows[0]['rel']:.3e} (twin {rows[0]['twin']:.3e}, tol {rows[0]['tol']:.3e}); "
+          f"min cos {min(r['cos'] for r in rows):.5f}")
+    bad = [r for r in rows if r["rel"] > r["tol"] or r["cos"] < 0.995]
+    assert not bad, bad[:5]
 
     # running statistics follow nn.BatchNorm2d (momentum 0.1, unbiased variance)
     new_stats = {}

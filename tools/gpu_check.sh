@@ -1,0 +1,41 @@
+#!/bin/bash
+# One parameterised GPU recipe (run under gpurun):  tools/gpu_check.sh [tests] [bench] [ops] [ncu] [hbm]
+#   tests  pytest -m gpu (+ smoke)          bench  default bench.py + reference arm
+#   ops    per-op / per-segment / in-graph timings   ncu   launch list + DRAM bytes per kernel of one step
+#   hbm    tools/hbm_bench.py ([64,1,1024,1024] loss / metric / augment kernels)
+# Outputs land in gpurun_out/ (scratch); copy what should be judged into profiles/.
+mkdir -p gpurun_out
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm --format=csv > gpurun_out/gpu.txt 2>&1
+for what in "$@"; do case $what in
+tests)
+  timeout 2400 python -m pytest tests -q -m gpu -x -s > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"
+  grep -E "^\[|worst|passed|failed|Error|error" gpurun_out/pytest_gpu.log | tail -40
+  timeout 300 python -c 'import __graft_entry__ as g; g.smoke()' > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -3 gpurun_out/smoke.log;;
+bench)
+  timeout 1200 python bench.py > gpurun_out/bench_b64.json 2> gpurun_out/bench_b64.err; echo "bench rc=$?"; tail -5 gpurun_out/bench_b64.err
+  python - <<'PY'
+import json
+d = json.load(open('gpurun_out/bench_b64.json'))
+print('value', round(d['value'], 1), 'ms', round(d['ms_per_step'], 3), 'e2e', round(d['e2e']['value'], 1), d['e2e'].get('ms_per_step_blocks'),
+      'loss', d['final_loss'], 'launches', d['launches_per_step'])
+for k in ('parity_check', 'sustained', 'roofline', 'c1_batch4', 'dp_c5', 'cpu_baseline'):
+    print(k, json.dumps(d.get(k))[:600])
+print('loss_hbm', json.dumps({k: (v['us'], v['frac']) for k, v in d.get('loss_hbm', {}).get('kernels', {}).items()}))
+PY
+  timeout 900 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"; cut -c1-300 gpurun_out/bench_ref.json;;
+ops)
+  timeout 300 python tools/step_segments.py 64 256 > gpurun_out/step_segments_b64.txt 2>&1; grep -E "graph|full" gpurun_out/step_segments_b64.txt
+  timeout 600 python tools/op_times.py 64 256 > gpurun_out/op_times_b64.txt 2>&1; echo "op_times rc=$?"
+  timeout 300 python tools/graph_costs.py 64 256 > gpurun_out/graph_costs_b64.txt 2>&1; echo "graph_costs rc=$?"; grep -E "^==|without" gpurun_out/graph_costs_b64.txt;;
+ncu)
+  A="--steps 2 --warmup 3 --no-kernel-timing --no-cpu-baseline --no-extras"
+  timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv \
+      --log-file gpurun_out/launches.csv python bench.py $A > gpurun_out/ncu_launch.log 2>&1; echo "launch list rc=$?"
+  timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none \
+      --profile-from-start off --csv --log-file gpurun_out/dram_step.csv \
+      python bench.py --steps 1 --warmup 3 --no-kernel-timing --no-cpu-baseline --no-extras > gpurun_out/ncu_dram.log 2>&1; echo "dram list rc=$?"
+  python tools/dram_summary.py gpurun_out/dram_step.csv > gpurun_out/dram_step_summary.txt 2>&1; head -30 gpurun_out/dram_step_summary.txt;;
+hbm)
+  timeout 600 python tools/hbm_bench.py > gpurun_out/hbm_kernels.json 2> gpurun_out/hbm_kernels.err; echo "hbm rc=$?"; tail -3 gpurun_out/hbm_kernels.err;;
+esac; done
+ls gpurun_out | wc -l
