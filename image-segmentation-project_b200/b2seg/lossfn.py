@@ -119,7 +119,7 @@ def metrics_from_probs(probs, target) -> torch.Tensor:
     out = torch.empty(L.STATS_LEN, dtype=torch.float64, device=p.device)
     L.check(L.lib().b2seg_seg_metrics_from_probs(p.data_ptr(), t.data_ptr(), p.numel(),
                                                  _Scratch.get(p.device).data_ptr(), out.data_ptr(),
-                                                 int(torch.cuda.current_stream(device).cuda_stream)))
+                                                 L.stream_ptr()))
     return out
 
 
