@@ -8,7 +8,7 @@ from __future__ import annotations
 import ctypes as C
 import os
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb2seg.so")
 
@@ -82,7 +82,7 @@ class WgradDesc(C.Structure):
 
 
 class EwDesc(C.Structure):
-    _fields_ = [("kind", C.c_int32), ("p", C.c_void_p * 10), ("i", C.c_int64 * 10), ("f", C.c_float * 4)]
+    _fields_ = [("kind", C.c_int32), ("p", C.c_void_p * 18), ("i", C.c_int64 * 12), ("f", C.c_float * 4)]
 
 
 class PackJob(C.Structure):
@@ -95,7 +95,7 @@ EW_MAX_PARTIAL_ROWS = 592
 (EW_BN_FINALIZE, EW_BN_APPLY, EW_BN_BWD_REDUCE, EW_BN_BWD_FINALIZE, EW_BN_BWD_APPLY, EW_MAXPOOL_FWD,
  EW_MAXPOOL_BWD, EW_STEM_FWD, EW_STEM_WGRAD, EW_DOT1_FWD, EW_DOT1_BWD, EW_COLSUM_FINALIZE, EW_COLSUM,
  EW_PACK, EW_GATE_APPLY, EW_GATE_BWD, EW_SE_POOL, EW_SE_MLP, EW_SE_SCALE, EW_SE_BWD_REDUCE,
- EW_SE_MLP_BWD, EW_SE_BWD_APPLY, EW_FILL) = range(1, 24)
+ EW_SE_MLP_BWD, EW_SE_BWD_APPLY, EW_FILL, EW_BN_APPLY_FUSED, EW_BN_BWD_FUSED) = range(1, 26)
 
 
 # ------------------------------------------------------------- signatures ----

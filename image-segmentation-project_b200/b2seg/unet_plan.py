@@ -47,6 +47,23 @@ class Act:
         return acc
 
 
+class BNRef:
+    """One BatchNorm2d of the plan: its parameter prefix, the [4][C] constants buffer (scale,
+    shift, mean, invstd) the backward pass reads, and -- in training mode, until a consumer has
+    folded them -- the conv epilogue's partial statistics."""
+
+    __slots__ = ("prefix", "C", "bnp", "stats", "rows", "count", "ready")
+
+    def __init__(self, prefix, C_, bnp, stats, rows, count, ready):
+        self.prefix, self.C, self.bnp, self.stats = prefix, C_, bnp, stats
+        self.rows, self.count, self.ready = rows, count, ready
+
+
+def _fused_bn_enabled():
+    import os
+    return os.environ.get("B2SEG_BN_FUSED", "1") != "0"
+
+
 class UNetPlan:
     def __init__(self, model, N, H, W, training, need_grad):
         if H % 32 or W % 32:
@@ -154,22 +171,53 @@ class UNetPlan:
         if self.need_grad:
             self._ws_req = max(self._ws_req, co.wgrad_workspace_bytes(a_ch, b_ch, ntaps, n, h, w))
 
-    def bn_finalize(self, prefix, C_, rows, count, partial):
-        """BatchNorm statistics -> bnp [4][C] (scale, shift, mean, invstd); updates running stats."""
+    def bn_finalize(self, prefix, C_, rows, count, partial, defer=False) -> BNRef:
+        """BatchNorm statistics -> BNRef.  Eval mode (running statistics) and `defer=False` emit the
+        finalize kernel here; in training mode with `defer=True` the ONE consumer of the statistics
+        (`bn_apply`) folds the partial rows itself, updates the running statistics and publishes
+        bnp [4][C] (scale, shift, mean, invstd) -- one launch less per BatchNorm."""
         if self.training and count <= 1:
             raise ValueError(f"Expected more than 1 value per channel when training ({prefix})")
         bnp = self._alloc((4, C_), F32)
+        if defer and self.training and C_ % 8 == 0 and _fused_bn_enabled():
+            return BNRef(prefix, C_, bnp, partial, rows, count, False)
+        self._emit_finalize(prefix, C_, rows, count, partial, bnp)
+        return BNRef(prefix, C_, bnp, partial, rows, count, True)
+
+    def _emit_finalize(self, prefix, C_, rows, count, partial, bnp):
         self.F(eo.ew(L.EW_BN_FINALIZE,
                      p=[partial if self.training else None, self.params[prefix + ".weight"],
                         self.params[prefix + ".bias"], self.buffers[prefix + ".running_mean"],
                         self.buffers[prefix + ".running_var"],
                         self.buffers[prefix + ".num_batches_tracked"], bnp],
                      i=[rows, C_, count, 1 if self.training else 0], f=[1e-5, 0.1]))
-        return bnp
 
-    def bn_apply(self, y: View, bnp, out: View, relu, res: View | None = None, rbnp=None):
-        self.F(eo.ew(L.EW_BN_APPLY, p=[y, bnp, out, res, rbnp],
-                     i=[y.n * y.h * y.w, y.c, y.sw, out.sw, res.sw if res else 0, 1 if relu else 0]))
+    def _bn_ptrs(self, bn: BNRef):
+        pr = bn.prefix
+        return [bn.stats, self.params[pr + ".weight"], self.params[pr + ".bias"],
+                self.buffers[pr + ".running_mean"], self.buffers[pr + ".running_var"],
+                self.buffers[pr + ".num_batches_tracked"], bn.bnp]
+
+    def bn_apply(self, y: View, bn: BNRef, out: View, relu, res: View | None = None, rbn: BNRef | None = None):
+        """out = act(BN(y) (+ res | + BN_r(res))).  Statistics still pending on `bn` (and `rbn`) are
+        folded inside the same launch (EW_BN_APPLY_FUSED)."""
+        P = y.n * y.h * y.w
+        if not bn.ready:
+            if rbn is not None and rbn.ready:
+                raise AssertionError("a pending BatchNorm cannot take a finalized residual BatchNorm")
+            pp = [y, out, res] + self._bn_ptrs(bn) + (self._bn_ptrs(rbn) if rbn is not None else [])
+            self.F(eo.ew(L.EW_BN_APPLY_FUSED, p=pp,
+                         i=[P, y.c, y.sw, out.sw, res.sw if res else 0, 1 if relu else 0, bn.rows, bn.count,
+                            rbn.rows if rbn is not None else 0], f=[1e-5, 0.1]))
+            bn.ready = True
+            if rbn is not None:
+                rbn.ready = True
+            return
+        if rbn is not None and not rbn.ready:
+            self._emit_finalize(rbn.prefix, rbn.C, rbn.rows, rbn.count, rbn.stats, rbn.bnp)
+            rbn.ready = True
+        self.F(eo.ew(L.EW_BN_APPLY, p=[y, bn.bnp, out, res, rbn.bnp if rbn is not None else None],
+                     i=[P, y.c, y.sw, out.sw, res.sw if res else 0, 1 if relu else 0]))
 
     def conv_bn(self, x: View, wname, bnprefix, k, stride, cout, biasname=None):
         """Conv2d (+bias) with BatchNorm partial statistics in the epilogue, then the statistics
@@ -181,11 +229,14 @@ class UNetPlan:
         bias = self.params[biasname] if biasname else None
         self.F(co.conv_fprop(x, self.packed(wname, "fprop"), k, stride, y, bias=bias, stats=stats))
         self.wgrad_ws(x.c, cout, k * k, N, ho, wo)
-        return y, self.bn_finalize(bnprefix, cout, rows, N * ho * wo, stats)
+        return y, self.bn_finalize(bnprefix, cout, rows, N * ho * wo, stats, defer=True)
 
-    def bn_backward(self, prefix, da: View, mask, y: View, bnp, dy: View, da2=None, dz=None,
+    def bn_backward(self, prefix, da: View, mask, y: View, bn, dy: View, da2=None, dz=None,
                     dz_acc=False, dbias=None):
-        """dz = (da [+ da2]) * [mask > 0];  dy = BatchNorm-backward(dz);  dgamma, dbeta (, dbias)."""
+        """dz = (da [+ da2]) * [mask > 0];  dy = BatchNorm-backward(dz);  dgamma, dbeta (, dbias).
+        One persistent launch (EW_BN_BWD_FUSED: reduce, device-wide barrier, fold, apply) unless
+        B2SEG_BN_FUSED=0 selects the three-kernel sequence."""
+        bnp = bn.bnp if isinstance(bn, BNRef) else bn
         P, C_ = y.n * y.h * y.w, y.c
         rows = eo.partial_rows(L.EW_BN_BWD_REDUCE, P, C_)
         self_mask = isinstance(mask, str)  # "self": a = relu(BN(y)), the mask is recomputed from y
@@ -194,6 +245,13 @@ class UNetPlan:
             mask = None
         pp = [da, da2, mask, y, bnp]
         ii = [P, C_, da.sw, da2.sw if da2 else 0, mask.sw if mask else 0, y.sw]
+        if _fused_bn_enabled():
+            self.B(eo.ew(L.EW_BN_BWD_FUSED,
+                         p=pp + [self.part, dy, dz, self.params[prefix + ".weight"], self.gview(prefix + ".weight"),
+                                 self.gview(prefix + ".bias"), dbias],
+                         i=ii + [dy.sw, dz.sw if dz else 0, 2 if dz_acc else 1, 1 if self_mask else 0,
+                                 1 if self.training else 0, 0]))
+            return
         tail = [0, 0, 0, 1 if self_mask else 0]  # i6..i8 unused by REDUCE, i9 = self-mask flag
         self.B(eo.ew(L.EW_BN_BWD_REDUCE, p=pp + [self.part], i=ii + tail))
         coef = self._alloc((3, C_), F32)
@@ -253,7 +311,7 @@ class UNetPlan:
         rows0 = eo.stem_stat_rows(N, H, W)
         st0 = self._alloc((rows0, 2, 64), F32) if self.training else None
         self.F(eo.ew(L.EW_STEM_FWD, p=[self.x_in, P["input_conv.weight"], y0, st0], i=[N, H, W]))
-        bnp0 = self.bn_finalize("bn1", 64, rows0, N * h1 * w1, st0)
+        bnp0 = self.bn_finalize("bn1", 64, rows0, N * h1 * w1, st0, defer=True)
         self.bn_apply(y0, bnp0, x1.v, True)
         self.stored.update({"stem.y": y0, "x1": x1.v})
         h0 = self.act(N, h1 // 2, w1 // 2, 64)
@@ -372,7 +430,7 @@ class UNetPlan:
         ds = (pre + ".downsample.0.weight") in self.params
         if ds:
             yd, bd = self.conv_bn(hin.v, pre + ".downsample.0.weight", pre + ".downsample.1", 1, stride, cout)
-            self.bn_apply(y2, b2, out.v, True, res=yd, rbnp=bd)
+            self.bn_apply(y2, b2, out.v, True, res=yd, rbn=bd)
         else:
             self.bn_apply(y2, b2, out.v, True, res=hin.v)
         self.stored.update({pre + ".y1": y1, pre + ".a1": a1.v, pre + ".y2": y2, pre + ".out": out.v})
@@ -414,7 +472,7 @@ class UNetPlan:
         ds = (pre + ".downsample.0.weight") in self.params
         if ds:
             yd, bd = self.conv_bn(hin.v, pre + ".downsample.0.weight", pre + ".downsample.1", 1, stride, cout)
-            self.bn_apply(y3, b3, out.v, True, res=yd, rbnp=bd)
+            self.bn_apply(y3, b3, out.v, True, res=yd, rbn=bd)
         else:
             self.bn_apply(y3, b3, out.v, True, res=hin.v)
         self.stored.update({pre + ".y1": y1, pre + ".a1": a1.v, pre + ".y2": y2, pre + ".a2": a2.v,
@@ -503,13 +561,13 @@ class UNetPlan:
         yg, bg = self.conv_bn(up.v, a + ".W_g.0.weight", a + ".W_g.1", 1, 1, fint, biasname=a + ".W_g.0.bias")
         ys, bs = self.conv_bn(skip.v, a + ".W_x.0.weight", a + ".W_x.1", 1, 1, fint, biasname=a + ".W_x.0.bias")
         pin = self.act(N, hh, ww, fint)
-        self.bn_apply(yg, bg, pin.v, True, res=ys, rbnp=bs)
+        self.bn_apply(yg, bg, pin.v, True, res=ys, rbn=bs)
         pre = self._alloc((NP,), F32)
         psi = self._alloc((NP,), F32)
         rows = eo.partial_rows(L.EW_DOT1_FWD, NP, fint)
         self.F(eo.ew(L.EW_DOT1_FWD, p=[pin.v, P[a + ".psi.0.weight"], P[a + ".psi.0.bias"], pre,
                                        self.part if self.training else None], i=[NP, fint, pin.v.sw]))
-        bp = self.bn_finalize(a + ".psi.1", 1, rows, NP, self.part)
+        bp = self.bn_finalize(a + ".psi.1", 1, rows, NP, self.part).bnp
         self.F(eo.ew(L.EW_GATE_APPLY, p=[pre, bp, skip.v, outS, psi], i=[NP, skip.v.c, skip.v.sw, outS.sw]))
         self.stored.update({f"att{k}.yg": yg, f"att{k}.ys": ys, f"att{k}.pin": pin.v,
                             f"att{k}.pre": pre.view(N, 1, hh, ww), f"att{k}.out": outS})

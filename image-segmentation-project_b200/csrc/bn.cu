@@ -349,6 +349,377 @@ __global__ void __launch_bounds__(kEwThreads) bn_bwd_apply_kernel(const EwArgs a
   }
 }
 
+// ------------------------------------------------- fused (single-launch) BatchNorm ----
+// Both fused kernels run 512-thread blocks, at most one (backward) or two (forward) per SM.
+constexpr int kBnT = 512;
+
+// Fold the rows of a block-partial buffer [rows][NACC][C] into sm_sum[NACC*C] (fp64), by the whole
+// block, in an order fixed by (rows, C, blockDim) alone -> every block of every run computes
+// bit-identical sums.  Column q = k*C + c; with fewer columns than threads the rows are dealt to
+// blockDim/cols lanes and the lane sums are added in lane order.  Ends with __syncthreads().
+template <int NACC>
+__device__ __forceinline__ void bn_fold_rows(const float* partial, int rows, int C, double* sm_sum,
+                                             double* sm_tmp /* blockDim doubles */) {
+  const int cols = NACC * C, T = blockDim.x, t = threadIdx.x;
+  if (cols >= T) {
+    for (int q = t; q < cols; q += T) {
+      double acc = 0.0;
+      for (int r = 0; r < rows; r += 8) {
+        float v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) v[u] = r + u < rows ? __ldcg(partial + (size_t)(r + u) * cols + q) : 0.0f;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) acc += (double)v[u];
+      }
+      sm_sum[q] = acc;
+    }
+    __syncthreads();
+    return;
+  }
+  const int nl = T / cols, lane = t / cols, q = t - lane * cols;
+  double acc = 0.0;
+  if (lane < nl) {
+    for (int r = lane; r < rows; r += 8 * nl) {
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = r + u * nl < rows ? __ldcg(partial + (size_t)(r + u * nl) * cols + q) : 0.0f;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) acc += (double)v[u];
+    }
+    sm_tmp[t] = acc;
+  }
+  __syncthreads();
+  if (t < cols) {
+    double s = 0.0;
+    for (int l = 0; l < nl; ++l) s += sm_tmp[l * cols + t];
+    sm_sum[t] = s;
+  }
+  __syncthreads();
+}
+
+// (sum, sumsq) -> scale / shift in shared memory; block 0 also publishes bnp = scale, shift, mean,
+// invstd and updates the running statistics: the arithmetic of bn_finalize_kernel, verbatim.
+__device__ __forceinline__ void bn_affine_from_sums(const double* sm_sum, int C, double count, float eps,
+                                                    float mom, const float* gamma, const float* beta,
+                                                    float* rmean, float* rvar, long long* nbt, float* bnp,
+                                                    float* sm_scale, float* sm_shift) {
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const double m = sm_sum[c] / count;
+    double var = sm_sum[C + c] / count - m * m;
+    if (var < 0.0) var = 0.0;
+    const float mean = (float)m;
+    const float invstd = (float)(1.0 / sqrt(var + (double)eps));
+    const float g = gamma ? gamma[c] : 1.0f, b = beta ? beta[c] : 0.0f;
+    const float scale = g * invstd;
+    const float shift = b - mean * scale;
+    sm_scale[c] = scale;
+    sm_shift[c] = shift;
+    if (blockIdx.x == 0) {
+      if (rmean) {
+        const double unb = count > 1.0 ? var * count / (count - 1.0) : var;
+        rmean[c] = (1.0f - mom) * rmean[c] + mom * mean;
+        rvar[c] = (1.0f - mom) * rvar[c] + mom * (float)unb;
+      }
+      if (nbt && c == 0) *nbt += 1;
+      bnp[c] = scale;
+      bnp[C + c] = shift;
+      bnp[2 * C + c] = mean;
+      bnp[3 * C + c] = invstd;
+    }
+  }
+}
+
+// dynamic shared memory: [2C] doubles (sums) | [blockDim] doubles (lanes) | [4C] floats (sc, sf, rs, rf)
+__global__ void __launch_bounds__(kBnT, 2) bn_apply_fused_kernel(const EwArgs a) {
+  pdl_prologue();
+  extern __shared__ __align__(16) unsigned char bn_sm[];
+  const bf16* y = (const bf16*)a.p[0];
+  bf16* out = (bf16*)a.p[1];
+  const bf16* res = (const bf16*)a.p[2];
+  const long long P = a.i[0];
+  const int C = (int)a.i[1];
+  const long long ldy = a.i[2], ldo = a.i[3], ldr = a.i[4];
+  const bool relu = a.i[5] != 0;
+  const bool rnorm = a.p[10] != nullptr;
+  double* sm_sum = reinterpret_cast<double*>(bn_sm);
+  double* sm_tmp = sm_sum + 2 * C;
+  float* sm_aff = reinterpret_cast<float*>(sm_tmp + kBnT);
+  const float eps = a.f[0], mom = a.f[1];
+  bn_fold_rows<2>((const float*)a.p[3], (int)a.i[6], C, sm_sum, sm_tmp);
+  bn_affine_from_sums(sm_sum, C, (double)a.i[7], eps, mom, (const float*)a.p[4], (const float*)a.p[5],
+                      (float*)a.p[6], (float*)a.p[7], (long long*)a.p[8], (float*)a.p[9], sm_aff, sm_aff + C);
+  __syncthreads();
+  if (rnorm) {
+    bn_fold_rows<2>((const float*)a.p[10], (int)a.i[8], C, sm_sum, sm_tmp);
+    bn_affine_from_sums(sm_sum, C, (double)a.i[7], eps, mom, (const float*)a.p[11], (const float*)a.p[12],
+                        (float*)a.p[13], (float*)a.p[14], (long long*)a.p[15], (float*)a.p[16],
+                        sm_aff + 2 * C, sm_aff + 3 * C);
+    __syncthreads();
+  }
+  const int cv = C >> 3;
+  BnApplyCh ch;
+  if (kBnT % cv == 0) {
+    const int ppb = kBnT / cv;
+    const int c0 = (threadIdx.x % cv) * 8;
+    const long long pstep = (long long)gridDim.x * ppb;
+    ch.sc = ld_f8(sm_aff + c0);
+    ch.sf = ld_f8(sm_aff + C + c0);
+    if (rnorm) {
+      ch.rs = ld_f8(sm_aff + 2 * C + c0);
+      ch.rf = ld_f8(sm_aff + 3 * C + c0);
+    }
+    long long p = (long long)blockIdx.x * ppb + threadIdx.x / cv;
+    for (; p + pstep < P; p += 2 * pstep) {
+      const long long q = p + pstep;
+      const uint4 y0 = bn_ld_raw8(y + p * ldy + c0), y1 = bn_ld_raw8(y + q * ldy + c0);
+      uint4 r0 = make_uint4(0, 0, 0, 0), r1 = r0;
+      if (res) {
+        r0 = bn_ld_raw8(res + p * ldr + c0);
+        r1 = bn_ld_raw8(res + q * ldr + c0);
+      }
+      st_bf8(out + p * ldo + c0, bn_apply_one(y0, r0, res != nullptr, ch, rnorm, relu));
+      st_bf8(out + q * ldo + c0, bn_apply_one(y1, r1, res != nullptr, ch, rnorm, relu));
+    }
+    if (p < P) {
+      const uint4 y0 = bn_ld_raw8(y + p * ldy + c0);
+      uint4 r0 = make_uint4(0, 0, 0, 0);
+      if (res) r0 = bn_ld_raw8(res + p * ldr + c0);
+      st_bf8(out + p * ldo + c0, bn_apply_one(y0, r0, res != nullptr, ch, rnorm, relu));
+    }
+    return;
+  }
+  const long long total = P * cv;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    long long p;
+    int c8;
+    ew_divmod(idx, cv, p, c8);
+    const int c0 = c8 * 8;
+    ch.sc = ld_f8(sm_aff + c0);
+    ch.sf = ld_f8(sm_aff + C + c0);
+    const uint4 y0 = bn_ld_raw8(y + p * ldy + c0);
+    uint4 r0 = make_uint4(0, 0, 0, 0);
+    if (res) {
+      r0 = bn_ld_raw8(res + p * ldr + c0);
+      if (rnorm) {
+        ch.rs = ld_f8(sm_aff + 2 * C + c0);
+        ch.rf = ld_f8(sm_aff + 3 * C + c0);
+      }
+    }
+    st_bf8(out + p * ldo + c0, bn_apply_one(y0, r0, res != nullptr, ch, rnorm, relu));
+  }
+}
+
+// Device-wide barrier of a grid whose blocks are all co-resident (<= one per SM).  Sense-reversing
+// on a generation word, so it needs no host reset between launches or graph replays.  Bounded: a
+// scheduling surprise traps instead of hanging the GPU.
+static __device__ unsigned g_bn_bar_count = 0;
+static __device__ unsigned g_bn_bar_gen = 0;
+__device__ __forceinline__ void bn_grid_barrier() {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    volatile unsigned* genp = &g_bn_bar_gen;
+    const unsigned gen = *genp;  // read BEFORE arriving: the generation cannot advance without us
+    __threadfence();
+    if (atomicAdd(&g_bn_bar_count, 1u) == gridDim.x - 1) {
+      g_bn_bar_count = 0;
+      __threadfence();
+      atomicAdd(&g_bn_bar_gen, 1u);
+    } else {
+      const long long t0 = clock64();
+      while (*genp == gen) {
+        __nanosleep(64);
+        if (clock64() - t0 > 8000000000LL) {  // ~4 s
+          printf("b2seg: bn grid barrier timeout (block %d of %d)\n", blockIdx.x, gridDim.x);
+          __trap();
+        }
+      }
+    }
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+// dynamic shared memory: [2][pl][C] floats (block reduction; reused as [2C] doubles + [blockDim]
+// doubles for the fold) | [3C] floats (A, B, D).
+// 256 threads, <= 128 registers, <= ~22 KB of shared memory and ONE block per SM: the block fits
+// beside a weight-gradient CTA of the side branch (192 threads, ~50 registers, 197 KB), so the
+// barrier never has to wait for the side branch to drain.
+constexpr int kBnB = 256;
+struct BnBwdLean {
+  uint4 d1, m, y, old;
+};
+template <bool HAS_ACT>
+__device__ __forceinline__ BnBwdLean bn_lean_fetch(const BnBwdIn& s, long long p, int c0) {
+  BnBwdLean r;
+  r.d1 = bn_ld_raw8(s.da1 + p * s.ld1 + c0);
+  if (HAS_ACT) r.m = bn_ld_raw8(s.act + p * s.lda + c0);
+  r.y = bn_ld_raw8(s.y + p * s.ldy + c0);
+  return r;
+}
+template <bool HAS_ACT>
+__device__ __forceinline__ void bn_lean_dz(const BnBwdIn& s, const F8& sc, const F8& sf, const BnBwdLean& r,
+                                           F8& dz, F8& y) {
+  dz = bn_unpack8(r.d1);
+  if (HAS_ACT) {
+    const F8 m = bn_unpack8(r.m);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dz.v[j] = m.v[j] > 0.0f ? dz.v[j] : 0.0f;
+  }
+  y = bn_unpack8(r.y);
+  if (!HAS_ACT && s.self_mask) {  // the forward pass stored bf16(relu(fma(y, scale, shift))): same arithmetic
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float act = __bfloat162float(__float2bfloat16_rn(fmaf(y.v[j], sc.v[j], sf.v[j])));
+      dz.v[j] = act > 0.0f ? dz.v[j] : 0.0f;
+    }
+  }
+}
+
+template <bool HAS_ACT>
+__global__ void __launch_bounds__(kBnB, 1) bn_bwd_fused_kernel(const EwArgs a) {
+  pdl_prologue();
+  extern __shared__ __align__(16) unsigned char bn_sm[];
+  BnBwdIn s = bn_bwd_in(a);
+  s.self_mask = (int)a.i[9];
+  float* partial = (float*)a.p[5];
+  bf16* dy = (bf16*)a.p[6];
+  bf16* dzo = (bf16*)a.p[7];
+  const long long P = a.i[0], lddy = a.i[6], lddz = a.i[7];
+  const bool dz_acc = dzo && (int)a.i[8] == 2;
+  const bool training = a.i[10] != 0, accumulate = a.i[11] != 0;
+  const int C = s.C, cv = C >> 3;
+  const int pl = kBnB / cv > 0 ? kBnB / cv : 1;
+  const int lc = threadIdx.x % cv, lp = threadIdx.x / cv;
+  const int c0 = lc * 8;
+  const bool active = lp < pl;
+  const long long pstep = (long long)gridDim.x * pl;
+  const long long pfirst = (long long)blockIdx.x * pl + lp;
+  float* red = reinterpret_cast<float*>(bn_sm);
+  const size_t red_bytes = (size_t)2 * pl * C * sizeof(float);
+  const size_t fold_bytes = (size_t)(2 * C + kBnB) * sizeof(double);
+  float* sm_k = reinterpret_cast<float*>(bn_sm + (red_bytes > fold_bytes ? red_bytes : fold_bytes));
+
+  // ---- phase 1: block partials of (sum dz, sum dz*y), four pixels in flight
+  F8 sc, sf;
+  if (!HAS_ACT && s.self_mask) {
+    sc = ld_f8(s.bnp + c0);
+    sf = ld_f8(s.bnp + C + c0);
+  }
+  float acc[2][8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[0][j] = acc[1][j] = 0.0f;
+  long long nmine = 0;  // pixels this thread owns: pfirst + k*pstep, k < nmine
+  if (active && pfirst < P) nmine = (P - pfirst + pstep - 1) / pstep;
+  {
+    constexpr int U1 = 4;
+    long long k = 0;
+    for (; k + U1 <= nmine; k += U1) {
+      BnBwdLean r[U1];
+#pragma unroll
+      for (int u = 0; u < U1; ++u) r[u] = bn_lean_fetch<HAS_ACT>(s, pfirst + (k + u) * pstep, c0);
+#pragma unroll
+      for (int u = 0; u < U1; ++u) {
+        F8 dz, yv;
+        bn_lean_dz<HAS_ACT>(s, sc, sf, r[u], dz, yv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { acc[0][j] += dz.v[j]; acc[1][j] = fmaf(dz.v[j], yv.v[j], acc[1][j]); }
+      }
+    }
+    for (; k < nmine; ++k) {
+      F8 dz, yv;
+      bn_lean_dz<HAS_ACT>(s, sc, sf, bn_lean_fetch<HAS_ACT>(s, pfirst + k * pstep, c0), dz, yv);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { acc[0][j] += dz.v[j]; acc[1][j] = fmaf(dz.v[j], yv.v[j], acc[1][j]); }
+    }
+  }
+  if (active) {
+#pragma unroll
+    for (int k = 0; k < 2; ++k)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) red[((size_t)k * pl + lp) * C + c0 + j] = acc[k][j];
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < 2 * C; idx += blockDim.x) {
+    const int k = idx / C, c = idx % C;
+    float v = 0.0f;
+    for (int l = 0; l < pl; ++l) v += red[((size_t)k * pl + l) * C + c];
+    partial[((size_t)blockIdx.x * 2 + k) * C + c] = v;
+  }
+  bn_grid_barrier();
+
+  // ---- every block folds the gridDim.x rows; per-channel constants as BN_BWD_FINALIZE + bn_bwd_lin
+  double* sm_sum = reinterpret_cast<double*>(bn_sm);
+  bn_fold_rows<2>(partial, (int)gridDim.x, C, sm_sum, sm_sum + 2 * C);
+  {
+    const float* gamma = (const float*)a.p[8];
+    float* dgamma = (float*)a.p[9];
+    float* dbeta = (float*)a.p[10];
+    float* dbias = (float*)a.p[11];
+    const double count = (double)P;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      const double sd = sm_sum[c];
+      const float mean = s.bnp[2 * C + c], inv = s.bnp[3 * C + c];
+      const double q = (double)inv * (sm_sum[C + c] - (double)mean * sd);
+      const float g = gamma ? gamma[c] : 1.0f;
+      const float c1 = g * inv;
+      const float c2 = training ? (float)(sd / count) : 0.0f;
+      const float c3 = training ? (float)(q / count) : 0.0f;
+      const float t = c3 * inv;
+      sm_k[c] = c1;
+      sm_k[C + c] = -c1 * t;
+      sm_k[2 * C + c] = c1 * (t * mean - c2);
+      if (blockIdx.x == 0) {
+        if (dgamma) dgamma[c] = accumulate ? dgamma[c] + (float)q : (float)q;
+        if (dbeta) dbeta[c] = accumulate ? dbeta[c] + (float)sd : (float)sd;
+        if (dbias) {
+          const float vb = training ? 0.0f : c1 * (float)sd;
+          dbias[c] = accumulate ? dbias[c] + vb : vb;
+        }
+      }
+    }
+  }
+  __syncthreads();
+
+  // ---- phase 2: dy = A*dz + B*y + D over the same pixels, last read first (L2-hot)
+  if (!active) return;
+  const F8 kA = ld_f8(sm_k + c0), kB = ld_f8(sm_k + C + c0), kD = ld_f8(sm_k + 2 * C + c0);
+  auto emit = [&](const BnBwdLean& r, long long p) {
+    F8 dz, yv, o;
+    bn_lean_dz<HAS_ACT>(s, sc, sf, r, dz, yv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o.v[j] = fmaf(kA.v[j], dz.v[j], fmaf(kB.v[j], yv.v[j], kD.v[j]));
+    st_bf8(dy + p * lddy + c0, o);
+    if (dzo) {
+      if (dz_acc) {
+        const F8 old = bn_unpack8(r.old);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) dz.v[j] += old.v[j];
+      }
+      st_bf8(dzo + p * lddz + c0, dz);
+    }
+  };
+  constexpr int U = 4;
+  long long k = nmine;
+  for (; k >= U; k -= U) {
+    BnBwdLean r[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long p = pfirst + (k - 1 - u) * pstep;
+      r[u] = bn_lean_fetch<HAS_ACT>(s, p, c0);
+      if (dz_acc) r[u].old = bn_ld_raw8(dzo + p * lddz + c0);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) emit(r[u], pfirst + (k - 1 - u) * pstep);
+  }
+  for (; k >= 1; --k) {
+    const long long p = pfirst + (k - 1) * pstep;
+    BnBwdLean r0 = bn_lean_fetch<HAS_ACT>(s, p, c0);
+    if (dz_acc) r0.old = bn_ld_raw8(dzo + p * lddz + c0);
+    emit(r0, p);
+  }
+}
+
 // ---------------------------------------------------------------------- COLSUM ----
 __global__ void __launch_bounds__(kEwThreads) colsum_kernel(const EwArgs a) {
   pdl_prologue();
@@ -486,6 +857,31 @@ EW_LAUNCHER(launch_colsum, colsum_kernel)
 EW_LAUNCHER(launch_colsum_finalize, colsum_finalize_kernel)
 EW_LAUNCHER(launch_pack, pack_kernel)
 EW_LAUNCHER(launch_fill, fill_kernel)
+EW_LAUNCHER(launch_bn_apply_fused, bn_apply_fused_kernel)
+EW_LAUNCHER(launch_bn_bwd_fused_act, bn_bwd_fused_kernel<true>)
+EW_LAUNCHER(launch_bn_bwd_fused_noact, bn_bwd_fused_kernel<false>)
+
+constexpr size_t kBnFusedSmemMax = 96 * 1024;
+int bn_fused_attrs() {
+  static bool done = false;
+  if (!done) {
+    B2_CHECK_CUDA(cudaFuncSetAttribute(bn_apply_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)kBnFusedSmemMax));
+    B2_CHECK_CUDA(cudaFuncSetAttribute(bn_bwd_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)kBnFusedSmemMax));
+    B2_CHECK_CUDA(cudaFuncSetAttribute(bn_bwd_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)kBnFusedSmemMax));
+    done = true;
+  }
+  return B2SEG_OK;
+}
+
+size_t bn_bwd_fused_smem(int C) {
+  const int cv = C / 8;
+  const int pl = kBnB / cv > 0 ? kBnB / cv : 1;
+  const size_t red = (size_t)2 * pl * C * sizeof(float), fold = (size_t)(2 * C + kBnB) * sizeof(double);
+  return (red > fold ? red : fold) + (size_t)3 * C * sizeof(float);
+}
 
 bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
@@ -575,6 +971,42 @@ int ew_plan_bn(const b2seg_ew_desc* d, EwPlan* pl) {
       pl->grid = dim3((unsigned)i[1]);  /* one block per 32 x 32 x T tile */
       pl->block = dim3(kEwThreads);
       return B2SEG_OK;
+    }
+    case B2SEG_EW_BN_APPLY_FUSED: {
+      EW_REQ_VEC(i[1]);
+      B2_REQUIRE(p[0] && p[1] && p[3] && p[9] && i[0] >= 1 && i[6] >= 1 && i[7] >= 1, "bn_apply_fused: null argument");
+      B2_REQUIRE(!p[10] || (p[2] && p[16] && i[8] >= 1), "bn_apply_fused: residual BatchNorm needs res, bnp and rows");
+      B2_REQUIRE(i[2] % 8 == 0 && i[3] % 8 == 0 && i[4] % 8 == 0 && aligned16(p[0]) &&
+                     aligned16(p[1]) && aligned16(p[2]),
+                 "bn_apply_fused: leading dimensions / pointers must be 16-byte aligned");
+      pl->fn = launch_bn_apply_fused;
+      long long b = (i[0] * (i[1] / 8) + kBnT * 4 - 1) / (kBnT * 4);  // >= 4 vectors per thread
+      const long long cap = 2ll * b2_num_sms();
+      pl->grid = dim3((unsigned)(b > cap ? cap : (b < 1 ? 1 : b)));
+      pl->block = dim3(kBnT);
+      pl->smem = (size_t)(2 * i[1] + kBnT) * sizeof(double) + (size_t)4 * i[1] * sizeof(float);
+      pl->smem_limit = kBnFusedSmemMax;
+      return bn_fused_attrs();
+    }
+    case B2SEG_EW_BN_BWD_FUSED: {
+      EW_REQ_VEC(i[1]);
+      B2_REQUIRE(p[0] && p[3] && p[4] && p[5] && p[6] && i[0] >= 1, "bn_bwd_fused: null argument");
+      B2_REQUIRE(!p[1], "bn_bwd_fused: a second upstream gradient (da2) takes the three-kernel sequence");
+      B2_REQUIRE(i[2] % 8 == 0 && i[3] % 8 == 0 && i[4] % 8 == 0 && i[5] % 8 == 0 && i[6] % 8 == 0 &&
+                     i[7] % 8 == 0 && aligned16(p[0]) && aligned16(p[1]) && aligned16(p[2]) &&
+                     aligned16(p[3]) && aligned16(p[6]) && aligned16(p[7]),
+                 "bn_bwd_fused: leading dimensions / pointers must be 16-byte aligned");
+      B2_REQUIRE(!p[7] || i[8] == 1 || i[8] == 2, "bn_bwd_fused: dz mode must be 1 or 2");
+      pl->fn = p[2] ? launch_bn_bwd_fused_act : launch_bn_bwd_fused_noact;
+      const int cvv = (int)i[1] / 8;
+      const int plv = kBnB / cvv > 0 ? kBnB / cvv : 1;
+      long long b = (i[0] + plv - 1) / plv;  // at least one pixel per lane
+      const long long cap = b2_num_sms();     // ONE block per SM: the device-wide barrier needs co-residency
+      pl->grid = dim3((unsigned)(b > cap ? cap : (b < 1 ? 1 : b)));
+      pl->block = dim3(kBnB);
+      pl->smem = bn_bwd_fused_smem((int)i[1]);
+      pl->smem_limit = kBnFusedSmemMax;
+      return bn_fused_attrs();
     }
     case B2SEG_EW_FILL: {
       B2_REQUIRE(p[0] && i[0] >= 4 && i[0] % 4 == 0, "fill: bytes must be a positive multiple of 4");

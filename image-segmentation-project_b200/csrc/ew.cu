@@ -31,6 +31,7 @@ extern "C" int b2seg_ew_create(const b2seg_ew_desc* d, b2seg_op** out) {
     case B2SEG_EW_BN_FINALIZE: case B2SEG_EW_BN_APPLY: case B2SEG_EW_BN_BWD_REDUCE:
     case B2SEG_EW_BN_BWD_FINALIZE: case B2SEG_EW_BN_BWD_APPLY: case B2SEG_EW_COLSUM:
     case B2SEG_EW_COLSUM_FINALIZE: case B2SEG_EW_PACK: case B2SEG_EW_FILL:
+    case B2SEG_EW_BN_APPLY_FUSED: case B2SEG_EW_BN_BWD_FUSED:
       rc = ew_plan_bn(d, &plan);
       break;
     case B2SEG_EW_STEM_FWD: case B2SEG_EW_STEM_WGRAD: case B2SEG_EW_MAXPOOL_FWD:
@@ -50,13 +51,14 @@ extern "C" int b2seg_ew_create(const b2seg_ew_desc* d, b2seg_op** out) {
       return B2SEG_EINVAL;
   }
   if (rc != B2SEG_OK) return rc;
-  if (plan.smem > 48 * 1024) {
+  if (plan.smem > (plan.smem_limit ? plan.smem_limit : (size_t)48 * 1024)) {
     b2seg_set_error("ew_create: kind %d needs %zu bytes of shared memory", d->kind, plan.smem);
     return B2SEG_EINVAL;
   }
   auto* op = new (std::nothrow) EwOp();
   B2_REQUIRE(op, "ew_create: out of host memory");
-  for (int k = 0; k < 10; ++k) { op->args.p[k] = d->p[k]; op->args.i[k] = d->i[k]; }
+  for (int k = 0; k < B2SEG_EW_NPTR; ++k) op->args.p[k] = d->p[k];
+  for (int k = 0; k < B2SEG_EW_NINT; ++k) op->args.i[k] = d->i[k];
   for (int k = 0; k < 4; ++k) op->args.f[k] = d->f[k];
   op->plan = plan;
   op->kind = d->kind;

@@ -8,8 +8,8 @@
 #include "ops.cuh"
 
 struct EwArgs {
-  void* p[10];
-  long long i[10];
+  void* p[B2SEG_EW_NPTR];
+  long long i[B2SEG_EW_NINT];
   float f[4];
 };
 
@@ -20,6 +20,7 @@ struct EwPlan {
   dim3 grid, block;
   size_t smem;
   int launches;
+  size_t smem_limit;  // 0 = the default 48 KB; planners that opt a kernel in to more set this
 };
 
 // planners, one per source file; each fills `plan` for desc->kind or returns an error

@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define B2SEG_ABI_VERSION 1
+#define B2SEG_ABI_VERSION 2
 
 #define B2SEG_OK 0
 #define B2SEG_EINVAL (-1)  /* bad argument / unsupported shape            */
@@ -400,6 +400,27 @@ enum {
   B2SEG_EW_SE_BWD_APPLY = 22,
   /* p0 dst, i0 bytes (multiple of 4), i1 32-bit pattern */
   B2SEG_EW_FILL = 23,
+  /* Training-mode BatchNorm forward in ONE launch (BN_FINALIZE + BN_APPLY): every block folds the
+   * conv epilogue's partial rows itself (fixed order, fp64) into scale / shift, block 0 also writes
+   * bnp and updates the running statistics; then out = act(y*scale+shift (+ res | + BN_r(res))).
+   * With p10 the residual carries its own training-mode BatchNorm (downsample branch, gate W_x).
+   * p0 y bf16  p1 out bf16  p2 res bf16|NULL
+   * p3 partial f32 [rows][2][C]  p4 gamma  p5 beta  p6 running_mean  p7 running_var
+   * p8 num_batches_tracked|NULL  p9 out bnp f32 [4][C]
+   * p10 res partial|NULL  p11..p16 = gamma, beta, running_mean, running_var, nbt, bnp of the residual BN
+   * i0 P  i1 C  i2 ld_y  i3 ld_out  i4 ld_res  i5 relu  i6 rows  i7 count  i8 res rows
+   * f0 eps  f1 momentum */
+  B2SEG_EW_BN_APPLY_FUSED = 24,
+  /* BatchNorm backward in ONE persistent launch (BN_BWD_REDUCE + _FINALIZE + _APPLY): phase 1 block
+   * partials of (sum dz, sum dz*y); device-wide barrier (all blocks are co-resident: one per SM);
+   * every block folds the partial rows (fixed order, fp64) into the three per-channel constants,
+   * block 0 writes dgamma / dbeta / dbias; phase 2 walks the block's pixels in reverse (they are
+   * the most recently read, L2-hot) and writes dy (and dz).
+   * p0 da1 bf16  p1 da2 bf16|NULL  p2 a bf16|NULL  p3 y bf16  p4 bnp  p5 scratch partial f32 [grid][2][C]
+   * p6 dy bf16  p7 dz bf16|NULL  p8 gamma|NULL  p9 dgamma|NULL  p10 dbeta|NULL  p11 dbias|NULL
+   * i0 P  i1 C  i2 ld_da1  i3 ld_da2  i4 ld_a  i5 ld_y  i6 ld_dy  i7 ld_dz  i8 dz mode (1 store,
+   * 2 accumulate)  i9 self-mask  i10 training  i11 accumulate into dgamma/dbeta/dbias */
+  B2SEG_EW_BN_BWD_FUSED = 25,
 };
 
 /* out[t][a][b] = bf16(in[a*sa + b*sb + t*st]); `start` = number of 32x32xT tiles
@@ -412,10 +433,12 @@ typedef struct b2seg_pack_job {
   int64_t start;
 } b2seg_pack_job;
 
+#define B2SEG_EW_NPTR 18
+#define B2SEG_EW_NINT 12
 typedef struct b2seg_ew_desc {
   int32_t kind;
-  void* p[10];
-  int64_t i[10];
+  void* p[B2SEG_EW_NPTR];
+  int64_t i[B2SEG_EW_NINT];
   float f[4];
 } b2seg_ew_desc;
 

