@@ -85,6 +85,11 @@ class EwDesc(C.Structure):
     _fields_ = [("kind", C.c_int32), ("p", C.c_void_p * 18), ("i", C.c_int64 * 12), ("f", C.c_float * 4)]
 
 
+class WarpItem(C.Structure):
+    _fields_ = [("minv", C.c_double * 6), ("interp", C.c_int32 * 4), ("cval", C.c_int32 * 4),
+                ("border", C.c_int32), ("pad", C.c_int32)]
+
+
 class PackJob(C.Structure):
     _fields_ = [("inp", C.c_void_p), ("out", C.c_void_p), ("T", C.c_int32), ("A", C.c_int32),
                 ("B", C.c_int32), ("pad", C.c_int32), ("sa", C.c_int64), ("sb", C.c_int64),
@@ -112,6 +117,25 @@ _SIGS = {
     "b2seg_aug_permute_u8": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "b2seg_aug_warp_affine_u8": (C.c_int, [_vp, _vp, _i, _i, _i, C.POINTER(C.c_double), _i, _i, _i, _vp]),
     "b2seg_aug_remap_u8": (C.c_int, [_vp, _vp, _i, _i, _i, _vp, _vp, _i, _i, _i, _vp]),
+    "b2seg_aug_warp_affine_batch_u8": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _vp, _vp]),
+    "b2seg_aug_remap_batch_u8": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _i64, _vp, _vp]),
+    "b2seg_aug_lut_u8": (C.c_int, [_vp, _vp, _i64, _vp, _vp]),
+    "b2seg_aug_hist_u8": (C.c_int, [_vp, _i64, _i, _vp, _vp]),
+    "b2seg_aug_affine_lut_u8": (C.c_int, [_vp, _vp, _i64, _vp, C.c_double, C.c_double, _vp]),
+    "b2seg_aug_fill_rects_u8": (C.c_int, [_vp, _i, _i, _vp, _i, _i, _vp]),
+    "b2seg_aug_gauss_noise_u8": (C.c_int, [_vp, _vp, _i64, C.c_float, C.c_float, C.c_uint64, _vp]),
+    "b2seg_aug_filter2d_u8": (C.c_int, [_vp, _vp, _i, _i, _i, _vp, _i, _vp]),
+    "b2seg_aug_pad_u8": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "b2seg_aug_uniform_f32": (C.c_int, [_vp, _i64, C.c_uint64, _vp]),
+    "b2seg_aug_blur1d_f32": (C.c_int, [_vp, _vp, _i, _i, _i, _vp, _i, _i, C.c_float, _i, _vp]),
+    "b2seg_resize_nearest_u8": (C.c_int, [_vp, _i, _i, _i, _vp, _vp, _i, _i, _vp, _vp, _vp]),
+    "b2seg_resize_linear_u8": (C.c_int, [_vp, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp]),
+    "b2seg_resize_areafast_u8": (C.c_int, [_vp, _i, _i, _i, _vp, _i, _i, _vp]),
+    "b2seg_resize_area_u8": (C.c_int, [_vp, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "b2seg_pre_percentile_lut": (C.c_int, [_vp, _i, _i64, C.c_double, C.c_double, _vp, _vp, _vp]),
+    "b2seg_pre_clahe_workspace_bytes": (_sz, [_i, _i, _i]),
+    "b2seg_pre_clahe_normalize": (C.c_int, [_vp, _i, _i, _i, _vp, C.c_double, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "b2seg_pre_scale255_f32": (C.c_int, [_vp, _i, _i64, _vp, _vp]),
     "b2seg_adam_step": (C.c_int, [_vp, _i, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float,
                                   C.c_double, _vp]),
     "b2seg_op_run": (C.c_int, [_vp, _vp]),

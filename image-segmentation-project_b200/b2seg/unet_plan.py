@@ -59,9 +59,20 @@ class BNRef:
         self.rows, self.count, self.ready = rows, count, ready
 
 
-def _fused_bn_enabled():
+def _fused_bn_fwd():
+    """EW_BN_APPLY_FUSED (the consumer folds the conv epilogue's partial statistics itself).  Off by
+    default: every block re-reads all partial rows (<= 296 x 2C floats), which costs more than the
+    finalize launch it saves (measured: DESIGN 3.7); B2SEG_BN_FUSED_FWD=1 turns it on."""
     import os
-    return os.environ.get("B2SEG_BN_FUSED", "1") != "0"
+    return os.environ.get("B2SEG_BN_FUSED_FWD", "0") == "1"
+
+
+def _fused_bn_bwd_max_bytes():
+    """EW_BN_BWD_FUSED is planned for BatchNorm layers whose pre-BN tensor is at most this many
+    bytes (B2SEG_BN_FUSED_BWD_MB, default below; 0 = never): small layers are launch-latency bound
+    and their operands stay L2-resident between the two phases."""
+    import os
+    return float(os.environ.get("B2SEG_BN_FUSED_BWD_MB", "24")) * 2 ** 20
 
 
 class UNetPlan:
@@ -179,7 +190,7 @@ class UNetPlan:
         if self.training and count <= 1:
             raise ValueError(f"Expected more than 1 value per channel when training ({prefix})")
         bnp = self._alloc((4, C_), F32)
-        if defer and self.training and C_ % 8 == 0 and _fused_bn_enabled():
+        if defer and self.training and C_ % 8 == 0 and _fused_bn_fwd():
             return BNRef(prefix, C_, bnp, partial, rows, count, False)
         self._emit_finalize(prefix, C_, rows, count, partial, bnp)
         return BNRef(prefix, C_, bnp, partial, rows, count, True)
@@ -234,8 +245,9 @@ class UNetPlan:
     def bn_backward(self, prefix, da: View, mask, y: View, bn, dy: View, da2=None, dz=None,
                     dz_acc=False, dbias=None):
         """dz = (da [+ da2]) * [mask > 0];  dy = BatchNorm-backward(dz);  dgamma, dbeta (, dbias).
-        One persistent launch (EW_BN_BWD_FUSED: reduce, device-wide barrier, fold, apply) unless
-        B2SEG_BN_FUSED=0 selects the three-kernel sequence."""
+        One persistent launch (EW_BN_BWD_FUSED: reduce, device-wide barrier, distributed fold,
+        barrier, apply) for layers up to _fused_bn_bwd_max_bytes(); the reduce / finalize / apply
+        sequence above that."""
         bnp = bn.bnp if isinstance(bn, BNRef) else bn
         P, C_ = y.n * y.h * y.w, y.c
         rows = eo.partial_rows(L.EW_BN_BWD_REDUCE, P, C_)
@@ -245,7 +257,7 @@ class UNetPlan:
             mask = None
         pp = [da, da2, mask, y, bnp]
         ii = [P, C_, da.sw, da2.sw if da2 else 0, mask.sw if mask else 0, y.sw]
-        if _fused_bn_enabled():
+        if P * C_ * 2 <= _fused_bn_bwd_max_bytes():
             self.B(eo.ew(L.EW_BN_BWD_FUSED,
                          p=pp + [self.part, dy, dz, self.params[prefix + ".weight"], self.gview(prefix + ".weight"),
                                  self.gview(prefix + ".bias"), dbias],

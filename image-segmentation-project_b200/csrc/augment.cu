@@ -233,10 +233,29 @@ constexpr int FPITCH = FOOT + 8;  // bytes; multiple of 4 so footprint rows take
 // horizontally adjacent pixels -> one 32-bit store.  Affine coordinates come from four 32-entry
 // integer tables (the double-precision products are evaluated once per tile row / column, not per
 // pixel); the source footprint of an affine tile is the bounding box of its four corners.
+//
+// Table mode (`items` != NULL): blockIdx.z = item * ppi + plane; every item brings its own matrix
+// (or its own pair of maps, `map_stride` floats apart) and every plane of an item its own
+// interpolation and constant -- image (bilinear) and mask (nearest) of ALL augmented copies of a
+// batch are one launch.
 __global__ void __launch_bounds__(256)
     warp_u8_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, WarpArgs a,
-                   int planes, int pz, int vec_ok) {
+                   int planes, int pz, int vec_ok, const b2seg_warp_item* __restrict__ items, int ppi,
+                   long long map_stride) {
   __shared__ __align__(16) uint8_t foot[FOOT][FPITCH];
+  if (items != nullptr) {
+    const int item = blockIdx.z / ppi, pl = blockIdx.z - item * ppi;
+    const b2seg_warp_item& it = items[item];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) a.m[i] = it.minv[i];
+    a.interp = it.interp[pl];
+    a.cval = it.cval[pl] & 255;
+    a.border = it.border;
+    if (a.map_x != nullptr) {
+      a.map_x += (size_t)item * map_stride;
+      a.map_y += (size_t)item * map_stride;
+    }
+  }
   __shared__ int s_ad[TILE], s_bd[TILE], s_X0[TILE], s_Y0[TILE];
   __shared__ int s_box[4];
   const int h = a.h, w = a.w;
@@ -321,7 +340,8 @@ __global__ void __launch_bounds__(256)
   const bool staged = bx0 != INT_MAX && bw > 0 && bh > 0 && bwords * 4 <= FPITCH && bh <= FOOT;
   const bool valid_row = y < h;
 
-  const int p_begin = blockIdx.z * pz, p_end = min(planes, p_begin + pz);
+  const int p_begin = items ? (int)blockIdx.z : blockIdx.z * pz;
+  const int p_end = items ? p_begin + 1 : min(planes, p_begin + pz);
   for (int plane = p_begin; plane < p_end; ++plane) {
     const uint8_t* s = src + (size_t)plane * h * w;
     uint8_t* d = dst + (size_t)plane * h * w;
@@ -396,7 +416,20 @@ int launch_warp(const uint8_t* src, uint8_t* dst, int planes, const WarpArgs& a,
   const int vec_ok = (a.w % 4 == 0) && (reinterpret_cast<uintptr_t>(src) % 4 == 0) &&
                      (reinterpret_cast<uintptr_t>(dst) % 4 == 0);
   dim3 grid(tx, ty, gz);
-  warp_u8_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, dst, a, planes, pz, vec_ok);
+  warp_u8_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, dst, a, planes, pz, vec_ok, nullptr, 1, 0);
+  B2_CHECK_CUDA(cudaGetLastError());
+  return B2SEG_OK;
+}
+
+int launch_warp_batch(const uint8_t* src, uint8_t* dst, int n_items, int ppi, WarpArgs a,
+                      const b2seg_warp_item* items, long long map_stride, void* stream) {
+  const int tx = (a.w + TILE - 1) / TILE, ty = (a.h + TILE - 1) / TILE;
+  const size_t plane_bytes = (size_t)a.h * a.w;
+  const int vec_ok = (a.w % 4 == 0) && (plane_bytes % 4 == 0) && (reinterpret_cast<uintptr_t>(src) % 4 == 0) &&
+                     (reinterpret_cast<uintptr_t>(dst) % 4 == 0);
+  dim3 grid(tx, ty, n_items * ppi);
+  warp_u8_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, dst, a, n_items * ppi, 1, vec_ok, items, ppi,
+                                                           map_stride);
   B2_CHECK_CUDA(cudaGetLastError());
   return B2SEG_OK;
 }
@@ -484,4 +517,31 @@ extern "C" int b2seg_aug_remap_u8(const uint8_t* src, uint8_t* dst, int planes, 
   a.map_x = map_x; a.map_y = map_y;
   a.h = h; a.w = w; a.interp = interp; a.border = border; a.cval = border_value & 255;
   return launch_warp(src, dst, planes, a, stream);
+}
+
+// Batched warps: `items` is a DEVICE table of n_items entries; planes are [n_items][ppi][h][w].
+extern "C" int b2seg_aug_warp_affine_batch_u8(const uint8_t* src, uint8_t* dst, int n_items, int ppi, int h,
+                                              int w, const b2seg_warp_item* items, void* stream) {
+  B2_REQUIRE(src && dst && items && src != dst, "aug_warp_affine_batch: bad pointers");
+  B2_REQUIRE(n_items > 0 && ppi >= 1 && ppi <= 4 && (long long)n_items * ppi <= 65535 && h > 0 && w > 0,
+             "aug_warp_affine_batch: bad shape (%d items x %d planes)", n_items, ppi);
+  WarpArgs a;
+  for (int i = 0; i < 6; ++i) a.m[i] = 0.0;
+  a.map_x = a.map_y = nullptr;
+  a.h = h; a.w = w; a.interp = B2SEG_INTERP_LINEAR; a.border = B2SEG_BORDER_CONSTANT; a.cval = 0;
+  return launch_warp_batch(src, dst, n_items, ppi, a, items, 0, stream);
+}
+
+extern "C" int b2seg_aug_remap_batch_u8(const uint8_t* src, uint8_t* dst, int n_items, int ppi, int h, int w,
+                                        const float* map_x, const float* map_y, int64_t map_stride,
+                                        const b2seg_warp_item* items, void* stream) {
+  B2_REQUIRE(src && dst && items && map_x && map_y && src != dst, "aug_remap_batch: bad pointers");
+  B2_REQUIRE(n_items > 0 && ppi >= 1 && ppi <= 4 && (long long)n_items * ppi <= 65535 && h > 0 && w > 0,
+             "aug_remap_batch: bad shape (%d items x %d planes)", n_items, ppi);
+  B2_REQUIRE(map_stride == 0 || map_stride >= (int64_t)h * w, "aug_remap_batch: map stride %lld", (long long)map_stride);
+  WarpArgs a;
+  for (int i = 0; i < 6; ++i) a.m[i] = 0.0;
+  a.map_x = map_x; a.map_y = map_y;
+  a.h = h; a.w = w; a.interp = B2SEG_INTERP_LINEAR; a.border = B2SEG_BORDER_REFLECT; a.cval = 0;
+  return launch_warp_batch(src, dst, n_items, ppi, a, items, map_stride, stream);
 }

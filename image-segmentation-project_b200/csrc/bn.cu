@@ -648,36 +648,64 @@ __global__ void __launch_bounds__(kBnB, 1) bn_bwd_fused_kernel(const EwArgs a) {
   }
   bn_grid_barrier();
 
-  // ---- every block folds the gridDim.x rows; per-channel constants as BN_BWD_FINALIZE + bn_bwd_lin
-  double* sm_sum = reinterpret_cast<double*>(bn_sm);
-  bn_fold_rows<2>(partial, (int)gridDim.x, C, sm_sum, sm_sum + 2 * C);
+  // ---- distributed fold: block b owns channels [b*nch, (b+1)*nch); one warp per (channel, sum)
+  // pair adds that column over the gridDim.x rows (lane l takes rows l, l+32, ...; lanes combined by
+  // a fixed shuffle tree -> bit-reproducible), then the per-channel constants of BN_BWD_FINALIZE +
+  // bn_bwd_lin go to a [3][C] table behind the partial rows; a second barrier publishes the table.
   {
+    const int G = (int)gridDim.x;
+    const int nch = (C + G - 1) / G;
+    const int cbase = (int)blockIdx.x * nch;
+    double* sm_pair = reinterpret_cast<double*>(bn_sm);  // [nch][2]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int pair = warp; pair < 2 * nch; pair += kBnB / 32) {
+      const int c = cbase + (pair >> 1), k = pair & 1;
+      double acc = 0.0;
+      if (c < C) {
+        float v[5];
+#pragma unroll
+        for (int u = 0; u < 5; ++u) {
+          const int r = lane + 32 * u;
+          v[u] = r < G ? __ldcg(partial + ((size_t)r * 2 + k) * C + c) : 0.0f;
+        }
+#pragma unroll
+        for (int u = 0; u < 5; ++u) acc += (double)v[u];
+        for (int r = lane + 160; r < G; r += 32) acc += (double)__ldcg(partial + ((size_t)r * 2 + k) * C + c);
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      if (lane == 0) sm_pair[pair] = acc;
+    }
+    __syncthreads();
+    float* coef = partial + (size_t)G * 2 * C;
     const float* gamma = (const float*)a.p[8];
     float* dgamma = (float*)a.p[9];
     float* dbeta = (float*)a.p[10];
     float* dbias = (float*)a.p[11];
     const double count = (double)P;
-    for (int c = threadIdx.x; c < C; c += blockDim.x) {
-      const double sd = sm_sum[c];
+    for (int j = threadIdx.x; j < nch; j += blockDim.x) {
+      const int c = cbase + j;
+      if (c >= C) break;
+      const double sd = sm_pair[2 * j], sq = sm_pair[2 * j + 1];
       const float mean = s.bnp[2 * C + c], inv = s.bnp[3 * C + c];
-      const double q = (double)inv * (sm_sum[C + c] - (double)mean * sd);
+      const double q = (double)inv * (sq - (double)mean * sd);
       const float g = gamma ? gamma[c] : 1.0f;
       const float c1 = g * inv;
       const float c2 = training ? (float)(sd / count) : 0.0f;
       const float c3 = training ? (float)(q / count) : 0.0f;
       const float t = c3 * inv;
-      sm_k[c] = c1;
-      sm_k[C + c] = -c1 * t;
-      sm_k[2 * C + c] = c1 * (t * mean - c2);
-      if (blockIdx.x == 0) {
-        if (dgamma) dgamma[c] = accumulate ? dgamma[c] + (float)q : (float)q;
-        if (dbeta) dbeta[c] = accumulate ? dbeta[c] + (float)sd : (float)sd;
-        if (dbias) {
-          const float vb = training ? 0.0f : c1 * (float)sd;
-          dbias[c] = accumulate ? dbias[c] + vb : vb;
-        }
+      coef[c] = c1;
+      coef[C + c] = -c1 * t;
+      coef[2 * C + c] = c1 * (t * mean - c2);
+      if (dgamma) dgamma[c] = accumulate ? dgamma[c] + (float)q : (float)q;
+      if (dbeta) dbeta[c] = accumulate ? dbeta[c] + (float)sd : (float)sd;
+      if (dbias) {
+        const float vb = training ? 0.0f : c1 * (float)sd;
+        dbias[c] = accumulate ? dbias[c] + vb : vb;
       }
     }
+    bn_grid_barrier();
+    for (int e = threadIdx.x; e < 3 * C; e += blockDim.x) sm_k[e] = __ldcg(coef + e);
   }
   __syncthreads();
 

@@ -42,10 +42,14 @@ class DevicePrefetcher:
 
     def __init__(self, loader, device):
         self.loader, self.device = loader, torch.device(device)
+        if self.device.type == "cuda" and self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
 
     def _stage(self, batch, slot, side):
         if self._done[slot] is not None:
             side.wait_event(self._done[slot])  # the step that last read this slot has been enqueued
+        if all(torch.is_tensor(t) and t.device == self.device for t in batch):
+            return tuple(batch)  # already resident (dataset.DeviceBatchLoader): nothing to copy
         out = []
         with torch.cuda.stream(side):
             for j, t in enumerate(batch):

@@ -153,6 +153,55 @@ int b2seg_aug_remap_u8(const uint8_t* src, uint8_t* dst, int planes, int h, int 
                        const float* map_x, const float* map_y, int interp, int border,
                        int border_value, void* stream);
 
+/* One entry of the device table the batched warps read: the dst->src matrix of the item (already
+ * inverted, as cv2.warpAffine does; unused by remap), and per PLANE of the item (image, mask, ...)
+ * the interpolation and the constant-border value; one border rule per item. */
+typedef struct b2seg_warp_item {
+  double minv[6];
+  int32_t interp[4];
+  int32_t cval[4];
+  int32_t border;
+  int32_t pad;
+} b2seg_warp_item;
+
+/* All augmented copies of a batch in ONE launch: planes are [n_items][ppi][h][w] (ppi <= 4, e.g.
+ * image + mask), `items` a DEVICE table of n_items entries.  Arithmetic per plane is exactly that
+ * of b2seg_aug_warp_affine_u8 / b2seg_aug_remap_u8 (replaces the per-image A.Affine /
+ * A.GridDistortion calls of dataset.py:184 and forward_selection_integration.py:295).
+ * remap: item i reads map_x + i*map_stride (map_stride 0 = one shared pair of maps). */
+int b2seg_aug_warp_affine_batch_u8(const uint8_t* src, uint8_t* dst, int n_items, int ppi, int h, int w,
+                                   const b2seg_warp_item* items /*device*/, void* stream);
+int b2seg_aug_remap_batch_u8(const uint8_t* src, uint8_t* dst, int n_items, int ppi, int h, int w,
+                             const float* map_x, const float* map_y, int64_t map_stride,
+                             const b2seg_warp_item* items /*device*/, void* stream);
+
+/* Non-geometric augmentations on uint8 planes (forward_selection_integration.py:107-178).
+ * lut:        dst[i] = lut[src[i]] (InvertImg, Solarize, RandomGamma); lut = 256 device bytes.
+ * hist:       256-bin histograms of n_images images of n_per_image bytes (also CLAHE / percentiles).
+ * affine_lut: dst = uint8(clip(v*factor + mean(src)*mean_coef)) with the mean taken from `hist`
+ *             (ColorJitter brightness: mean_coef 0, hist may be NULL; contrast: mean_coef 1-factor).
+ * fill_rects: in place, rects = device int32 [n][4] = (y1, x1, y2, x2) (CoarseDropout, GridDropout).
+ * gauss_noise: dst = uint8(clip(src + mean + sigma*N(0,1))), Philox-4x32-10 keyed by `seed`.
+ * filter2d:   cv2.filter2D(src, -1, k x k float32 kernel), BORDER_REFLECT_101 (AdvancedBlur).
+ * pad:        cv2.copyMakeBorder (CropAndPad).
+ * uniform_f32 / blur1d_f32: U(-1,1) noise and one pass of scipy.ndimage.gaussian_filter
+ *             (mode='reflect'); out = gain*blur(in) (+ x if add_coord 1, + y if 2): ElasticTransform maps. */
+int b2seg_aug_lut_u8(const uint8_t* src, uint8_t* dst, int64_t n, const uint8_t* lut, void* stream);
+int b2seg_aug_hist_u8(const uint8_t* src, int64_t n_per_image, int n_images, uint32_t* hist, void* stream);
+int b2seg_aug_affine_lut_u8(const uint8_t* src, uint8_t* dst, int64_t n, const uint32_t* hist, double factor,
+                            double mean_coef, void* stream);
+int b2seg_aug_fill_rects_u8(uint8_t* plane, int h, int w, const int32_t* rects, int n_rects, int value,
+                            void* stream);
+int b2seg_aug_gauss_noise_u8(const uint8_t* src, uint8_t* dst, int64_t n, float mean, float sigma, uint64_t seed,
+                             void* stream);
+int b2seg_aug_filter2d_u8(const uint8_t* src, uint8_t* dst, int planes, int h, int w, const float* kernel,
+                          int k, void* stream);
+int b2seg_aug_pad_u8(const uint8_t* src, uint8_t* dst, int planes, int h, int w, int top, int bottom, int left,
+                     int right, int border, int border_value, void* stream);
+int b2seg_aug_uniform_f32(float* dst, int64_t n, uint64_t seed, void* stream);
+int b2seg_aug_blur1d_f32(const float* src, float* dst, int planes, int h, int w, const float* weights,
+                         int radius, int along_x, float gain, int add_coord, void* stream);
+
 /* ======================================================================== *
  *  2b. Optimizer step (replaces torch.optim.Adam.step, train.py:49; the    *
  *      optimizer the reference builds at train.py:331-335 and               *
@@ -293,6 +342,40 @@ typedef struct b2seg_wgrad_desc {
 size_t b2seg_wgrad_workspace_bytes(int a_channels, int b_channels, int ntaps, int pn, int ph,
                                    int pw);
 int b2seg_wgrad_create(const b2seg_wgrad_desc* desc /*host*/, b2seg_op** out);
+
+/* ======================================================================== *
+ *  3b. Input pipeline of CellSegmentationDataset.__getitem__ (dataset.py:30-66):   *
+ *      cv2.resize (INTER_AREA / INTER_NEAREST / INTER_LINEAR), np.percentile(2, 98) clip,       *
+ *      CLAHE(2.0, 8 x 8), min-max -- batched uint8 planes in, fp32 out, bit-exact vs cv2.       *
+ *      Coefficient tables are device arrays built by the caller once per size pair              *
+ *      (resize.cpp's own table formulas; b2seg/preproc.py, oracle/preproc_cv.py).               *
+ * ======================================================================== */
+/* nearest: xofs[dw], yofs[dh] source indices; dst u8 and/or dst_binary_f32 = (v > 0) (the mask path, dataset.py:47,58) */
+int b2seg_resize_nearest_u8(const uint8_t* src, int planes, int sh, int sw, uint8_t* dst, float* dst_binary_f32,
+                            int dh, int dw, const int32_t* xofs, const int32_t* yofs, void* stream);
+/* linear: xofs[dw] + int16 xcoef[dw][2] (x 2048), same for y (HResizeLinear / VResizeLinear fixed point) */
+int b2seg_resize_linear_u8(const uint8_t* src, int planes, int sh, int sw, uint8_t* dst, int dh, int dw,
+                           const int32_t* xofs, const int16_t* xcoef, const int32_t* yofs, const int16_t* ycoef,
+                           void* stream);
+/* area, integer ratios (ResizeAreaFast) */
+int b2seg_resize_areafast_u8(const uint8_t* src, int planes, int sh, int sw, uint8_t* dst, int dh, int dw,
+                             void* stream);
+/* area, fractional ratios (ResizeArea): CSR tables xstart[dw+1] -> (xsi, xalpha), ystart[dh+1] -> (ysi, ybeta) */
+int b2seg_resize_area_u8(const uint8_t* src, int planes, int sh, int sw, uint8_t* dst, int dh, int dw,
+                         const int32_t* xstart, const int32_t* xsi, const float* xalpha, const int32_t* ystart,
+                         const int32_t* ysi, const float* ybeta, void* stream);
+/* lut[i][v] = uint8(clip(v, *np.percentile(image_i, [q_lo, q_hi]))) from 256-bin histograms (b2seg_aug_hist_u8);
+ * `percentiles` (double [n][2]) optional */
+int b2seg_pre_percentile_lut(const uint32_t* hist, int n_images, int64_t pixels_per_image, double q_lo, double q_hi,
+                             uint8_t* lut, double* percentiles, void* stream);
+size_t b2seg_pre_clahe_workspace_bytes(int n_images, int tiles_x, int tiles_y);
+/* clipped = clip_lut[src]; eq = cv2.createCLAHE(clip_limit, (tiles_x, tiles_y)).apply(clipped);
+ * out = (eq - min) / (max - min + 1e-8) as fp32 (four launches) */
+int b2seg_pre_clahe_normalize(const uint8_t* src, int n_images, int h, int w, const uint8_t* clip_lut,
+                              double clip_limit, int tiles_x, int tiles_y, uint8_t* clipped, uint8_t* eq,
+                              float* out, void* workspace, size_t workspace_bytes, void* stream);
+/* normalize=False path (dataset.py:55): out = v / 255 */
+int b2seg_pre_scale255_f32(const uint8_t* src, int n_images, int64_t pixels_per_image, float* out, void* stream);
 
 /* ======================================================================== *
  *  4. HBM-bound layer kernels (BatchNorm, ReLU, pooling, stem, 1-channel    *

@@ -208,15 +208,17 @@ def test_module_contract(cuda):
 def test_fused_batchnorm_matches_three_kernel_sequence(cuda, monkeypatch):
     """The single-launch BatchNorm kernels (EW_BN_APPLY_FUSED folds the statistics in the consumer,
     EW_BN_BWD_FUSED = reduce + device-wide barrier + apply) against the finalize / reduce / apply
-    sequence they replace (B2SEG_BN_FUSED=0): the forward arithmetic is the same, so logits and
+    sequence they replace: the forward arithmetic is the same, so logits and
     running statistics must be BIT-identical; the backward sums are folded over a different block
-    decomposition, so gradients agree to fp32 summation noise (1e-3 of the largest gradient)."""
+    decomposition, so gradients agree up to
+    fp32 summation noise re-rounded through ~60 bf16 gradient buffers (2e-2 relative per tensor)."""
     import losses
     from b2seg import synth
     x, t = synth.cell_tiles(4, 96, seed=13)
     results = {}
     for mode in ("1", "0"):
-        monkeypatch.setenv("B2SEG_BN_FUSED", mode)
+        monkeypatch.setenv("B2SEG_BN_FUSED_FWD", mode)
+        monkeypatch.setenv("B2SEG_BN_FUSED_BWD_MB", "100000" if mode == "1" else "0")
         model, _ = _build("resnet34", True, seed=21)
         model = model.to(cuda).train()
         crit = losses.get_loss_function({"loss_fn": "combo"})
@@ -234,6 +236,6 @@ def test_fused_batchnorm_matches_three_kernel_sequence(cuda, monkeypatch):
         assert torch.equal(sf[k], su[k]), k
     gmax = max(float(v.norm()) for v in gu.values())
     for n in gu:
-        assert float((gf[n].double() - gu[n].double()).norm()) <= 1e-3 * max(float(gu[n].norm()), 1e-3 * gmax), n
+        assert float((gf[n].double() - gu[n].double()).norm()) <= 2e-2 * max(float(gu[n].norm()), 1e-2 * gmax), n
     print(f"\n[fused BN] launches per step {nf} (three-kernel sequence: {nu})")
     assert nf < nu - 100
