@@ -9,6 +9,8 @@ from __future__ import annotations
 import ctypes as C
 import math
 
+import numpy as np
+
 import torch
 
 from . import _lib as L

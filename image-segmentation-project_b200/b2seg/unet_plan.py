@@ -72,7 +72,7 @@ def _fused_bn_bwd_max_bytes():
     bytes (B2SEG_BN_FUSED_BWD_MB, default below; 0 = never): small layers are launch-latency bound
     and their operands stay L2-resident between the two phases."""
     import os
-    return float(os.environ.get("B2SEG_BN_FUSED_BWD_MB", "24")) * 2 ** 20
+    return float(os.environ.get("B2SEG_BN_FUSED_BWD_MB", "12")) * 2 ** 20
 
 
 class UNetPlan:

@@ -111,3 +111,62 @@ def test_augment_oracle_matches_cv2():
             for bt, cb in borders.items():
                 ref = cv2.remap(img, mx, my, cf, borderMode=cb, borderValue=0)
                 assert np.array_equal(A.remap_u8(img, mx, my, it, bt, 0), ref)
+
+
+def _smooth_u8(rng, h, w):
+    cv2 = pytest.importorskip("cv2")
+    a = cv2.GaussianBlur(rng.integers(0, 256, (h, w), dtype=np.uint8), (0, 0), 3)
+    return cv2.normalize(a, None, 0, 255, cv2.NORM_MINMAX).astype(np.uint8)
+
+
+@pytest.mark.parametrize("h,w,dh,dw", [(96, 96, 64, 64), (512, 512, 256, 256), (520, 696, 256, 256), (300, 300, 128, 128),
+                                       (100, 130, 256, 256), (97, 131, 64, 64), (64, 64, 96, 96), (64, 64, 64, 64)])
+def test_preproc_oracle_resize_matches_cv2(h, w, dh, dw):
+    """oracle/preproc_cv.py against cv2.resize itself (dataset.py:52-53): AREA (all three of OpenCV's
+    code paths: integer-factor, fractional, enlarging) and NEAREST bit-exact; LINEAR bit-exact when
+    shrinking, within 1 LSB on < 1 % of the pixels when enlarging (cv2's own SIMD path)."""
+    cv2 = pytest.importorskip("cv2")
+    from oracle import preproc_cv as P
+    rng = np.random.default_rng(h * 7 + dw)
+    for img in (_smooth_u8(rng, h, w), rng.integers(0, 256, (h, w), dtype=np.uint8)):
+        assert np.array_equal(P.resize_area_u8(img, dh, dw), cv2.resize(img, (dw, dh), interpolation=cv2.INTER_AREA))
+        assert np.array_equal(P.resize_nearest_u8(img, dh, dw), cv2.resize(img, (dw, dh), interpolation=cv2.INTER_NEAREST))
+        d = np.abs(P.resize_linear_u8(img, dh, dw).astype(int) - cv2.resize(img, (dw, dh), interpolation=cv2.INTER_LINEAR).astype(int))
+        assert d.max() <= (1 if (dh > h or dw > w) else 0) and (d > 0).mean() < 0.01
+
+
+@pytest.mark.parametrize("h,w", [(256, 256), (128, 128), (64, 64), (250, 250), (100, 130)])
+def test_preproc_oracle_normalize_matches_reference_arithmetic(h, w):
+    """normalize_microscopy_image (dataset.py:30-43) on the host with np.percentile and cv2's CLAHE
+    vs the restatement: clip, CLAHE and the final float image all bit-exact (incl. sizes the 8x8
+    tile grid does not divide, where OpenCV pads by reflection, and a constant image)."""
+    cv2 = pytest.importorskip("cv2")
+    from oracle import preproc_cv as P
+    rng = np.random.default_rng(h + 3 * w)
+    for img in (_smooth_u8(rng, h, w), rng.integers(0, 256, (h, w), dtype=np.uint8),
+                (rng.integers(0, 40, (h, w)) + 100).astype(np.uint8), np.full((h, w), 77, np.uint8)):
+        lo, hi = np.percentile(img, [2, 98])
+        clipped = np.clip(img, lo, hi).astype(np.uint8)
+        eq = cv2.createCLAHE(clipLimit=2.0, tileGridSize=(8, 8)).apply(clipped)
+        ref = (eq - eq.min()) / (eq.max() - eq.min() + 1e-8)
+        assert np.array_equal(P.percentile_clip_u8(img), clipped)
+        assert np.array_equal(P.clahe_u8(clipped), eq)
+        assert np.array_equal(P.normalize_microscopy_image(img), ref.astype(np.float32))
+
+
+def test_augmentation_map_oracles_match_their_formulas():
+    """oracle/augment_cv.py's grid / optical map builders: identity when undistorted, monotone,
+    and the maps drive cv2.remap to the same picture as the oracle's own remap."""
+    cv2 = pytest.importorskip("cv2")
+    h, w = 90, 120
+    mx, my = A.grid_distortion_maps(h, w, [1.0] * 6, [1.0] * 6)
+    xs, ys = np.meshgrid(np.arange(w, dtype=np.float32), np.arange(h, dtype=np.float32))
+    assert np.allclose(mx, xs, atol=1e-4) and np.allclose(my, ys, atol=1e-4)
+    mx, my = A.grid_distortion_maps(h, w, [1.2, 0.8, 1.1, 0.9, 1.0, 1.3], [0.7, 1.3, 1.0, 1.1, 0.9, 1.0])
+    assert (np.diff(mx, axis=1) >= 0).all() and (np.diff(my, axis=0) >= 0).all()
+    ox, oy = A.optical_distortion_maps(h, w, 0.0, 0, 0)
+    assert np.allclose(ox, xs, atol=1e-3) and np.allclose(oy, ys, atol=1e-3)
+    ox, oy = A.optical_distortion_maps(h, w, 0.4, 3, -2)
+    img = _smooth_u8(np.random.default_rng(0), h, w)
+    assert np.array_equal(A.remap_u8(img, ox, oy, A.LINEAR, A.REFLECT, 0),
+                          cv2.remap(img, ox, oy, cv2.INTER_LINEAR, borderMode=cv2.BORDER_REFLECT))
