@@ -105,7 +105,7 @@ class Compose:
         """[planes,H,W] uint8 CUDA tensor -> same (possibly different H,W), all on the device."""
         if self.transforms and (force_apply or random.random() < self.p):
             for t in self.transforms:
-                if t._fire():
+                if t._fire(force_apply):
                     planes = t.apply_planes(planes, **t.get_params(planes.shape[-2], planes.shape[-1]))
         return planes
 

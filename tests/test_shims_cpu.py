@@ -27,8 +27,8 @@ def test_albumentations_surface():
     assert a == b and len(a["matrix"]) == 2 and len(a["matrix"][0]) == 3
     pipe = A.Compose([A.HorizontalFlip(p=0.5), t2])
     assert len(pipe.transforms) == 2 and pipe.transforms[1] is t2
-    with pytest.raises(TypeError):
-        A.HorizontalFlip(p=1.0)(None)  # albumentations: keyword arguments only
+    with pytest.raises(KeyError):
+        A.HorizontalFlip(p=1.0)(None)  # albumentations: data goes in as named arguments
 
 
 def test_cell_segmentation_aliases():
