@@ -26,6 +26,8 @@ class LossSpec(C.Structure):
         ("w_sens_spec", C.c_float), ("ss_w", C.c_float), ("ss_eps", C.c_float),
         ("w_bce", C.c_float), ("bce_mode", C.c_int32), ("bce_beta", C.c_float),
         ("w_focal", C.c_float), ("focal_alpha", C.c_float), ("focal_gamma", C.c_float),
+        ("w_explog_dice", C.c_float), ("w_explog_cross", C.c_float),
+        ("el_gamma_dice", C.c_float), ("el_gamma_cross", C.c_float),
     ]
 
 
@@ -114,6 +116,9 @@ _SIGS = {
     "b2seg_seg_loss_finish": (C.c_int, [C.POINTER(LossSpec), _i64, _vp, _vp, _vp, _vp]),
     "b2seg_seg_loss_bwd": (C.c_int, [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp]),
     "b2seg_seg_metrics_from_probs": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _vp]),
+    "b2seg_loss_boundary_weight_map": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _i, C.POINTER(C.c_float), C.c_float, _vp]),
+    "b2seg_loss_edt_workspace_bytes": (C.c_size_t, [_i, _i, _i]),
+    "b2seg_loss_edt_f32": (C.c_int, [_vp, _vp, _i, _i, _i, _i, C.c_float, _vp, _vp]),
     "b2seg_aug_permute_u8": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "b2seg_aug_warp_affine_u8": (C.c_int, [_vp, _vp, _i, _i, _i, C.POINTER(C.c_double), _i, _i, _i, _vp]),
     "b2seg_aug_remap_u8": (C.c_int, [_vp, _vp, _i, _i, _i, _vp, _vp, _i, _i, _i, _vp]),

@@ -123,6 +123,41 @@ def metrics_from_probs(probs, target) -> torch.Tensor:
     return out
 
 
+def _planes_f32(t: torch.Tensor):
+    if t.dim() < 2:
+        raise ValueError(f"expected [..., H, W] planes, got {tuple(t.shape)}")
+    t = _flat_f32(t)
+    h, w = t.shape[-2], t.shape[-1]
+    return t, t.numel() // (h * w), h, w
+
+
+def boundary_weight_map(target, theta0: int = 3, theta: int = 5, gauss=None, gain: float = 10.0) -> torch.Tensor:
+    """1 + gain * gauss(dilate(t) - erode(t)) of BoundaryLoss (losses.py:283-301), one launch.
+    `gauss`: the theta x theta kernel as a CPU float32 tensor (BoundaryLoss._gaussian_kernel)."""
+    L.require_cuda(target)
+    t, planes, h, w = _planes_f32(target)
+    k = gauss.detach().to("cpu", torch.float32).contiguous()
+    if tuple(k.shape) != (theta, theta):
+        raise ValueError(f"gaussian kernel must be {theta} x {theta}, got {tuple(k.shape)}")
+    out = torch.empty_like(t)
+    L.check(L.lib().b2seg_loss_boundary_weight_map(
+        t.data_ptr(), out.data_ptr(), planes, h, w, int(theta0), int(theta),
+        C.cast(k.data_ptr(), C.POINTER(C.c_float)), float(gain), L.stream_ptr()))
+    return out
+
+
+def distance_transform(src, mode: int = 0, alpha: float = 1.0) -> torch.Tensor:
+    """scipy.ndimage.distance_transform_edt per [H, W] plane of `src`, on the device.
+    mode 0: the distances; mode 1: 1 + alpha * d / (max_plane(d) + 1e-7) (losses.py:203-232)."""
+    L.require_cuda(src)
+    t, planes, h, w = _planes_f32(src)
+    ws = torch.empty(L.lib().b2seg_loss_edt_workspace_bytes(planes, h, w), dtype=torch.uint8, device=t.device)
+    out = torch.empty_like(t)
+    L.check(L.lib().b2seg_loss_edt_f32(t.data_ptr(), out.data_ptr(), planes, h, w, int(mode), float(alpha),
+                                       ws.data_ptr(), L.stream_ptr()))
+    return out
+
+
 def metrics_dict(stats_host, eps: float = 1e-7) -> dict:
     """utils.py:136-151 from a host copy of the stats block."""
     tp, fp, fn, tn = (float(stats_host[i]) for i in (L.S_TP, L.S_FP, L.S_FN, L.S_TN))

@@ -64,9 +64,34 @@ __device__ __forceinline__ float pow_pos(float base, float g) {
   return exp2f(g * __log2f(base));
 }
 
-template <bool NEED_FOCAL, bool HAS_WMAP, bool SOFT = true>
+// Per-pixel term of ExponentialLogarithmicLoss (losses.py:190-192), in the reference's own float32
+// formulation -- through probabilities, F.binary_cross_entropy's logs clamped at -100, then
+//   f = (-log(clamp(1 - ce, 1e-7)))^g,   df/dx = g u^(g-1) / (1 - ce) * (p - t),  u = -log(1 - ce).
+// For confident pixels `1 - ce` sits a few float32 steps below 1 and f is steep there, so that
+// rounding is part of the reference's answer and is kept (accurate logf / log1pf, rn subtract).
+// 1 - ce < 1e-7 (a badly wrong pixel) is the clamped constant with zero slope, as autograd sees
+// it; u == 0 (p rounds to the target) has an infinite slope that the reference turns into NaN
+// through inf * 0 -- it contributes 0 here.
+__device__ __forceinline__ float explog_om(float p, float t) {
+  const float l1 = fmaxf(logf(p), -100.0f), l0 = fmaxf(log1pf(-p), -100.0f);
+  const float ce = __fsub_rn(__fmul_rn(t - 1.0f, l0), __fmul_rn(t, l1));
+  return __fsub_rn(1.0f, ce);
+}
+__device__ __forceinline__ float explog_f(float om, float g) {
+  const float u = -logf(fmaxf(om, 1e-7f));
+  return u > 0.0f ? powf(u, g) : 0.0f;
+}
+__device__ __forceinline__ float explog_df(float om, float g) {
+  if (!(om >= 1e-7f)) return 0.0f;
+  const float u = -logf(om);
+  return u > 0.0f ? g * powf(u, g - 1.0f) / om : 0.0f;
+}
+
+// MODE selects what accumulator 5 carries: 0 nothing, 1 the focal term, 2 the exp-log term.
+template <int MODE, bool HAS_WMAP, bool SOFT = true>
 __device__ __forceinline__ void accumulate(float (&acc)[kAcc], float x, float t, float w,
                                            float gamma, bool gamma_is_two) {
+  constexpr bool NEED_FOCAL = MODE == 1;
   const PixelTerms q = pixel_terms<NEED_FOCAL, SOFT>(x, t);
   const float bce_w = HAS_WMAP ? q.bce * w : q.bce;
   acc[0] += q.p;
@@ -78,6 +103,7 @@ __device__ __forceinline__ void accumulate(float (&acc)[kAcc], float x, float t,
     const float m = gamma_is_two ? q.one_m_pt * q.one_m_pt : pow_pos(q.one_m_pt, gamma);
     acc[5] = fmaf(m, q.bce, acc[5]);
   }
+  if (MODE == 2) acc[5] += explog_f(explog_om(q.p, t), gamma);
   const float pb = q.p > 0.5f ? 1.0f : 0.0f;
   acc[6] += pb;
   acc[7] = fmaf(pb, t, acc[7]);
@@ -212,6 +238,22 @@ __device__ void finish_loss(const b2seg_loss_spec& s, const double* tot, double 
     loss += s.w_focal * s.focal_alpha * Sfoc / n;
     F += s.w_focal * s.focal_alpha / n;
   }
+  if (s.w_explog_dice != 0.0f) {  // w (-log(clamp(1 - dice_loss, 1e-7)))^g, losses.py:186-187
+    const double sm = s.dice_smooth, U = Sp + St, g = s.el_gamma_dice;
+    const double dice = (2.0 * Spt + sm) / (U + sm);
+    const double a = -2.0 / (U + sm), b = (2.0 * Spt + sm) / ((U + sm) * (U + sm));
+    const bool clamped = !(dice > 1e-7);
+    const double u = -log(clamped ? 1e-7 : dice);
+    loss += s.w_explog_dice * (u > 0.0 ? pow(u, g) : 0.0);
+    const double fac = (clamped || !(u > 0.0)) ? 0.0 : g * pow(u, g - 1.0) / dice;  // d/d(dice_loss)
+    A += s.w_explog_dice * fac * a;
+    B += s.w_explog_dice * fac * b;
+  }
+  const bool explog = s.w_explog_cross != 0.0f;
+  if (explog) {  // Sfoc carries sum f(bce_i)
+    loss += s.w_explog_cross * Sfoc / n;
+    F = s.w_explog_cross / n;
+  }
   for (int i = 0; i < kAcc; ++i) stats[i] = tot[i];
   write_confusion(stats, n);
   stats[B2SEG_S_LOSS] = loss;
@@ -221,13 +263,13 @@ __device__ void finish_loss(const b2seg_loss_spec& s, const double* tot, double 
   coef[2] = (float)W0;
   coef[3] = (float)W1;
   coef[4] = (float)F;
-  coef[5] = s.focal_gamma;
+  coef[5] = explog ? s.el_gamma_cross : s.focal_gamma;
   coef[6] = (float)Wm;
-  coef[7] = 0.0f;
+  coef[7] = explog ? 2.0f : 0.0f;  // what coef[4] multiplies: the focal or the exp-log pixel term
 }
 
 // ---- forward kernel -----------------------------------------------------------
-template <bool NEED_FOCAL, bool HAS_WMAP, bool SOFT>
+template <int NEED_FOCAL, bool HAS_WMAP, bool SOFT>
 __device__ __forceinline__ void accumulate4(float (&acc)[kAcc], const float4& x, const float4& t,
                                             const float4& w, float gamma, bool g2) {
   accumulate<NEED_FOCAL, HAS_WMAP, SOFT>(acc, x.x, t.x, w.x, gamma, g2);
@@ -236,7 +278,7 @@ __device__ __forceinline__ void accumulate4(float (&acc)[kAcc], const float4& x,
   accumulate<NEED_FOCAL, HAS_WMAP, SOFT>(acc, x.w, t.w, w.w, gamma, g2);
 }
 
-template <bool NEED_FOCAL, bool HAS_WMAP, bool VEC4>
+template <int NEED_FOCAL, bool HAS_WMAP, bool VEC4>
 __global__ void __launch_bounds__(kThreads)
     seg_loss_fwd_kernel(const float* __restrict__ x, const float* __restrict__ t,
                         const float* __restrict__ wm, long long n, LossSpecDev spec, ReduceWs* ws,
@@ -244,7 +286,7 @@ __global__ void __launch_bounds__(kThreads)
   float acc[kAcc];
 #pragma unroll
   for (int i = 0; i < kAcc; ++i) acc[i] = 0.0f;
-  const float gamma = spec.s.focal_gamma;
+  const float gamma = NEED_FOCAL == 2 ? spec.s.el_gamma_cross : spec.s.focal_gamma;
   const bool g2 = gamma == 2.0f;
   const long long tid = (long long)blockIdx.x * kThreads + threadIdx.x;
   const long long nthreads = (long long)gridDim.x * kThreads;
@@ -264,7 +306,7 @@ __global__ void __launch_bounds__(kThreads)
         wa = ldg_stream_f4(w4 + i);
         wb = ldg_stream_f4(w4 + i + nthreads);
       }
-      if (NEED_FOCAL && is_hard4(ta) && is_hard4(tb)) {
+      if (NEED_FOCAL == 1 && is_hard4(ta) && is_hard4(tb)) {
         accumulate4<NEED_FOCAL, HAS_WMAP, false>(acc, xa, ta, wa, gamma, g2);
         accumulate4<NEED_FOCAL, HAS_WMAP, false>(acc, xb, tb, wb, gamma, g2);
       } else {
@@ -296,10 +338,11 @@ __global__ void __launch_bounds__(kThreads)
 }
 
 // ---- backward kernel ----------------------------------------------------------
-template <bool NEED_FOCAL, bool HAS_WMAP, bool SOFT = true>
+template <int MODE, bool HAS_WMAP, bool SOFT = true>
 __device__ __forceinline__ float pixel_grad(float x, float t, float w, float A, float B, float W0,
                                             float W1, float F, float Wm, float gamma,
                                             bool gamma_is_two, float go) {
+  constexpr bool NEED_FOCAL = MODE == 1;
   const PixelTerms q = pixel_terms<NEED_FOCAL, SOFT>(x, t);
   const float d = q.p - t;
   float g = (fmaf(A, t, B)) * q.p * (1.0f - q.p);
@@ -318,6 +361,7 @@ __device__ __forceinline__ float pixel_grad(float x, float t, float w, float A, 
     }
     wl = fmaf(F, fmaf(mg1 * pt, q.bce, mg), wl);
   }
+  if (MODE == 2) wl = fmaf(F, explog_df(explog_om(q.p, t), gamma), wl);
   g = fmaf(wl, d, g);
   return g * go;
 }
@@ -326,7 +370,7 @@ struct BwdCoef {
   float A, B, W0, W1, F, gamma, Wm, go;
   bool g2;
 };
-template <bool NEED_FOCAL, bool HAS_WMAP, bool SOFT>
+template <int NEED_FOCAL, bool HAS_WMAP, bool SOFT>
 __device__ __forceinline__ float4 pixel_grad4(const float4& x, const float4& t, const float4& w,
                                               const BwdCoef& c) {
   float4 g;
@@ -337,7 +381,7 @@ __device__ __forceinline__ float4 pixel_grad4(const float4& x, const float4& t, 
   return g;
 }
 
-template <bool NEED_FOCAL, bool HAS_WMAP, bool VEC4>
+template <int NEED_FOCAL, bool HAS_WMAP, bool VEC4>
 __device__ __forceinline__ void seg_loss_bwd_body(const float* __restrict__ x, const float* __restrict__ t,
                                                   const float* __restrict__ wm, long long n,
                                                   const BwdCoef& c, float* __restrict__ gx) {
@@ -361,7 +405,7 @@ __device__ __forceinline__ void seg_loss_bwd_body(const float* __restrict__ x, c
         wb = ldg_stream_f4(w4 + i + nthreads);
       }
       float4 ga, gb;
-      if (NEED_FOCAL && is_hard4(ta) && is_hard4(tb)) {
+      if (NEED_FOCAL == 1 && is_hard4(ta) && is_hard4(tb)) {
         ga = pixel_grad4<NEED_FOCAL, HAS_WMAP, false>(xa, ta, wa, c);
         gb = pixel_grad4<NEED_FOCAL, HAS_WMAP, false>(xb, tb, wb, c);
       } else {
@@ -389,7 +433,7 @@ __device__ __forceinline__ void seg_loss_bwd_body(const float* __restrict__ x, c
 
 // The focal coefficient is only known on the device (the forward kernel wrote it), so the
 // kernel branches once, uniformly, between the focal and the focal-free instantiation.
-template <bool NEED_FOCAL_UNUSED, bool HAS_WMAP, bool VEC4>
+template <int NEED_FOCAL_UNUSED, bool HAS_WMAP, bool VEC4>
 __global__ void __launch_bounds__(kThreads)
     seg_loss_bwd_kernel(const float* __restrict__ x, const float* __restrict__ t,
                         const float* __restrict__ wm, long long n,
@@ -401,9 +445,11 @@ __global__ void __launch_bounds__(kThreads)
   c.go = grad_out ? *grad_out : 1.0f;
   c.g2 = c.gamma == 2.0f;
   if (c.F == 0.0f)
-    seg_loss_bwd_body<false, HAS_WMAP, VEC4>(x, t, wm, n, c, gx);
+    seg_loss_bwd_body<0, HAS_WMAP, VEC4>(x, t, wm, n, c, gx);
+  else if (coef[7] == 2.0f)
+    seg_loss_bwd_body<2, HAS_WMAP, VEC4>(x, t, wm, n, c, gx);
   else
-    seg_loss_bwd_body<true, HAS_WMAP, VEC4>(x, t, wm, n, c, gx);
+    seg_loss_bwd_body<1, HAS_WMAP, VEC4>(x, t, wm, n, c, gx);
 }
 
 // ---- metrics from probabilities (utils.py:120-151) --------------------------------
@@ -484,6 +530,11 @@ extern "C" int b2seg_seg_loss_fwd(const float* logits, const float* target,
   B2_REQUIRE(spec->w_focal == 0.0f || spec->focal_gamma > 0.0f,
              "seg_loss_fwd: focal_gamma must be > 0");
   const bool focal = spec->w_focal != 0.0f;
+  const bool explog = spec->w_explog_cross != 0.0f;
+  B2_REQUIRE(!(focal && explog), "seg_loss_fwd: the focal and the exp-log pixel terms are exclusive");
+  B2_REQUIRE((!explog || spec->el_gamma_cross > 0.0f) &&
+                 (spec->w_explog_dice == 0.0f || spec->el_gamma_dice > 0.0f),
+             "seg_loss_fwd: exp-log exponents must be > 0");
   const bool vec = aligned16(logits) && aligned16(target) && (!wmap || aligned16(weight_map));
   LossSpecDev sd;
   sd.s = *spec;
@@ -494,11 +545,14 @@ extern "C" int b2seg_seg_loss_fwd(const float* logits, const float* target,
   seg_loss_fwd_kernel<F, W, V><<<blocks, kThreads, 0, st>>>(logits, target, weight_map, n, sd, \
                                                             ws, stats, loss_out, coef)
   if (focal) {
-    if (wmap) { if (vec) LAUNCH(true, true, true); else LAUNCH(true, true, false); }
-    else      { if (vec) LAUNCH(true, false, true); else LAUNCH(true, false, false); }
+    if (wmap) { if (vec) LAUNCH(1, true, true); else LAUNCH(1, true, false); }
+    else      { if (vec) LAUNCH(1, false, true); else LAUNCH(1, false, false); }
+  } else if (explog) {
+    if (wmap) { if (vec) LAUNCH(2, true, true); else LAUNCH(2, true, false); }
+    else      { if (vec) LAUNCH(2, false, true); else LAUNCH(2, false, false); }
   } else {
-    if (wmap) { if (vec) LAUNCH(false, true, true); else LAUNCH(false, true, false); }
-    else      { if (vec) LAUNCH(false, false, true); else LAUNCH(false, false, false); }
+    if (wmap) { if (vec) LAUNCH(0, true, true); else LAUNCH(0, true, false); }
+    else      { if (vec) LAUNCH(0, false, true); else LAUNCH(0, false, false); }
   }
 #undef LAUNCH
   B2_CHECK_CUDA(cudaGetLastError());
@@ -518,7 +572,7 @@ extern "C" int b2seg_seg_loss_bwd(const float* logits, const float* target,
   // The focal coefficient lives on the device: the kernel branches once, uniformly, between its
   // focal and focal-free bodies (the first template argument is unused).
 #define LAUNCH(W, V)                                                                        \
-  seg_loss_bwd_kernel<true, W, V><<<blocks, kThreads, 0, st>>>(logits, target, weight_map, n, \
+  seg_loss_bwd_kernel<1, W, V><<<blocks, kThreads, 0, st>>>(logits, target, weight_map, n, \
                                                                coef, grad_out, grad_logits)
   if (wmap) { if (vec) LAUNCH(true, true); else LAUNCH(true, false); }
   else      { if (vec) LAUNCH(false, true); else LAUNCH(false, false); }

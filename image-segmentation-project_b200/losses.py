@@ -168,87 +168,72 @@ class _MapWeightedBCE(_FusedLoss):
 
 
 class DistanceMapPenalizedCrossEntropy(_MapWeightedBCE):
+    """mean((1 + alpha * edt(t) / max(edt(t))) * bce)  (losses.py:197-232).  The exact Euclidean
+    distance transform runs on the device (csrc/map_loss.cu), bit-identical to the scipy path."""
+
     def __init__(self, alpha=1.0):
         super().__init__()
         self.alpha = alpha
 
     def _compute_distance_map(self, target):
-        # exact Euclidean distance transform per sample/channel, normalised to [0, 1]
-        from scipy.ndimage import distance_transform_edt
-        host = target.detach().cpu().numpy()
-        out = np.empty(host.shape, dtype=np.float32)
-        for b in range(host.shape[0]):
-            for c in range(host.shape[1]):
-                d = distance_transform_edt(host[b, c])
-                out[b, c] = d / (d.max() + 1e-7)
-        return torch.from_numpy(out).to(target.device)
+        return (lossfn.distance_transform(target, mode=1, alpha=1.0) - 1.0).view(target.shape)
 
     def _weight_map(self, pred, target):
-        return 1 + self.alpha * self._compute_distance_map(target)
+        return lossfn.distance_transform(target, mode=1, alpha=self.alpha).view(target.shape)
 
 
 class BoundaryLoss(_MapWeightedBCE):
+    """mean((1 + 10 * gauss(dilate(t) - erode(t))) * bce)  (losses.py:276-318); the weight map is one
+    fused kernel (csrc/map_loss.cu)."""
+
     def __init__(self, theta0=3, theta=5):
         super().__init__()
         self.theta0, self.theta = theta0, theta
 
     def _gaussian_kernel(self, size, sigma):
-        ax = torch.arange(size, dtype=torch.float32) - (size - 1) / 2.0
-        g = torch.exp(-(ax[:, None] ** 2 + ax[None, :] ** 2) / (2 * sigma ** 2))
-        return g / g.sum()
+        ax = torch.arange(size).float()
+        ax -= (size - 1) / 2.0
+        g = ax ** 2
+        g = (-(g.unsqueeze(0) + g.unsqueeze(1)) / (2 * sigma ** 2)).exp()
+        g /= g.sum()
+        return g
 
-    @torch.no_grad()
     def _weight_map(self, pred, target):
-        pad0 = self.theta0 // 2
-        grown = F.max_pool2d(target, self.theta0, 1, pad0)
-        shrunk = -F.max_pool2d(-target, self.theta0, 1, pad0)
-        ch = target.size(1)
-        k = self._gaussian_kernel(self.theta, self.theta / 3.0).to(target.device)
-        k = k.expand(ch, 1, self.theta, self.theta).contiguous()
-        edge = F.conv2d(grown - shrunk, k, padding=self.theta // 2, groups=ch)
-        return 1 + 10 * edge
+        k = self._gaussian_kernel(self.theta, self.theta / 3.0)
+        return lossfn.boundary_weight_map(target, self.theta0, self.theta, k, 10.0).view(target.shape)
 
 
-class ExponentialLogarithmicLoss(nn.Module):
-    """w_dice * (-log(1 - dice_loss))^g_d + w_cross * mean((-log(clamp(1 - bce_i)))^g_c).
-    The Dice part comes from the fused kernel; the per-pixel power term is a composite."""
+class ExponentialLogarithmicLoss(_FusedLoss):
+    """w_dice * (-log(1 - dice_loss))^g_d + w_cross * mean((-log(clamp(1 - bce_i, 1e-7)))^g_c)
+    (losses.py:174-194): both parts, and the gradient, in the fused kernel."""
 
     def __init__(self, w_dice=0.5, w_cross=0.5, gamma_dice=0.3, gamma_cross=0.3):
         super().__init__()
         self.w_dice, self.w_cross = w_dice, w_cross
         self.gamma_dice, self.gamma_cross = gamma_dice, gamma_cross
-        self.dice_loss = DiceLoss()
-        self.last_stats = None
-        self.last_logits_ref = None
 
-    def forward(self, pred, target):
-        dice = self.dice_loss(pred, target)
-        self.last_stats, self.last_logits_ref = self.dice_loss.last_stats, pred
-        e_dice = torch.pow(-torch.log(torch.clamp(1 - dice, min=1e-7)), self.gamma_dice)
-        ce = F.binary_cross_entropy(torch.sigmoid(pred), target, reduction='none')
-        e_cross = torch.pow(-torch.log(torch.clamp(1 - ce, min=1e-7)), self.gamma_cross).mean()
-        return self.w_dice * e_dice + self.w_cross * e_cross
+    def _spec(self):
+        return lossfn.make_spec(w_explog_dice=self.w_dice, w_explog_cross=self.w_cross,
+                                el_gamma_dice=self.gamma_dice, el_gamma_cross=self.gamma_cross, dice_smooth=1.0)
 
 
 class HausdorffDistanceLoss(nn.Module):
-    """(sigmoid(x) - t)^2 * (dtm(pred)^a + dtm(target)^a).  The reference version cannot be
-    differentiated (it calls .numpy() on a tensor that requires grad, losses.py:268); here the
-    distance maps are treated as constants, which is what the formula intends."""
+    """(sigmoid(x) - t)^2 * (dtm(pred)^a + dtm(target)^a)  (losses.py:235-273).  The reference version
+    cannot be differentiated (it calls .numpy() on a tensor that requires grad, losses.py:268); here
+    the distance maps are constants, which is what the formula intends.  The distance transforms run
+    on the device, including scipy's answer for the zero-free sigmoid planes."""
 
     def __init__(self, alpha=2.0, reduction='mean'):
         super().__init__()
         self.alpha, self.reduction = alpha, reduction
+        self.last_stats = None
+        self.last_logits_ref = None
 
     @torch.no_grad()
     def _compute_dtm(self, img):
-        from scipy.ndimage import distance_transform_edt
-        host = img.detach().cpu().numpy()
-        out = np.zeros(host.shape, dtype=np.float32)
-        for b in range(host.shape[0]):
-            for c in range(host.shape[1]):
-                if host[b, c].max() > 0:
-                    out[b, c] = distance_transform_edt(host[b, c])
-        field = torch.from_numpy(out).to(img.device)
+        field = lossfn.distance_transform(img, mode=0).view(img.shape)
+        keep = (img.flatten(2).amax(dim=2) > 0).to(field.dtype)[:, :, None, None]  # losses.py:269
+        field = field * keep
         return field / (field.max() + 1e-7)
 
     def forward(self, pred, target):

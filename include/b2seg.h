@@ -68,6 +68,10 @@ typedef struct b2seg_loss_spec {
   float bce_beta;
   float w_focal;         /* losses.py:76-86 (reduction='mean') */
   float focal_alpha, focal_gamma;
+  /* ExponentialLogarithmicLoss, losses.py:174-194: w_explog_dice (-log(1 - dice_loss))^el_gamma_dice
+   * + w_explog_cross mean((-log(clamp(1 - bce_i, 1e-7)))^el_gamma_cross).  The per-pixel term shares
+   * the focal accumulator: w_focal and w_explog_cross are exclusive. */
+  float w_explog_dice, w_explog_cross, el_gamma_dice, el_gamma_cross;
 } b2seg_loss_spec;
 
 /* Layout of the device-side result block written by the forward kernels
@@ -78,7 +82,7 @@ enum {
   B2SEG_S_PT = 2,      /* sum sigmoid(x)*t                        */
   B2SEG_S_BCE = 3,     /* sum bce_i (times weight map in mode 3)  */
   B2SEG_S_BCE_T = 4,   /* sum bce_i*t                             */
-  B2SEG_S_FOCAL = 5,   /* sum (1-pt)^gamma * bce_i                */
+  B2SEG_S_FOCAL = 5,   /* sum (1-pt)^gamma * bce_i, or sum of the exp-log pixel term */
   B2SEG_S_PB = 6,      /* sum [sigmoid(x) > 0.5]                  */
   B2SEG_S_PB_T = 7,    /* sum [sigmoid(x) > 0.5]*t                */
   B2SEG_S_N = 8,       /* n                                       */
@@ -119,6 +123,26 @@ int b2seg_seg_loss_finish(const b2seg_loss_spec* spec, int64_t n_total, double* 
  * probabilities; fills stats[S_PB, S_PB_T, S_T, S_N, S_TP..S_TN]. */
 int b2seg_seg_metrics_from_probs(const float* probs, const float* target, int64_t n,
                                  void* workspace, double* stats, void* stream);
+
+/* Weight maps of the boundary-style losses: they depend on the target only, are built on the
+ * device and go into b2seg_seg_loss_fwd/_bwd as `weight_map` (bce_mode 3).
+ *
+ * BoundaryLoss (losses.py:283-301): weight = 1 + gain * conv2d(dilate(t) - erode(t), gauss) with
+ * max_pool2d(theta0, stride 1, pad theta0/2) as dilation / erosion (window clipped at the image
+ * edge) and a theta x theta kernel `gauss` (HOST, row-major; BoundaryLoss._gaussian_kernel,
+ * losses.py:309-318) applied with zero padding.  theta0, theta odd, <= 15.  One launch, 8 B/px. */
+int b2seg_loss_boundary_weight_map(const float* target, float* weight, int planes, int h, int w,
+                                   int theta0, int theta, const float* gauss /*host*/, float gain,
+                                   void* stream);
+
+/* scipy.ndimage.distance_transform_edt on `planes` float32 planes (non-zero = foreground): exact
+ * Euclidean distance to the nearest zero pixel; a plane without zeros gets scipy's distances to
+ * (row -1, column 0).  mode 0: out = float32(distance)  (HausdorffDistanceLoss._compute_dtm,
+ * losses.py:262-273).  mode 1: out = 1 + alpha * float32(d / (max_plane(d) + 1e-7))
+ * (DistanceMapPenalizedCrossEntropy, losses.py:203-232).  Bit-identical to the scipy/numpy path. */
+size_t b2seg_loss_edt_workspace_bytes(int planes, int h, int w);
+int b2seg_loss_edt_f32(const float* src, float* out, int planes, int h, int w, int mode,
+                       float alpha, void* workspace, void* stream);
 
 /* ======================================================================== *
  *  2. Geometric augmentation gather                                         *

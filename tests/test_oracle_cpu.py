@@ -172,3 +172,19 @@ def test_augmentation_map_oracles_match_their_formulas():
     img = _smooth_u8(np.random.default_rng(0), h, w)
     assert np.array_equal(A.remap_u8(img, ox, oy, A.LINEAR, A.REFLECT, 0),
                           cv2.remap(img, ox, oy, cv2.INTER_LINEAR, borderMode=cv2.BORDER_REFLECT))
+
+
+def test_map_loss_oracle_matches_reference_fixture(loss_kat):
+    """The boundary-style losses of the oracle against the values the reference itself produced
+    (tests/golden/make_golden.py), and its distance transform against the definition."""
+    for tag, shape in (("kat", (4, 1, 256, 256)), ("small", (2, 1, 32, 48))):
+        logits, target = seg_losses.kat_inputs(shape)
+        for name in seg_losses.MAP_LOSSES:
+            ref = loss_kat[tag][name]
+            val, grad = seg_losses.loss_and_grad(name, logits, target)
+            assert val == pytest.approx(ref["loss"], rel=2e-5), name
+            assert float(grad.abs().sum()) == pytest.approx(ref["grad_l1"], rel=2e-4), name
+    rng = np.random.default_rng(0)
+    for plane in ((rng.random((23, 31)) > 0.3).astype(np.float32), np.ones((9, 14), np.float32),
+                  np.zeros((5, 5), np.float32), rng.random((12, 12)).astype(np.float32) + 0.1):
+        assert np.array_equal(seg_losses.edt(plane), seg_losses.edt_brute(plane))
