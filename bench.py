@@ -399,6 +399,15 @@ def _dp_c5(a, dev, world, rank, peaks):
     if world > 1:
         out["allreduce_bytes"] = int(plan.gflat.numel() * 4)
         out["buckets"] = getattr(model, "_dp_buckets", 1)
+        out["bucket_bytes"] = [int((hi - lo) * 4) for _, lo, hi in plan.buckets]
+        dataparallel.detach(model, crit)
+        os.environ["B2SEG_DP_BUCKETS"] = "0"   # A/B: one all-reduce after the whole backward
+        dataparallel.attach(model, world, criterion=crit)
+        for i in range(2):
+            step(i)
+        ms1 = _max_over_ranks(_timed_steps(step, a.c5_steps, world), world, dev)
+        out["ms_per_step_single_allreduce"] = ms1 / a.c5_steps
+        os.environ.pop("B2SEG_DP_BUCKETS", None)
         dataparallel.detach(model, crit)
         for i in range(2):
             step(i)

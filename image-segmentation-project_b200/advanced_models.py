@@ -83,9 +83,17 @@ class _UNetStep(torch.autograd.Function):
         lo, hi = plan.gflat.data_ptr(), plan.gflat.data_ptr() + plan.gflat.numel() * 4
         aliased = [p.grad is not None and lo <= p.grad.data_ptr() < hi for p in params]
         carry = plan.gflat.clone() if any(aliased) else None
-        plan.run_backward(dlogits.contiguous())
-        if model._grad_hook is not None:
-            model._grad_hook(plan.gflat)
+        hook = model._grad_hook
+        if hook is not None and getattr(hook, "bucketed", False) and len(plan.buckets) > 1:
+            # data parallel: one graph per gradient bucket, its all-reduce right behind it
+            plan.run_backward(dlogits.contiguous(), on_bucket=hook.bucket)
+            hook.finish(plan.gflat)
+            model._dp_buckets = len(plan.buckets)
+        else:
+            plan.run_backward(dlogits.contiguous())
+            if hook is not None:
+                hook(plan.gflat)
+                model._dp_buckets = 1
         if carry is not None:
             plan.gflat.add_(carry)
         grads = []

@@ -1,9 +1,12 @@
 """Data-parallel training of one UNetWithBackbone over the GPUs of a box (north_star config 5).
 
 One process per GPU (torch.distributed, NCCL over NVLink 5 / NVSwitch).  The plan writes every
-parameter gradient into ONE flat fp32 buffer (unet_plan.UNetPlan.gflat), so the whole gradient
-exchange is a single in-place `all_reduce` of ~97 MB (resnet34) -- on NVSwitch the bandwidth
-term is ~0.2 ms and launch latency dominates, which is why there is one bucket, not many.
+parameter gradient into ONE flat fp32 buffer (unet_plan.UNetPlan.gflat, ~97 MB for resnet34) laid
+out in the order the backward pass finishes them: decoder / gates / head, enc4, enc3, enc2,
+enc1 + stem.  The backward is replayed as one CUDA graph per such bucket and each bucket's in-place
+`all_reduce` is issued (async, on NCCL's stream) right behind its graph, so the exchange of the big
+early buckets overlaps the encoder backward and only the last, smallest one (~1 MB) is exposed.
+B2SEG_DP_BUCKETS=0 falls back to one all-reduce after the whole backward (the A/B in bench dp_c5).
 BatchNorm stays per replica, as in the reference (it has no SyncBN).
 
 The reference has no data-parallel path at all; this is the B200 addition
@@ -21,6 +24,33 @@ import torch
 import torch.distributed as dist
 
 
+import os
+
+
+class GradSync:
+    """The gradient exchange installed on a model: `bucket(slice)` starts one async all-reduce,
+    `finish(gflat)` makes the current stream wait for all of them; calling the object with the whole
+    buffer is the unbucketed form."""
+
+    def __init__(self, group, scale):
+        self.group, self.scale, self.works = group, scale, []
+        self.bucketed = os.environ.get("B2SEG_DP_BUCKETS", "1") != "0"
+
+    def bucket(self, t):
+        self.works.append(dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+
+    def finish(self, gflat):
+        for w in self.works:
+            w.wait()
+        self.works.clear()
+        if self.scale is not None:
+            gflat.mul_(self.scale)
+
+    def __call__(self, gflat):
+        self.bucket(gflat)
+        self.finish(gflat)
+
+
 def attach(model, world_size=None, group=None, criterion=None):
     """Install the flat-gradient all-reduce on `model` and make all replicas start identical."""
     world = world_size or dist.get_world_size(group)
@@ -34,14 +64,7 @@ def attach(model, world_size=None, group=None, criterion=None):
         if not hasattr(criterion, "dp_group"):
             raise TypeError("criterion must be one of the fused losses of losses.py")
         criterion.dp_group = group if group is not None else dist.group.WORLD
-    inv = 1.0 / world
-
-    def hook(gflat):
-        dist.all_reduce(gflat, op=dist.ReduceOp.SUM, group=group)
-        if not global_loss:
-            gflat.mul_(inv)
-
-    model._grad_hook = hook
+    model._grad_hook = GradSync(group, None if global_loss else 1.0 / world)
     return model
 
 

@@ -75,6 +75,15 @@ def _fused_bn_bwd_max_bytes():
     return float(os.environ.get("B2SEG_BN_FUSED_BWD_MB", "12")) * 2 ** 20
 
 
+def _grad_group(name: str) -> int:
+    """Order in which the backward pass finishes parameter gradients: 0 = decoder, attention gates
+    and head, 1..3 = enc4..enc2, 4 = enc1 and the stem."""
+    for g, pre in enumerate(("enc4.", "enc3.", "enc2."), start=1):
+        if name.startswith(pre):
+            return g
+    return 4 if name.startswith(("enc1.", "input_conv.", "bn1.")) else 0
+
+
 class UNetPlan:
     def __init__(self, model, N, H, W, training, need_grad):
         if H % 32 or W % 32:
@@ -89,6 +98,7 @@ class UNetPlan:
         self.backbone = model.backbone_name
         self.attn = bool(model.use_attention)
         self.fwd_ops, self.bwd_ops, self.tape = [], [], []
+        self._gview_log, self.buckets = None, []
         self.stored_g = {}  # name -> View of the gradient w.r.t. that activation (after backward)
         self.stored = {}  # name -> View / fp32 tensor of every activation kept in HBM (parity tests)
         self.keep = []
@@ -99,12 +109,21 @@ class UNetPlan:
                 raise L.B2SegError(f"parameter {n} must be a contiguous fp32 tensor on {self.dev}")
         self.param_ptrs = tuple(p.data_ptr() for p in self.params.values())
         # flat gradient buffer, one view per parameter (64-element aligned)
+        # The buffer is laid out in the order the backward pass FINISHES gradients (decoder, gates and
+        # head first, then enc4 .. enc1 and the stem), so that the slice of each group is contiguous
+        # and a data-parallel run can all-reduce it while the rest of the backward still runs.
         if self.need_grad:
-            off, self.goff = 0, {}
-            for n, p in self.params.items():
-                self.goff[n] = off
+            off, self.goff, self.ggroup = 0, {}, {}
+            order = sorted(self.params, key=lambda n: (_grad_group(n), list(self.params).index(n)))
+            self.group_range = {}
+            for n in order:
+                p, g = self.params[n], _grad_group(n)
+                self.goff[n], self.ggroup[n] = off, g
+                lo, _ = self.group_range.get(g, (off, off))
                 off += (p.numel() + 63) // 64 * 64
+                self.group_range[g] = (lo, off)
             self.gflat = self._alloc((off,), F32, zero=True)
+            self._gview_log, self.bwd_segs, self.buckets = [], None, None
         # bf16 GEMM-operand copies of the conv weights
         tot = sum(2 * ((p.numel() + 63) // 64 * 64) for p in self.params.values() if p.dim() == 4)
         self.packbuf = self._alloc((tot + 64,), BF16)
@@ -138,6 +157,8 @@ class UNetPlan:
     def gview(self, name):
         p = self.params[name]
         o = self.goff[name]
+        if self._gview_log is not None:
+            self._gview_log.append(name)
         return self.gflat[o:o + p.numel()].view(p.shape)
 
     def packed(self, name, layout):
@@ -396,8 +417,23 @@ class UNetPlan:
         self.tape += [bwd_up0, bwd_final]
         if ng:
             self.ws = self._alloc((max(self._ws_req, 1024) // 4 + 64,), F32)
+            done = {}  # gradient group -> index one past the last backward op that writes into it
             for fn in reversed(self.tape):
+                self._gview_log = []
                 fn()
+                for n in self._gview_log:
+                    done[self.ggroup[n]] = len(self.bwd_ops)
+            self._gview_log = None
+            # buckets in group order; a group can go out once every earlier group is final too
+            self.buckets, cut = [], 0
+            for g in sorted(self.group_range):
+                cut = max(cut, done.get(g, 0))
+                lo, hi = self.group_range[g]
+                if self.buckets and self.buckets[-1][0] == cut:
+                    self.buckets[-1] = (cut, self.buckets[-1][1], hi)
+                else:
+                    self.buckets.append((cut, lo, hi))
+            self.buckets[-1] = (len(self.bwd_ops),) + self.buckets[-1][1:]
         self.tape = None
         self._finish_pack()
         # the weight repack (fp32 parameters -> bf16 GEMM operands) overlaps the stem, which reads the
@@ -656,6 +692,20 @@ class UNetPlan:
         self.generation += 1
         return self.logits
 
-    def run_backward(self, dlogits: torch.Tensor):
+    def run_backward(self, dlogits: torch.Tensor, on_bucket=None):
+        """Replay the backward pass.  With `on_bucket` (data-parallel runs) it is replayed as one CUDA
+        graph per gradient bucket, and on_bucket(slice of gflat) is called as soon as the segment
+        that completes that slice has been enqueued -- the caller starts its all-reduce there, which
+        then overlaps the remaining segments."""
         self.dlogits.copy_(dlogits.reshape(self.dlogits.shape))
-        self.bwd.run()
+        if on_bucket is None:
+            self.bwd.run()
+            return
+        if self.bwd_segs is None:
+            self.bwd_segs, start = [], 0
+            for cut, lo, hi in self.buckets:
+                self.bwd_segs.append((co.Seq(self.bwd_ops[start:cut], side_kinds=("wgrad",)), lo, hi))
+                start = cut
+        for seg, lo, hi in self.bwd_segs:
+            seg.run()
+            on_bucket(self.gflat[lo:hi])

@@ -239,3 +239,52 @@ def test_fused_batchnorm_matches_three_kernel_sequence(cuda, monkeypatch):
         assert float((gf[n].double() - gu[n].double()).norm()) <= 2e-2 * max(float(gu[n].norm()), 1e-2 * gmax), n
     print(f"\n[fused BN] launches per step {nf} (three-kernel sequence: {nu})")
     assert nf < nu - 100
+
+
+def test_bucketed_backward_equals_single_graph(cuda):
+    """Data-parallel replay (one CUDA graph per gradient bucket, b2seg.dataparallel) writes exactly
+    the gradients of the single-graph backward, hands out disjoint slices that tile the flat buffer in
+    the order the backward finishes them, and every slice is final when it is handed out."""
+    import advanced_models
+    import losses
+    torch.manual_seed(3)
+    model = advanced_models.UNetWithBackbone(1, "resnet34", pretrained=False, use_attention=True).to(cuda).train()
+    crit = losses.get_loss_function({"loss_fn": "combo"})
+    x = torch.rand(4, 1, 64, 64, device=cuda)
+    y = (torch.rand(4, 1, 64, 64, device=cuda) > 0.7).float()
+
+    def grads():
+        model.zero_grad(set_to_none=True)
+        crit(model(x), y).backward()
+        plan = model._plan_for(x, True)
+        return plan, plan.gflat.clone()
+
+    plan, want = grads()
+    assert 3 <= len(plan.buckets) <= 5
+    assert plan.buckets[0][1] == 0 and plan.buckets[-1][2] == plan.gflat.numel()
+    assert all(a[2] == b[1] and a[0] < b[0] for a, b in zip(plan.buckets, plan.buckets[1:]))
+    assert plan.buckets[-1][0] == len(plan.bwd_ops)
+
+    class Spy:
+        bucketed = True
+
+        def __init__(self):
+            self.seen, self.snap = [], []
+
+        def bucket(self, t):
+            self.seen.append((t.data_ptr(), t.numel()))
+            self.snap.append(t.clone())      # ordered behind the segment on the stream: must be final
+
+        def finish(self, gflat):
+            pass
+
+    spy = Spy()
+    model._grad_hook = spy
+    _, got = grads()
+    model._grad_hook = None
+    assert torch.equal(got, want)
+    base = plan.gflat.data_ptr()
+    assert [((p - base) // 4, n) for p, n in spy.seen] == [(lo, hi - lo) for _, lo, hi in plan.buckets]
+    for (_, lo, hi), snap in zip(plan.buckets, spy.snap):
+        assert torch.equal(snap, want[lo:hi])
+    assert model._dp_buckets == len(plan.buckets)

@@ -173,8 +173,13 @@ def _job_dp(rank, world):
     dataparallel.attach(model, world)
     gflat = torch.arange(8, dtype=torch.float32) * (rank + 1)
     model._grad_hook(gflat)
+    # the bucketed form: slices go out one by one (async), finish() waits for all and averages
+    g2 = torch.arange(8, dtype=torch.float32) * (rank + 1)
+    for lo, hi in ((5, 8), (2, 5), (0, 2)):
+        model._grad_hook.bucket(g2[lo:hi])
+    model._grad_hook.finish(g2)
     dataparallel.detach(model)
-    return {"w": model.w.detach().clone(), "running": model.running.clone(), "g": gflat,
+    return {"w": model.w.detach().clone(), "running": model.running.clone(), "g": gflat, "g2": g2,
             "hook_cleared": model._grad_hook is None}
 
 
@@ -185,4 +190,5 @@ def test_dataparallel_hook_gloo_world2(tmp_path):
     assert torch.equal(r0["running"], ref.running) and torch.equal(r1["running"], ref.running)
     want = torch.arange(8, dtype=torch.float32) * 1.5  # mean of (1x, 2x)
     assert torch.equal(r0["g"], want) and torch.equal(r1["g"], want)
+    assert torch.equal(r0["g2"], want) and torch.equal(r1["g2"], want)
     assert r0["hook_cleared"] and r1["hook_cleared"]

@@ -63,6 +63,25 @@ for loss_name in ("combo", "tversky", "focal"):
             ok = ok and good
             print(f"{loss_name:8s} step {step}: global loss {got:.7f} vs concatenated {want:.7f} (rel {rel_max:.1e}); "
                   f"replicas identical: {same_all}  {'OK' if good else 'FAIL'}", flush=True)
+    # (3) bucketed exchange (one all-reduce per backward segment) == one all-reduce at the end
+    plan = model._plan_for(x, True)
+    gs = []
+    for env in ("1", "0"):
+        dataparallel.detach(model, crit)
+        os.environ["B2SEG_DP_BUCKETS"] = env
+        dataparallel.attach(model, world, criterion=crit)
+        opt.zero_grad()
+        crit(model(x), y).backward()
+        gs.append((plan.gflat.clone(), model._dp_buckets))
+    os.environ.pop("B2SEG_DP_BUCKETS", None)
+    diff = float((gs[0][0] - gs[1][0]).abs().max() / gs[1][0].abs().max())
+    flags = torch.tensor([diff], device=dev, dtype=torch.float64)
+    dist.all_reduce(flags, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        good = float(flags[0]) < 1e-6 and gs[0][1] > 1 and gs[1][1] == 1
+        ok = ok and good
+        print(f"{loss_name:8s} bucketed ({gs[0][1]} buckets {[ (hi - lo) * 4 >> 10 for _, lo, hi in plan.buckets]} KiB) vs "
+              f"single all-reduce: max rel diff {float(flags[0]):.1e}  {'OK' if good else 'FAIL'}", flush=True)
     dataparallel.detach(model, crit)
 dist.barrier()
 dist.destroy_process_group()

@@ -1,5 +1,5 @@
 #!/bin/bash
-# One parameterised GPU recipe (run under gpurun):  tools/gpu_check.sh [tests] [bench] [ops] [ncu] [hbm]
+# One parameterised GPU recipe (run under gpurun):  tools/gpu_check.sh [tests] [bench] [ops] [ncu] [hbm] [dp]
 #   tests  pytest -m gpu (+ smoke)          bench  default bench.py + reference arm
 #   ops    per-op / per-segment / in-graph timings   ncu   launch list + DRAM bytes per kernel of one step
 #   hbm    tools/hbm_bench.py ([64,1,1024,1024] loss / metric / augment kernels)
@@ -35,6 +35,22 @@ ncu)
       --profile-from-start off --csv --log-file gpurun_out/dram_step.csv \
       python bench.py --steps 1 --warmup 3 --no-kernel-timing --no-cpu-baseline --no-extras > gpurun_out/ncu_dram.log 2>&1; echo "dram list rc=$?"
   python tools/dram_summary.py gpurun_out/dram_step.csv > gpurun_out/dram_step_summary.txt 2>&1; head -30 gpurun_out/dram_step_summary.txt;;
+dp)
+  # data parallel over all visible GPUs: consistency over real NCCL, then the bench line (carries dp_c5)
+  NG=$(nvidia-smi -L | wc -l)
+  timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $NG --master-addr 127.0.0.1 --master-port 29631 \
+      tools/dp_check.py > gpurun_out/dp_check_n$NG.txt 2>&1; echo "dp_check rc=$?"; grep -E "OK|FAIL|PASSED|FAILED|Error" gpurun_out/dp_check_n$NG.txt | tail -20
+  timeout 1200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $NG --master-addr 127.0.0.1 --master-port 29632 \
+      bench.py --gpus $NG > gpurun_out/bench_n$NG.json 2> gpurun_out/bench_n$NG.err; echo "bench N=$NG rc=$?"; tail -3 gpurun_out/bench_n$NG.err
+  python - <<PY
+import json
+d = json.load(open('gpurun_out/bench_n$NG.json'))
+print('value', round(d['value'], 1), 'ms', round(d['ms_per_step'], 3), 'n', d['n_gpus'], 'e2e', round(d['e2e']['value'], 1))
+print('dp_c5', json.dumps(d.get('dp_c5')))
+PY
+  NCCL_DEBUG=INFO timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $NG --master-addr 127.0.0.1 --master-port 29633 \
+      bench.py --gpus $NG --steps 2 --warmup 3 --no-extras --mode dp > gpurun_out/bench_dp_n$NG.json 2> gpurun_out/nccl_info_n$NG.txt; echo "dp-mode bench rc=$?"
+  grep -E "NVLS|via P2P|Channel 00/" gpurun_out/nccl_info_n$NG.txt | head -5; cut -c1-400 gpurun_out/bench_dp_n$NG.json;;
 hbm)
   timeout 600 python tools/hbm_bench.py > gpurun_out/hbm_kernels.json 2> gpurun_out/hbm_kernels.err; echo "hbm rc=$?"; tail -3 gpurun_out/hbm_kernels.err;;
 esac; done
