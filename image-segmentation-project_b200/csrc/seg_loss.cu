@@ -24,11 +24,32 @@ struct PixelTerms {
   float p, bce, one_m_pt;
 };
 
+// Single-instruction special functions (MUFU): the range fix-ups and the Newton step the CUDA
+// intrinsics wrap around them cost ~15 issue slots per pixel and a divergent slow-path call, which
+// made these streaming kernels issue-bound instead of HBM-bound.  Inputs here are always in the
+// units' accurate range (e in (0,1], 1+e in [1,2]); relative error <= 2^-22.
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float lg2_approx(float x) {
+  float y;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 // softplus(-|x|) = log1p(exp(-|x|)) without the 1+e rounding loss for small e.
-__device__ __forceinline__ float log1p_exp_neg(float e) {
+__device__ __forceinline__ float log1p_exp_neg(float e, float one_plus_e) {
   // e in (0, 1].  Series below 2^-6: error < e^4/4 relative 6e-8.
-  float series = e * (1.0f - e * (0.5f - e * (1.0f / 3.0f)));
-  return e < 0.015625f ? series : __logf(1.0f + e);
+  const float series = e * (1.0f - e * (0.5f - e * (1.0f / 3.0f)));
+  const float lg = lg2_approx(one_plus_e) * 0.69314718f;
+  return e < 0.015625f ? series : lg;
 }
 
 // SOFT = false is the hard-target shortcut of the focal term: pt = exp(-bce) (losses.py:78-80) is
@@ -37,14 +58,15 @@ __device__ __forceinline__ float log1p_exp_neg(float e) {
 template <bool NEED_FOCAL, bool SOFT = true>
 __device__ __forceinline__ PixelTerms pixel_terms(float x, float t) {
   PixelTerms r;
-  const float e = __expf(-fabsf(x));
-  const float inv = __frcp_rn(1.0f + e);
+  const float e = ex2_approx(fabsf(x) * -1.44269504f);
+  const float s1 = 1.0f + e;
+  const float inv = rcp_approx(s1);
   const float small = e * inv;  // min(p, 1-p)
   r.p = x >= 0.0f ? inv : small;
-  r.bce = fmaxf(x, 0.0f) - x * t + log1p_exp_neg(e);
+  r.bce = fmaxf(x, 0.0f) - x * t + log1p_exp_neg(e, s1);
   if (NEED_FOCAL) {
     if (SOFT) {
-      r.one_m_pt = 1.0f - __expf(-r.bce);
+      r.one_m_pt = 1.0f - ex2_approx(r.bce * -1.44269504f);
     } else {
       const float omp = x >= 0.0f ? small : inv;  // 1 - p
       r.one_m_pt = t == 1.0f ? omp : r.p;
@@ -61,7 +83,7 @@ __device__ __forceinline__ bool is_hard4(const float4& t) {
 
 __device__ __forceinline__ float pow_pos(float base, float g) {
   // base in [0,1]; g > 0.  lg2(0) = -inf -> ex2(-inf) = 0.
-  return exp2f(g * __log2f(base));
+  return ex2_approx(g * lg2_approx(base));
 }
 
 // Per-pixel term of ExponentialLogarithmicLoss (losses.py:190-192), in the reference's own float32
@@ -501,9 +523,22 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
-int pick_blocks(long long n, int per_thread) {
+// Grid = what is needed, capped at ONE resident wave of this instantiation (grid-stride loops: a
+// partial second wave would leave SMs idle for the tail).
+template <auto Kern>
+int resident_blocks() {
+  static int per_sm = 0;
+  if (per_sm == 0) {
+    int nb = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, Kern, kThreads, 0) != cudaSuccess || nb < 1) nb = 1;
+    per_sm = nb;
+  }
+  return per_sm * b2_num_sms();
+}
+
+int pick_blocks(long long n, int per_thread, int resident) {
   long long b = (n + (long long)kThreads * per_thread - 1) / ((long long)kThreads * per_thread);
-  const long long cap = (long long)b2_num_sms() * 8;
+  const long long cap = resident;
   if (b > cap) b = cap;
   if (b > kMaxBlocks) b = kMaxBlocks;
   if (b < 1) b = 1;
@@ -538,12 +573,12 @@ extern "C" int b2seg_seg_loss_fwd(const float* logits, const float* target,
   const bool vec = aligned16(logits) && aligned16(target) && (!wmap || aligned16(weight_map));
   LossSpecDev sd;
   sd.s = *spec;
-  const int blocks = pick_blocks(n, 16);
   cudaStream_t st = (cudaStream_t)stream;
   ReduceWs* ws = (ReduceWs*)workspace;
-#define LAUNCH(F, W, V)                                                                      \
-  seg_loss_fwd_kernel<F, W, V><<<blocks, kThreads, 0, st>>>(logits, target, weight_map, n, sd, \
-                                                            ws, stats, loss_out, coef)
+#define LAUNCH(F, W, V)                                                                            \
+  seg_loss_fwd_kernel<F, W, V>                                                                     \
+      <<<pick_blocks(n, 16, resident_blocks<seg_loss_fwd_kernel<F, W, V>>()), kThreads, 0, st>>>(  \
+          logits, target, weight_map, n, sd, ws, stats, loss_out, coef)
   if (focal) {
     if (wmap) { if (vec) LAUNCH(1, true, true); else LAUNCH(1, true, false); }
     else      { if (vec) LAUNCH(1, false, true); else LAUNCH(1, false, false); }
@@ -567,13 +602,13 @@ extern "C" int b2seg_seg_loss_bwd(const float* logits, const float* target,
   const bool wmap = weight_map != nullptr;
   const bool vec = aligned16(logits) && aligned16(target) && aligned16(grad_logits) &&
                    (!wmap || aligned16(weight_map));
-  const int blocks = pick_blocks(n, 8);
   cudaStream_t st = (cudaStream_t)stream;
   // The focal coefficient lives on the device: the kernel branches once, uniformly, between its
   // focal and focal-free bodies (the first template argument is unused).
-#define LAUNCH(W, V)                                                                        \
-  seg_loss_bwd_kernel<1, W, V><<<blocks, kThreads, 0, st>>>(logits, target, weight_map, n, \
-                                                               coef, grad_out, grad_logits)
+#define LAUNCH(W, V)                                                                             \
+  seg_loss_bwd_kernel<1, W, V>                                                                   \
+      <<<pick_blocks(n, 8, resident_blocks<seg_loss_bwd_kernel<1, W, V>>()), kThreads, 0, st>>>( \
+          logits, target, weight_map, n, coef, grad_out, grad_logits)
   if (wmap) { if (vec) LAUNCH(true, true); else LAUNCH(true, false); }
   else      { if (vec) LAUNCH(false, true); else LAUNCH(false, false); }
 #undef LAUNCH
@@ -612,13 +647,14 @@ extern "C" int b2seg_seg_metrics_from_probs(const float* probs, const float* tar
   B2_REQUIRE(probs && target && workspace && stats, "seg_metrics: null argument");
   B2_REQUIRE(n > 0, "seg_metrics: n must be positive (got %lld)", (long long)n);
   const bool vec = aligned16(probs) && aligned16(target);
-  const int blocks = pick_blocks(n, 16);
   cudaStream_t st = (cudaStream_t)stream;
   ReduceWs* ws = (ReduceWs*)workspace;
   if (vec)
-    seg_metrics_probs_kernel<true><<<blocks, kThreads, 0, st>>>(probs, target, n, ws, stats);
+    seg_metrics_probs_kernel<true>
+        <<<pick_blocks(n, 16, resident_blocks<seg_metrics_probs_kernel<true>>()), kThreads, 0, st>>>(probs, target, n, ws, stats);
   else
-    seg_metrics_probs_kernel<false><<<blocks, kThreads, 0, st>>>(probs, target, n, ws, stats);
+    seg_metrics_probs_kernel<false>
+        <<<pick_blocks(n, 16, resident_blocks<seg_metrics_probs_kernel<false>>()), kThreads, 0, st>>>(probs, target, n, ws, stats);
   B2_CHECK_CUDA(cudaGetLastError());
   return B2SEG_OK;
 }
