@@ -10,7 +10,8 @@ import os
 
 ABI_VERSION = 2
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb2seg.so")
+# B2SEG_LIB_PATH: development A/B runs against another build of the same ABI (never a fallback)
+LIB_PATH = os.environ.get("B2SEG_LIB_PATH") or os.path.join(_HERE, "libb2seg.so")
 
 
 class B2SegError(RuntimeError):

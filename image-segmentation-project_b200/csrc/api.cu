@@ -46,7 +46,7 @@ bool b2_pdl_enabled() {
 }
 
 int b2_encode_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
-                        const uint64_t* strides_bytes, const uint32_t* box, int swizzle128) {
+                        const uint64_t* strides_bytes, const uint32_t* box, int swizzle) {
   static PFN_cuTensorMapEncodeTiled_v12000 encode = nullptr;
   if (!encode) {
     void* fn = nullptr;
@@ -82,7 +82,8 @@ int b2_encode_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint
   CUresult r = encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank,
                       const_cast<void*>(base), gdim, gstr, bdim, estr,
                       CU_TENSOR_MAP_INTERLEAVE_NONE,
-                      swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                      swizzle == 1 ? CU_TENSOR_MAP_SWIZZLE_128B : swizzle == 2 ? CU_TENSOR_MAP_SWIZZLE_64B
+                                   : swizzle == 3 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_NONE,
                       CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     b2seg_set_error("cuTensorMapEncodeTiled failed: CUresult %d (rank %d, dims %llu,%llu,%llu,%llu "

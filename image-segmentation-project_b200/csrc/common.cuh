@@ -195,6 +195,39 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// Parked wait for warps that have nothing to do until the phase completes (epilogue warps waiting
+// for an accumulator, the producer waiting for a free slot).  A plain try_wait loop re-issues a SYNCS
+// instruction every few cycles, and SYNCS shares the SM's MIO queue with UTCHMMA: eight spinning
+// epilogue warps slowed the MMA issuer from 48 to ~85 cycles per MMA (profiles/r02_halo_timeline.txt).
+// The suspend-time hint lets the hardware park the warp until the barrier flips; B2SEG_WAIT_MODE
+// selects the variant at build time for A/B runs (0 = plain spin, 1 = hint, 2 = hint + nanosleep).
+#ifndef B2SEG_WAIT_MODE
+#define B2SEG_WAIT_MODE 0
+#endif
+__device__ __forceinline__ bool mbar_try_wait_hint(uint64_t* bar, uint32_t parity, uint32_t hint_ns) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity), "r"(hint_ns)
+      : "memory");
+  return ok != 0;
+}
+// Non-blocking probe of a phase (look-ahead polls in the MMA issue loops: the answer is only a hint,
+// the blocking wait above is the fallback).
+__device__ __forceinline__ bool mbar_test_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
 // Bounded wait: a pipeline bug must trap, never hang the GPU box.  The slow path is kept out of
 // line so the pipeline loops of the single-warp producer / MMA roles stay a few instructions long
 // (those warps are issue-latency bound: every instruction in their loops costs ~10 cycles).
@@ -210,6 +243,27 @@ static __device__ __noinline__ void mbar_wait_slow(uint64_t* bar, uint32_t parit
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (!mbar_try_wait(bar, parity)) mbar_wait_slow(bar, parity);
+}
+static __device__ __noinline__ void mbar_wait_parked_slow(uint64_t* bar, uint32_t parity) {
+  const long long t0 = clock64();
+  for (;;) {
+#if B2SEG_WAIT_MODE == 0
+    if (mbar_try_wait(bar, parity)) return;
+#else
+    if (mbar_try_wait_hint(bar, parity, 20000u)) return;
+#endif
+#if B2SEG_WAIT_MODE == 2
+    __nanosleep(64);
+#endif
+    if (clock64() - t0 > 4000000000LL) {
+      printf("b2seg: mbarrier wait timeout (block %d,%d,%d thread %d)\n", blockIdx.x, blockIdx.y, blockIdx.z,
+             threadIdx.x);
+      __trap();
+    }
+  }
+}
+__device__ __forceinline__ void mbar_wait_parked(uint64_t* bar, uint32_t parity) {
+  if (!mbar_test_wait(bar, parity)) mbar_wait_parked_slow(bar, parity);
 }
 
 __device__ __forceinline__ void tma_prefetch_desc(const void* tmap) {
@@ -238,6 +292,37 @@ __device__ __forceinline__ void tma_load_4d(void* dst, const void* tmap, uint64_
       "[%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(smem_u32(dst)),
       "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
       : "memory");
+}
+
+// TMA stores (shared -> global, bulk async-group completion).  The issuing thread commits the group
+// and later waits for the source reads (smem reusable) or for full completion.
+__device__ __forceinline__ void tma_store_4d(const void* tmap, const void* src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(tmap),
+               "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+// Element-wise add into global memory (bf16 tensor map: the L2 adds in bf16).
+__device__ __forceinline__ void tma_reduce_add_4d(const void* tmap, const void* src, int c0, int c1, int c2,
+                                                  int c3) {
+  asm volatile(
+      "cp.reduce.async.bulk.tensor.4d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(
+          tmap),
+      "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_group_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+template <int N>
+__device__ __forceinline__ void bulk_wait_group() {
+  asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void sts_u4(void* dst, uint4 v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(dst)), "r"(v.x), "r"(v.y), "r"(v.z),
+               "r"(v.w)
+               : "memory");
 }
 
 // ---------------------------------------------------------------------------
@@ -278,6 +363,31 @@ __device__ __forceinline__ void umma_bf16_ss(uint32_t tmem_d, uint64_t adesc, ui
       "setp.ne.b32 p, %4, 0;\n\t"
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+// Predicated forms for fully converged issue loops: every lane runs the (warp-uniform) descriptor
+// arithmetic, so ptxas keeps it in the uniform datapath, and only the async instruction itself is
+// guarded by the elect.sync result `leader`.  An `if (elect_one_sync()) { ...36 MMAs... }` region
+// instead made ptxas precompute all descriptors in vector registers and move them over with R2UR:
+// ~110 instructions before the first MMA of every tile and up to 22 per MMA (r02 notes in DESIGN 3.1).
+__device__ __forceinline__ void umma_bf16_ss_pred(uint32_t leader, uint32_t tmem_d, uint64_t adesc,
+                                                  uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "setp.ne.b32 q, %5, 0;\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(leader)
+      : "memory");
+}
+__device__ __forceinline__ void tcgen05_commit_pred(uint32_t leader, uint64_t* bar) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t"
+      "setp.ne.b32 q, %1, 0;\n\t"
+      "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(
+          smem_u32(bar)),
+      "r"(leader)
       : "memory");
 }
 
@@ -353,6 +463,7 @@ static inline cudaError_t b2_launch(void (*kernel)(KArgs...), dim3 grid, dim3 bl
 // ---------------------------------------------------------------------------
 // Host: TMA descriptor encoding through the driver entry point (no -lcuda).
 // ---------------------------------------------------------------------------
+// swizzle: 0 = none, 1 = 128 B, 2 = 64 B, 3 = 32 B
 int b2_encode_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
                         const uint64_t* strides_bytes /* rank-1 entries, dims 1.. */,
-                        const uint32_t* box, int swizzle128);
+                        const uint32_t* box, int swizzle);

@@ -15,17 +15,19 @@
 // slabs stream through a second ring.  Accumulators are double buffered in TMEM; eight epilogue
 // warps (two per TMEM lane quadrant) drain one tile while the next one is being multiplied.
 //
-// Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM alloc + MMA issuer,
-// warps 2..9 = epilogue.
+// Warp roles (352 threads): warp 0 = TMA producer, warps 1 and 2 = MMA issuers (even / odd pixel tiles,
+// one TMEM accumulator each; warp 1 owns the TMEM allocation), warps 3..10 = epilogue.
 #include <new>
 #include <stdlib.h>
 #include <string.h>
+#include <vector>
 
 #include "ops.cuh"
 
 namespace {
 
-constexpr int kThreadsH = 320;
+constexpr int kThreadsH = 352;  // producer, two MMA issuers, eight epilogue warps
+constexpr int kEpiWarp0 = 3;
 constexpr int kMaxAStages = 8;
 constexpr int kMaxBSlots = 18;
 constexpr int kAcc = 2;  // TMEM accumulator stages (4 measured no faster; 2 leaves TMEM for a PDL-overlapped successor)
@@ -33,8 +35,9 @@ constexpr int kAcc = 2;  // TMEM accumulator stages (4 measured no faster; 2 lea
 struct alignas(64) HaloParams {
   CUtensorMap tmA;  // box (64 ch, wt+2, ht+2, 1)
   CUtensorMap tmB;  // box (64 ch, BLOCK_N, 1 tap)
-  int8_t dh[9], dw[9], wtap[9];
+  int8_t wtap[9];    // weight tap index of raster tap r = (dh+1)*3 + (dw+1)
   int kchunks;
+  int ksteps_last;   // K = 16 steps of the last 64-channel chunk (cin % 64 != 0: TMA zero-fills the rest)
   int wt, ht, tilesW, tilesH, mtiles, ntiles;
   int on, oh, ow;
   bf16* out;
@@ -44,9 +47,51 @@ struct alignas(64) HaloParams {
   float* stats;
   int accumulate;
   int resident, a_stages, b_slots, stat_rows;
-  int probe;  // B2SEG_PROBE bits (perf experiments only): 1 no output stores, 2 no stats, 4 no MMAs, 8 issue every chunk's MMAs 3x
+  int probe;  // B2SEG_PROBE bits (perf experiments only): 1 no output stores, 2 no stats, 4 no MMAs, 16 no A traffic after the first tile, 32 no TMEM reads
   int a_stage_bytes, b_off, bar_off, stat_off;
+  CUtensorMap tmO;   // output view, box (32 ch, 8, 4, 1), 64 B swizzle: one epilogue warp's 32 pixels x 32 channels
+  int issuers;       // 2: MMA warps 1 and 2 alternate pixel tiles; 1: warp 1 issues every tile
+  int tma_out;       // epilogue stages through shared memory and stores / reduce-adds with TMA
+  int epi_off;
+  long long* trace;  // B2SEG_HALO_TRACE=1: CTA 0 records clock64 per tile and role (debug only)
 };
+
+#ifndef HALO_TRACE_ENABLE  // the trace points cost ~25 % even when off at run time: compile them in only on demand
+#define HALO_TRACE(k, tileidx) do {} while (0)
+#else
+#define HALO_TRACE(k, tileidx)                                                              \
+  do {                                                                                     \
+    if (p.trace && blockIdx.x == 0 && lane == 0 && (tileidx) < 64) p.trace[(tileidx) * 8 + (k)] = clock64(); \
+  } while (0)
+#endif
+
+constexpr int kHaloPitch = 10;  // halo tile pitch in pixels: wt + 2 with wt = 8 (enforced by the creator)
+
+// Taps [T0, T1) of one 64-channel chunk of a pixel tile (raster order) x KS K-steps into one accumulator,
+// issued by the elected thread.  Every operand offset is an immediate added to the two chunk descriptors,
+// which keeps the block at ~3 SASS instructions per MMA (2 x UIADD3.64 + UTCHMMA).  Keep ONE copy of this
+// block per code path: when the same offsets appeared in several unrolled copies ptxas hoisted all 72
+// descriptors into vector registers (~110 instructions ahead of the first MMA of every tile, R2UR pairs
+// per MMA) and the tensor pipe idled behind the issuing thread.
+template <int BLOCK_N, int KS, int T0, int T1>
+__device__ __forceinline__ void halo_issue_taps(uint32_t tmem_d, uint64_t ad, uint64_t bd, uint32_t idesc,
+                                                uint32_t acc0) {
+#pragma unroll
+  for (int t = T0; t < T1; ++t) {
+#pragma unroll
+    for (int k = 0; k < KS; ++k)
+      umma_bf16_ss(tmem_d, ad + (uint64_t)(((t / 3) * kHaloPitch + (t % 3)) * 8 + 2 * k),
+                   bd + (uint64_t)(t * ((BLOCK_N * 128) >> 4) + 2 * k), idesc, (t != T0 || k != 0) ? 1u : acc0);
+  }
+}
+template <int BLOCK_N, int T0, int T1>
+__device__ __forceinline__ void halo_issue_taps_ks(int ks, uint32_t tmem_d, uint64_t ad, uint64_t bd,
+                                                   uint32_t idesc, uint32_t acc0) {
+  if (ks == 4) halo_issue_taps<BLOCK_N, 4, T0, T1>(tmem_d, ad, bd, idesc, acc0);
+  else if (ks == 2) halo_issue_taps<BLOCK_N, 2, T0, T1>(tmem_d, ad, bd, idesc, acc0);
+  else if (ks == 1) halo_issue_taps<BLOCK_N, 1, T0, T1>(tmem_d, ad, bd, idesc, acc0);
+  else halo_issue_taps<BLOCK_N, 3, T0, T1>(tmem_d, ad, bd, idesc, acc0);
+}
 
 template <int BLOCK_N, bool STATS>
 __global__ void __launch_bounds__(kThreadsH, 1)
@@ -69,7 +114,7 @@ __global__ void __launch_bounds__(kThreadsH, 1)
   const int ntile = blockIdx.x % p.ntiles;
   const int mt0 = blockIdx.x / p.ntiles, mstep = gridDim.x / p.ntiles;
   const int col0 = ntile * BLOCK_N;
-  const int pitch = p.wt + 2;
+  constexpr int pitch = kHaloPitch;
 
   if (warp == 0 && lane == 0) {
     for (int i = 0; i < p.a_stages; ++i) {
@@ -87,22 +132,49 @@ __global__ void __launch_bounds__(kThreadsH, 1)
     fence_barrier_init();
     tma_prefetch_desc(&p.tmA);
     tma_prefetch_desc(&p.tmB);
+    if (p.tma_out) tma_prefetch_desc(&p.tmO);
   }
   if (warp == 1) tmem_alloc<kAcc * BLOCK_N>(tmem_slot);
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // Resident weights do not depend on the predecessor grid (the packed operands were written by a
+  // kernel that completed before any kernel of this chain started): request them BEFORE the
+  // dependency wait, one mbarrier per 64-channel chunk (nine tap slabs each).
+  if (warp == 0 && p.resident) {
+    for (int kc = 0; kc < p.kchunks; ++kc) {
+      if (elect_one_sync()) {
+        mbar_expect_tx(&b_full[kc], 9 * B_SLAB);
+        for (int t = 0; t < 9; ++t)
+          tma_load_3d(smem + p.b_off + (kc * 9 + t) * B_SLAB, &p.tmB, &b_full[kc], kc * 64, col0, p.wtap[t]);
+      }
+      __syncwarp();
+    }
+  }
   pdl_wait();  // barriers, TMEM and descriptors are set up; now wait for the producer grid
+
+  // pixel-tile walk without divisions: (tw, th, n) advance by the decomposition of mstep
+  const int tilesHW = p.tilesW * p.tilesH;
+  const int d_n = mstep / tilesHW, d_th = (mstep % tilesHW) / p.tilesW, d_tw = mstep % p.tilesW;
+  int tw = mt0 % p.tilesW, th = (mt0 / p.tilesW) % p.tilesH, tn = mt0 / tilesHW;
+  auto next_tile = [&]() {
+    tw += d_tw;
+    if (tw >= p.tilesW) { tw -= p.tilesW; ++th; }
+    th += d_th;
+    if (th >= p.tilesH) { th -= p.tilesH; ++tn; }
+    tn += d_n;
+  };
 
   if (warp == 0) {
     // ===================== TMA producer (converged warp, elected issue) =====================
     {
       uint32_t s = 0, ph = 1, bs = 0, bph = 1;  // ring slots and the parity a free slot shows
       bool first = true;
+      uint32_t ptile = 0;
       const uint32_t halo_bytes = (uint32_t)(pitch * (p.ht + 2) * 128);
-      for (int mt = mt0; mt < p.mtiles; mt += mstep, first = false) {
-        const int tw = mt % p.tilesW, th = (mt / p.tilesW) % p.tilesH, n0 = mt / (p.tilesW * p.tilesH);
+      for (int mt = mt0; mt < p.mtiles; mt += mstep, first = false, next_tile(), ++ptile) {
+        const int n0 = tn;
         const int w0 = tw * p.wt - 1, h0 = th * p.ht - 1;
         for (int kc = 0; kc < p.kchunks; ++kc) {
           mbar_wait(&a_empty[s], ph);
@@ -115,25 +187,16 @@ __global__ void __launch_bounds__(kThreadsH, 1)
             }
           }
           __syncwarp();
+          if (kc == 0) HALO_TRACE(0, ptile);
           if (++s == (uint32_t)p.a_stages) { s = 0; ph ^= 1u; }
-          if (p.resident) {
-            if (first) {
-              for (int t = 0; t < 9; ++t) {
-                const int slab = kc * 9 + t;
-                if (elect_one_sync()) {
-                  mbar_expect_tx(&b_full[slab], B_SLAB);
-                  tma_load_3d(smem + p.b_off + slab * B_SLAB, &p.tmB, &b_full[slab], kc * 64, col0,
-                              p.wtap[t]);
-                }
-                __syncwarp();
-              }
-            }
-          } else {
-            for (int t = 0; t < 9; ++t) {
+          if (!p.resident) {
+            for (int g = 0; g < 3; ++g) {  // one ring slot = one tap row (three 64-channel slabs)
               mbar_wait(&b_empty[bs], bph);
               if (elect_one_sync()) {
-                mbar_expect_tx(&b_full[bs], B_SLAB);
-                tma_load_3d(smem + p.b_off + bs * B_SLAB, &p.tmB, &b_full[bs], kc * 64, col0, p.wtap[t]);
+                mbar_expect_tx(&b_full[bs], 3 * B_SLAB);
+                for (int j = 0; j < 3; ++j)
+                  tma_load_3d(smem + p.b_off + (bs * 3 + j) * B_SLAB, &p.tmB, &b_full[bs], kc * 64, col0,
+                              p.wtap[g * 3 + j]);
               }
               __syncwarp();
               if (++bs == (uint32_t)p.b_slots) { bs = 0; bph ^= 1u; }
@@ -142,93 +205,90 @@ __global__ void __launch_bounds__(kThreadsH, 1)
         }
       }
     }
-  } else if (warp == 1) {
-    // ===================== MMA issuer (converged warp, elected issue) =====================
+  } else if (warp <= 2) {
+    // ===================== MMA issuers (converged warp, elected issue) =====================
+    // The issuing thread is instruction bound, not tensor bound, unless its loop is a few
+    // instructions per MMA (profiles/r02_ncu_conv_source_notes.txt: 22 SASS instructions per
+    // UTCHMMA made a 128x64x16 MMA cost 85 cycles instead of 48).  Taps are therefore kept in raster
+    // order so that every operand offset inside a chunk is an immediate added to two running
+    // descriptors: tap (i, j) reads the halo tile (i * 10 + j) rows further and weight slab 3i + j.
     {
       constexpr uint32_t idesc = umma_idesc_bf16(128, BLOCK_N, 0, 0);
       constexpr uint32_t BSLAB16 = B_SLAB >> 4;
-      uint32_t toff16[9];  // tap (dh,dw) -> rows into the halo tile, in 16-byte descriptor units
-#pragma unroll
-      for (int t = 0; t < 9; ++t) toff16[t] = (uint32_t)(((p.dh[t] + 1) * pitch + (p.dw[t] + 1)) * 8);
       const uint32_t a_stage16 = (uint32_t)p.a_stage_bytes >> 4;
-      const uint64_t adesc0 = umma_smem_desc(smem_u32(smem), 16, (uint32_t)pitch * 128);
+      const uint64_t adesc0 = umma_smem_desc(smem_u32(smem), 16, (uint32_t)kHaloPitch * 128);
       const uint64_t bdesc0 = umma_smem_desc(smem_u32(smem + p.b_off), 16, 1024);
-      uint32_t s = 0, ph = 0, bs = 0, bph = 0, tile = 0;
-      for (int mt = mt0; mt < p.mtiles; mt += mstep, ++tile) {
-        const uint32_t acc = tile % kAcc, aph = (tile / kAcc) & 1u;
-        mbar_wait(&tmem_empty[acc], aph ^ 1u);
-        tcgen05_fence_after();
-        const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
-        for (int kc = 0; kc < p.kchunks; ++kc) {
-          mbar_wait(&a_full[s], ph);
-          tcgen05_fence_after();
-          const uint64_t ad_s = adesc0 + (uint64_t)(s * a_stage16);
-          const bool last = kc == p.kchunks - 1;
-          if (p.resident && tile != 0) {
-            // steady state: weights are resident, the whole chunk (9 taps x 4 MMAs) is one issue block
-            const uint64_t bd_k = bdesc0 + (uint64_t)((uint32_t)kc * 9u * BSLAB16);
-            if (elect_one_sync()) {
-              for (int rep = (p.probe & 8) ? 2 : 0; rep > 0; --rep) {  // probe: extra MMA passes
-#pragma unroll
-                for (int t = 0; t < 9; ++t) {
-                  const uint64_t ad = ad_s + (uint64_t)toff16[t];
-                  const uint64_t bd = bd_k + (uint64_t)(t * BSLAB16);
-#pragma unroll
-                  for (int k = 0; k < 4; ++k)
-                    umma_bf16_ss(tmem_d, ad + (uint64_t)(2 * k), bd + (uint64_t)(2 * k), idesc, 1u);
-                }
-              }
-#pragma unroll
-              for (int t = 0; t < 9; ++t) {
-                if (p.probe & 4) break;
-                const uint64_t ad = ad_s + (uint64_t)toff16[t];
-                const uint64_t bd = bd_k + (uint64_t)(t * BSLAB16);
-#pragma unroll
-                for (int k = 0; k < 4; ++k)
-                  umma_bf16_ss(tmem_d, ad + (uint64_t)(2 * k), bd + (uint64_t)(2 * k), idesc,
-                               (t | k) != 0 ? 1u : (kc != 0 ? 1u : 0u));
-              }
-              tcgen05_commit(&a_empty[s]);
-              if (last) tcgen05_commit(&tmem_full[acc]);
-            }
-            __syncwarp();
-          } else {
-#pragma unroll
-            for (int t = 0; t < 9; ++t) {
-              uint32_t slot;
-              if (p.resident) {
-                slot = kc * 9 + t;
-                mbar_wait(&b_full[slot], 0);
-              } else {
-                slot = bs;
-                mbar_wait(&b_full[bs], bph);
-              }
+      // tcgen05.mma issue is nearly synchronous with execution (tools/umma_rate.cu: a 36-MMA burst is
+      // issued in 1825 cycles and complete after 1952), so the tensor pipe idles for every cycle
+      // the issuing warp spends elsewhere: the whole role is straight-line converged code.
+      // ONE elected thread runs the whole role.  tcgen05.mma issue is nearly synchronous with execution
+      // (tools/umma_rate.cu: a 36-MMA burst is issued in 1825 cycles and complete after 1952), and every
+      // separate `if (elect_one_sync()) {...} __syncwarp()` region costs ~180 cycles of tensor idle time
+      // (same probe: groups of 4 MMAs take 380 cycles, of 36 take 1905), so the tile loop, its barrier
+      // waits (3 cycles each once the phase is complete) and the commits all live inside one region.
+      // TWO issuers alternate pixel tiles (warp 1 the even ones into accumulator 0, warp 2 the odd ones
+      // into accumulator 1): between two tiles an issuer spends ~600 cycles on its barrier waits and
+      // commits (same probe: 2 waits + 36 MMAs + 2 commits = 2316 cycles against 1814 for the MMAs alone),
+      // and that now overlaps the other issuer's MMAs instead of idling the tensor pipe.
+      static_assert(kAcc == 2, "one accumulator per MMA issuer");
+      // An issuer must never be two phases ahead of a ring barrier (a parity wait cannot tell phase n
+      // from phase n - 2), so the second issuer only runs with resident weights and a_stages > kchunks
+      // (the creator sets p.issuers); the streaming path keeps one issuer for both accumulators.
+      if (elect_one_sync() && warp - 1 < p.issuers) {
+        const uint32_t me = (uint32_t)(warp - 1), nis = (uint32_t)p.issuers;
+        // ring positions advance in the global (tile, chunk) order the producer fills them in
+        uint32_t s = 0, ph = 0, bs = 0, bph = 0;
+        auto skip_a = [&](uint32_t n) { s += n; while (s >= (uint32_t)p.a_stages) { s -= p.a_stages; ph ^= 1u; } };
+        auto skip_b = [&](uint32_t n) { bs += n; while (bs >= (uint32_t)p.b_slots) { bs -= p.b_slots; bph ^= 1u; } };
+        if (me) skip_a(p.kchunks);
+        uint32_t tile = me;
+        for (int mt = mt0 + (int)me * mstep; mt < p.mtiles; mt += (int)nis * mstep, tile += nis) {
+          const uint32_t acc = tile & 1u, aph = (tile >> 1) & 1u;
+          const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
+          mbar_wait(&tmem_empty[acc], aph ^ 1u);
+          HALO_TRACE(6, tile);
+          for (int kc = 0; kc < p.kchunks; ++kc) {
+            const bool last = kc == p.kchunks - 1;
+            const int ks = last ? p.ksteps_last : 4;
+            mbar_wait(&a_full[s], ph);
+            if (kc == 0) HALO_TRACE(1, tile);
+            const uint64_t ad_s = adesc0 + (uint64_t)(s * a_stage16);
+            if (p.resident) {
+              if (tile < 2) mbar_wait(&b_full[kc], 0);  // this chunk's nine weight slabs have landed
               tcgen05_fence_after();
-              const uint64_t ad = ad_s + (uint64_t)toff16[t];
-              const uint64_t bd = bdesc0 + (uint64_t)(slot * BSLAB16);
-              if (elect_one_sync()) {
-#pragma unroll
-                for (int k = 0; k < 4; ++k)
-                  umma_bf16_ss(tmem_d, ad + (uint64_t)(2 * k), bd + (uint64_t)(2 * k), idesc,
-                               (kc | t | k) != 0 ? 1u : 0u);
-                if (!p.resident) tcgen05_commit(&b_empty[bs]);
-                if (t == 8) {
-                  tcgen05_commit(&a_empty[s]);
-                  if (last) tcgen05_commit(&tmem_full[acc]);
-                }
-              }
-              __syncwarp();
-              if (!p.resident && ++bs == (uint32_t)p.b_slots) { bs = 0; bph ^= 1u; }
+              const uint64_t bd_k = bdesc0 + (uint64_t)((uint32_t)kc * 9u * BSLAB16);
+              if (!(p.probe & 4)) halo_issue_taps_ks<BLOCK_N, 0, 9>(ks, tmem_d, ad_s, bd_k, idesc, kc != 0 ? 1u : 0u);
+            } else {
+              // tap row G: three taps against one ring slot of weights
+#define HALO_STREAM_ROW(G)                                                                               \
+  do {                                                                                                   \
+    mbar_wait(&b_full[bs], bph);                                                                         \
+    tcgen05_fence_after();                                                                               \
+    const uint64_t bd = bdesc0 + (uint64_t)(bs * 3u * BSLAB16) - (uint64_t)((G) * 3 * BSLAB16);          \
+    halo_issue_taps_ks<BLOCK_N, 3 * (G), 3 * (G) + 3>(ks, tmem_d, ad_s, bd, idesc,                       \
+                                                      (kc != 0 || (G) != 0) ? 1u : 0u);                 \
+    tcgen05_commit(&b_empty[bs]);                                                                        \
+    skip_b(1);                                                                                           \
+  } while (0)
+              HALO_STREAM_ROW(0);
+              HALO_STREAM_ROW(1);
+              HALO_STREAM_ROW(2);
+#undef HALO_STREAM_ROW
             }
+            tcgen05_commit(&a_empty[s]);
+            if (last) tcgen05_commit(&tmem_full[acc]);
+            skip_a(1);
           }
-          if (++s == (uint32_t)p.a_stages) { s = 0; ph ^= 1u; }
+          if (nis == 2) skip_a(p.kchunks);  // the other issuer's tile
+          HALO_TRACE(2, tile);
         }
       }
+      __syncwarp();
     }
   } else {
     // ===================== epilogue (8 warps) =====================
     const int wq = warp & 3;             // TMEM lane quadrant this warp may access
-    const int half = (warp - 2) >> 2;    // which 32-column chunks this warp drains
+    const int half = (warp - kEpiWarp0) >> 2;    // which 32-column chunks this warp drains
     const int r = wq * 32 + lane;
     const int lh = r / p.wt, lw = r % p.wt;
     constexpr int NCH = BLOCK_N / 32;
@@ -243,9 +303,10 @@ __global__ void __launch_bounds__(kThreadsH, 1)
 #pragma unroll
         for (int j = 0; j < 32; ++j) s1[ci][j] = s2[ci][j] = 0.0f;
     }
-    uint32_t tile = 0;
-    for (int mt = mt0; mt < p.mtiles; mt += mstep, ++tile) {
-      const int tw = mt % p.tilesW, th = (mt / p.tilesW) % p.tilesH, pn = mt / (p.tilesW * p.tilesH);
+    uint32_t tile = 0, nstore = 0;
+    uint8_t* epi_sm = smem + p.epi_off + (warp - kEpiWarp0) * 4096;  // two 2 KB staging slots per epilogue warp
+    for (int mt = mt0; mt < p.mtiles; mt += mstep, ++tile, next_tile()) {
+      const int pn = tn;
       const int phh = th * p.ht + lh, pw = tw * p.wt + lw;
       const bool row_ok = phh < p.oh && pw < p.ow;
       const long long row_off = (long long)pn * p.osn + (long long)phh * p.osh + (long long)pw * p.osw;
@@ -253,7 +314,7 @@ __global__ void __launch_bounds__(kThreadsH, 1)
       // accumulate mode: fetch the old output values BEFORE waiting for the accumulator, so
       // their (uncoalesced, one pixel row per lane) latency hides behind the MMAs
       uint4 old[MYCH][4];
-      if (!STATS && p.accumulate && row_ok) {
+      if (!STATS && p.accumulate && row_ok && !p.tma_out) {
 #pragma unroll
         for (int ci = 0; ci < MYCH; ++ci) {
           const int c = half + 2 * ci;
@@ -266,6 +327,7 @@ __global__ void __launch_bounds__(kThreadsH, 1)
       }
       mbar_wait(&tmem_full[acc], aph);
       tcgen05_fence_after();
+      if (warp == kEpiWarp0) HALO_TRACE(3, tile);
       const uint32_t tmem_d = tmem_base + acc * BLOCK_N + ((uint32_t)(wq * 32) << 16);
       if (half >= NCH) {  // BLOCK_N == 32: the second warp of the quadrant has no columns
         if (lane == 0) mbar_arrive(&tmem_empty[acc]);
@@ -275,7 +337,13 @@ __global__ void __launch_bounds__(kThreadsH, 1)
         const int c = half + 2 * ci;
         if (c < NCH) {
           float v[32];
-          tmem_ld_32x32b_x32(tmem_d + (uint32_t)(c * 32), v);
+          if (p.probe & 32) {  // probe: no TMEM read
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = 0.0f;
+          } else {
+            tmem_ld_32x32b_x32(tmem_d + (uint32_t)(c * 32), v);
+          }
+          if (warp == kEpiWarp0 && ci == 0) HALO_TRACE(4, tile);
           if (c + 2 >= NCH) {  // this warp's last chunk is in registers: release the accumulator
             tcgen05_fence_before();
             __syncwarp();
@@ -286,7 +354,35 @@ __global__ void __launch_bounds__(kThreadsH, 1)
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + colc + j);
           }
-          if (row_ok && !(p.probe & 1)) {
+          if (p.tma_out) {
+            // Stage this warp's 32 pixels x 32 channels in shared memory (64 B rows, 64 B swizzle: the
+            // 16-byte stores of a quarter warp land in eight different bank groups) and let TMA write --
+            // or reduce-add, in accumulate mode -- the 4 x 8 pixel box.  A warp's scattered 16-byte
+            // global stores cost 32 L1 wavefronts per instruction, and those wavefronts share the
+            // shared-memory pipe with the tensor core's operand reads (an N = 64 MMA needs all of it):
+            // 1024 (2048 with the old-value loads) wavefronts per tile added straight to the MMA time.
+            uint8_t* sb = epi_sm + ((nstore & 1u) << 11);
+            if (lane == 0) bulk_wait_group_read<1>();  // the store that last used this slot has read it
+            __syncwarp();
+            const int sw = (lane >> 1) & 3;
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+              uint4 pk;
+              pk.x = f2_to_bf2(v[g * 8 + 0], v[g * 8 + 1]);
+              pk.y = f2_to_bf2(v[g * 8 + 2], v[g * 8 + 3]);
+              pk.z = f2_to_bf2(v[g * 8 + 4], v[g * 8 + 5]);
+              pk.w = f2_to_bf2(v[g * 8 + 6], v[g * 8 + 7]);
+              sts_u4(sb + lane * 64 + ((g ^ sw) << 4), pk);
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0 && !(p.probe & 1)) {
+              if (!STATS && p.accumulate) tma_reduce_add_4d(&p.tmO, sb, colc, tw * 8, th * 16 + wq * 4, pn);
+              else tma_store_4d(&p.tmO, sb, colc, tw * 8, th * 16 + wq * 4, pn);
+              bulk_commit_group();
+            }
+            ++nstore;
+          } else if (row_ok && !(p.probe & 1)) {
             bf16* dst = p.out + row_off + colc;
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
@@ -319,7 +415,9 @@ __global__ void __launch_bounds__(kThreadsH, 1)
           }
         }
       }
+      if (warp == kEpiWarp0) HALO_TRACE(5, tile);
     }
+    if (p.tma_out && lane == 0) bulk_wait_group<0>();  // all of this warp's stores have completed
     if (STATS) {  // one (sum, sumsq) row per CTA group; rows no group owns are zero-filled
       float* stat_sm = reinterpret_cast<float*>(smem + p.stat_off) + wq * 2 * BLOCK_N;
 #pragma unroll
@@ -334,7 +432,7 @@ __global__ void __launch_bounds__(kThreadsH, 1)
       }
       asm volatile("bar.sync 1, 256;" ::: "memory");
       const float* sm0 = reinterpret_cast<const float*>(smem + p.stat_off);
-      for (int e = threadIdx.x - 64; e < 2 * BLOCK_N; e += 256) {
+      for (int e = threadIdx.x - 32 * kEpiWarp0; e < 2 * BLOCK_N; e += 256) {
         const float x = (sm0[e] + sm0[2 * BLOCK_N + e]) + (sm0[4 * BLOCK_N + e] + sm0[6 * BLOCK_N + e]);
         const int k = e / BLOCK_N, cc = e % BLOCK_N;
         p.stats[((size_t)mt0 * 2 + k) * p.ngemm + col0 + cc] = x;
@@ -368,6 +466,24 @@ struct HaloOp : b2seg_op {
     else HALO_LAUNCH(32);
 #undef HALO_LAUNCH
     B2_CHECK_CUDA(cudaGetLastError());
+    if (p.trace) {  // debug: dump CTA 0's per-tile timeline after every run
+      B2_CHECK_CUDA(cudaStreamSynchronize(st));
+      std::vector<long long> h(64 * 8);
+      B2_CHECK_CUDA(cudaMemcpy(h.data(), p.trace, h.size() * 8, cudaMemcpyDeviceToHost));
+      if (FILE* f = fopen(getenv("B2SEG_HALO_TRACE"), "a")) {
+        fprintf(f, "# halo3x3 BN=%d kchunks=%d mtiles=%d grid=%d resident=%d a_stages=%d  columns: tile prodA mma_afull mma_issued epi_full epi_ld epi_done mma_tmem_empty mma_half (cycles since first event)\n",
+                block_n, p.kchunks, p.mtiles, grid.x, p.resident, p.a_stages);
+        long long t0 = h[0];
+        for (int i = 0; i < 64 && h[i * 8 + 1]; ++i) {
+          fprintf(f, "%2d", i);
+          const int order[8] = {0, 1, 2, 3, 4, 5, 6, 7};
+          for (int k : order) fprintf(f, " %8lld", h[i * 8 + k] ? h[i * 8 + k] - t0 : -1LL);
+          fprintf(f, "\n");
+        }
+        fclose(f);
+      }
+      B2_CHECK_CUDA(cudaMemset(p.trace, 0, 64 * 8 * 8));
+    }
     return B2SEG_OK;
   }
 };
@@ -414,10 +530,13 @@ int b2_halo3x3_try_create(const b2seg_tapgemm_desc* d, b2seg_op** out) {
   const int kchunks = (d->cin + 63) / 64;
   const int a_stage = ((wt + 2) * (ht + 2) * 128 + 1023) / 1024 * 1024;
   const int bar_bytes = (2 * kMaxAStages + 2 * kMaxBSlots + 2 * kAcc) * 8 + 16;
-  // choose BLOCK_N and the weight mode
-  int bn = 0, resident = 0, a_stages = 0, b_slots = 0;
+  // choose BLOCK_N, the weight mode and the epilogue (TMA staging needs 4 KB per active epilogue warp)
+  int bn = 0, resident = 0, a_stages = 0, b_slots = 0, tma_out = 0;
   const int cands[3] = {128, 64, 32};
   auto fixed = [&](int n) { return bar_bytes + 4 * 2 * n * 4 + 1024; };
+  auto epi_bytes = [&](int n) { return (n >= 64 ? 8 : 4) * 4096 + 1024; };  // + alignment pad
+  bool want_tma = true;
+  if (const char* e = getenv("B2SEG_HALO_TMA_OUT")) want_tma = e[0] != '0';
   // 1) resident weights with the widest tile that leaves >= 3 A stages
   for (int c = 0; c < 3 && !bn; ++c) {
     const int n = cands[c];
@@ -425,9 +544,11 @@ int b2_halo3x3_try_create(const b2seg_tapgemm_desc* d, b2seg_op** out) {
     const int slabs = 9 * kchunks;
     if (slabs > kMaxBSlots) continue;
     const int left = kSmemMax - fixed(n) - slabs * n * 128;
-    if (left >= 3 * a_stage) {
+    const int min_stages = 3;
+    if (left >= min_stages * a_stage) {
       bn = n; resident = 1; b_slots = slabs;
-      a_stages = left / a_stage;
+      tma_out = want_tma && left - epi_bytes(n) >= min_stages * a_stage;
+      a_stages = (left - (tma_out ? epi_bytes(n) : 0)) / a_stage;
       if (a_stages > kMaxAStages) a_stages = kMaxAStages;
     }
   }
@@ -437,9 +558,14 @@ int b2_halo3x3_try_create(const b2seg_tapgemm_desc* d, b2seg_op** out) {
     if (nm % n) continue;
     bn = n; resident = 0;
     a_stages = 3;
-    b_slots = (kSmemMax - fixed(n) - a_stages * a_stage) / (n * 128);
-    if (b_slots > kMaxBSlots) b_slots = kMaxBSlots;
-    if (b_slots < 4) bn = 0;
+    tma_out = want_tma;
+    b_slots = (kSmemMax - fixed(n) - a_stages * a_stage - (tma_out ? epi_bytes(n) : 0)) / (3 * n * 128);  // ring slot = one tap row (3 slabs)
+    if (b_slots < 2 && tma_out) {
+      tma_out = 0;
+      b_slots = (kSmemMax - fixed(n) - a_stages * a_stage) / (3 * n * 128);
+    }
+    if (b_slots > 6) b_slots = 6;
+    if (b_slots < 2) bn = 0;
   }
   if (!bn) return B2SEG_OK;
 
@@ -461,12 +587,10 @@ int b2_halo3x3_try_create(const b2seg_tapgemm_desc* d, b2seg_op** out) {
     int rc = b2_encode_tmap_bf16(&p.tmB, d->weights, 3, dims, strides, box, 1);
     if (rc != B2SEG_OK) { delete op; return rc; }
   }
-  for (int t = 0; t < 9; ++t) {
-    p.dh[t] = sub.taps[t].dh;
-    p.dw[t] = sub.taps[t].dw;
-    p.wtap[t] = sub.taps[t].wtap;
-  }
+  for (int t = 0; t < 9; ++t)  // raster order: slot (dh+1)*3 + (dw+1)
+    p.wtap[(sub.taps[t].dh + 1) * 3 + sub.taps[t].dw + 1] = (int8_t)sub.taps[t].wtap;
   p.kchunks = kchunks;
+  p.ksteps_last = d->cin % 64 ? (d->cin % 64 + 15) / 16 : 4;
   p.wt = wt; p.ht = ht;
   p.tilesW = (d->ow + wt - 1) / wt;
   p.tilesH = (d->oh + ht - 1) / ht;
@@ -484,14 +608,29 @@ int b2_halo3x3_try_create(const b2seg_tapgemm_desc* d, b2seg_op** out) {
   {
     const char* e = getenv("B2SEG_PROBE");
     p.probe = e ? atoi(e) : 0;
+    if (const char* tr = getenv("B2SEG_HALO_TRACE")) {
+      if (tr[0] && cudaMalloc(&p.trace, 64 * 8 * 8) == cudaSuccess) cudaMemset(p.trace, 0, 64 * 8 * 8);
+      else p.trace = nullptr;
+    }
     const char* st = getenv("B2SEG_ASTAGES");
     if (st && atoi(st) >= 1 && atoi(st) <= p.a_stages) p.a_stages = atoi(st);
   }
   p.a_stage_bytes = a_stage;
   p.b_off = a_stages * a_stage;
-  p.bar_off = p.b_off + b_slots * bn * 128;
+  p.bar_off = p.b_off + (resident ? b_slots : 3 * b_slots) * bn * 128;
   p.stat_off = p.bar_off + bar_bytes;
-  op->smem = (size_t)p.stat_off + 4 * 2 * bn * 4 + 1024;
+  p.epi_off = (p.stat_off + 4 * 2 * bn * 4 + 1023) / 1024 * 1024;
+  p.tma_out = tma_out;
+  p.issuers = (resident && a_stages > kchunks) ? 2 : 1;
+  if (const char* e = getenv("B2SEG_HALO_ISSUERS")) if (e[0] == '1') p.issuers = 1;
+  op->smem = (size_t)p.epi_off + (tma_out ? epi_bytes(bn) : 0) + 1024;
+  if (tma_out) {
+    const uint64_t dims[4] = {(uint64_t)nm, (uint64_t)d->ow, (uint64_t)d->oh, (uint64_t)d->on};
+    const uint64_t strides[3] = {(uint64_t)d->osw * 2, (uint64_t)d->osh * 2, (uint64_t)d->osn * 2};
+    const uint32_t box[4] = {32, 8, 4, 1};
+    int rc = b2_encode_tmap_bf16(&p.tmO, d->out, 4, dims, strides, box, 2);
+    if (rc != B2SEG_OK) { delete op; return rc; }
+  }
   op->block_n = bn;
   // one persistent CTA per SM; a CTA owns one column tile, so the grid is a multiple of ntiles
   int groups = b2_num_sms() / p.ntiles;

@@ -12,7 +12,7 @@ cases = [tuple(int(v) for v in a.split(",")) for a in sys.argv[1:]] or [
     (64, 128, 128, 96, 32), (64, 128, 128, 32, 32), (64, 64, 64, 128, 64)]
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
-def timed(op, reps=10):
+def timed(op, reps=int(os.environ.get('REPS', '10'))):
     op.run(); torch.cuda.synchronize()
     ts = []
     for _ in range(reps):
