@@ -121,7 +121,8 @@ __global__ void __launch_bounds__(kThreadsH, 1)
       mbar_init(&a_full[i], 1);
       mbar_init(&a_empty[i], 1);
     }
-    for (int i = 0; i < p.b_slots; ++i) {
+    const int nb = p.resident ? p.kchunks : p.b_slots;  // resident weights: one barrier per 64-channel chunk
+    for (int i = 0; i < nb; ++i) {
       mbar_init(&b_full[i], 1);
       mbar_init(&b_empty[i], 1);
     }
@@ -166,6 +167,12 @@ __global__ void __launch_bounds__(kThreadsH, 1)
     tn += d_n;
   };
 
+  // Streaming weights: every CTA would walk the (chunk, tap row) slabs in the same order and ask the
+  // same few L2 lines for the same 48 KB at the same moment; each CTA group starts at its own position
+  // of the cycle instead (the accumulation order of a tile depends on its CTA only: still reproducible).
+  const int rot = p.resident ? 0 : mt0;
+  const int kc0 = rot % p.kchunks, g0 = (rot / p.kchunks) % 3;
+
   if (warp == 0) {
     // ===================== TMA producer (converged warp, elected issue) =====================
     {
@@ -176,7 +183,8 @@ __global__ void __launch_bounds__(kThreadsH, 1)
       for (int mt = mt0; mt < p.mtiles; mt += mstep, first = false, next_tile(), ++ptile) {
         const int n0 = tn;
         const int w0 = tw * p.wt - 1, h0 = th * p.ht - 1;
-        for (int kc = 0; kc < p.kchunks; ++kc) {
+        for (int kq = 0; kq < p.kchunks; ++kq) {
+          const int kc = kq + kc0 < p.kchunks ? kq + kc0 : kq + kc0 - p.kchunks;
           mbar_wait(&a_empty[s], ph);
           if (elect_one_sync()) {
             if ((p.probe & 16) && !first) {
@@ -187,10 +195,11 @@ __global__ void __launch_bounds__(kThreadsH, 1)
             }
           }
           __syncwarp();
-          if (kc == 0) HALO_TRACE(0, ptile);
+          if (kq == 0) HALO_TRACE(0, ptile);
           if (++s == (uint32_t)p.a_stages) { s = 0; ph ^= 1u; }
           if (!p.resident) {
-            for (int g = 0; g < 3; ++g) {  // one ring slot = one tap row (three 64-channel slabs)
+            for (int gq = 0; gq < 3; ++gq) {  // one ring slot = one tap row (three 64-channel slabs)
+              const int g = gq + g0 < 3 ? gq + g0 : gq + g0 - 3;
               mbar_wait(&b_empty[bs], bph);
               if (elect_one_sync()) {
                 mbar_expect_tx(&b_full[bs], 3 * B_SLAB);
@@ -247,33 +256,31 @@ __global__ void __launch_bounds__(kThreadsH, 1)
           const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
           mbar_wait(&tmem_empty[acc], aph ^ 1u);
           HALO_TRACE(6, tile);
-          for (int kc = 0; kc < p.kchunks; ++kc) {
-            const bool last = kc == p.kchunks - 1;
-            const int ks = last ? p.ksteps_last : 4;
+          for (int kq = 0; kq < p.kchunks; ++kq) {
+            const int kc = kq + kc0 < p.kchunks ? kq + kc0 : kq + kc0 - p.kchunks;
+            const bool last = kq == p.kchunks - 1;
+            const int ks = kc == p.kchunks - 1 ? p.ksteps_last : 4;
             mbar_wait(&a_full[s], ph);
-            if (kc == 0) HALO_TRACE(1, tile);
+            if (kq == 0) HALO_TRACE(1, tile);
             const uint64_t ad_s = adesc0 + (uint64_t)(s * a_stage16);
             if (p.resident) {
               if (tile < 2) mbar_wait(&b_full[kc], 0);  // this chunk's nine weight slabs have landed
               tcgen05_fence_after();
               const uint64_t bd_k = bdesc0 + (uint64_t)((uint32_t)kc * 9u * BSLAB16);
-              if (!(p.probe & 4)) halo_issue_taps_ks<BLOCK_N, 0, 9>(ks, tmem_d, ad_s, bd_k, idesc, kc != 0 ? 1u : 0u);
+              if (!(p.probe & 4)) halo_issue_taps_ks<BLOCK_N, 0, 9>(ks, tmem_d, ad_s, bd_k, idesc, kq != 0 ? 1u : 0u);
             } else {
-              // tap row G: three taps against one ring slot of weights
-#define HALO_STREAM_ROW(G)                                                                               \
-  do {                                                                                                   \
-    mbar_wait(&b_full[bs], bph);                                                                         \
-    tcgen05_fence_after();                                                                               \
-    const uint64_t bd = bdesc0 + (uint64_t)(bs * 3u * BSLAB16) - (uint64_t)((G) * 3 * BSLAB16);          \
-    halo_issue_taps_ks<BLOCK_N, 3 * (G), 3 * (G) + 3>(ks, tmem_d, ad_s, bd, idesc,                       \
-                                                      (kc != 0 || (G) != 0) ? 1u : 0u);                 \
-    tcgen05_commit(&b_empty[bs]);                                                                        \
-    skip_b(1);                                                                                           \
-  } while (0)
-              HALO_STREAM_ROW(0);
-              HALO_STREAM_ROW(1);
-              HALO_STREAM_ROW(2);
-#undef HALO_STREAM_ROW
+              // one ring slot of weights = one tap row (three taps); rows in this CTA's rotated order
+#pragma unroll 1
+              for (int gq = 0; gq < 3; ++gq) {
+                const int g = gq + g0 < 3 ? gq + g0 : gq + g0 - 3;
+                mbar_wait(&b_full[bs], bph);
+                tcgen05_fence_after();
+                const uint64_t ad = ad_s + (uint64_t)(g * kHaloPitch * 8);
+                const uint64_t bd = bdesc0 + (uint64_t)(bs * 3u * BSLAB16);
+                halo_issue_taps_ks<BLOCK_N, 0, 3>(ks, tmem_d, ad, bd, idesc, (kq | gq) != 0 ? 1u : 0u);
+                tcgen05_commit(&b_empty[bs]);
+                skip_b(1);
+              }
             }
             tcgen05_commit(&a_empty[s]);
             if (last) tcgen05_commit(&tmem_full[acc]);

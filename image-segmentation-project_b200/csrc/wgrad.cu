@@ -308,21 +308,25 @@ __global__ void __launch_bounds__(kThreadsWG, 1)
 }
 
 // Sum split-K partials in fixed order and scatter into the gradient layout.
-// grid (cchunks, ceil(b_channels/16), 64/kRedI); a block owns kRedI channels of the tap side x 16
-// columns x all taps.  The splits are dealt round-robin to kRedG thread groups (partial sums in
-// split order, combined as ((g0+g1)+(g2+g3)): fixed order, bit-reproducible).  Partials are read
-// along the column index (coalesced), transposed through shared memory and written along
-// (channel, tap) -- contiguous in OIHW / IOHW parameter layouts.
-constexpr int kRedI = 4, kRedJ = 16, kRedG = 4;
+// grid (cchunks, ceil(b_channels/kRedJ), 64/kRedI); a block owns kRedI channels of the tap side x kRedJ
+// columns x all taps.  The reads are the whole cost (up to 148 splits of an L2-resident workspace) and
+// they are latency bound, so they are spread as wide as the block allows: a thread owns one float4 of
+// one (tap, channel) row and one of kRedG split groups, keeps all its loads in flight, and leaves a
+// partial sum in shared memory; the partials are combined as ((g0+g1)+(g2+g3))+((g4+g5)+(g6+g7)) --
+// fixed order, bit-reproducible -- and written along (channel, tap), contiguous in OIHW / IOHW.
+// (The first version walked the splits serially per thread: 22 us per launch at 341 GB/s, 1.25 ms/step.)
+constexpr int kRedI = 2, kRedJ = 32, kRedG = 8, kRedPitch = 36;
 __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const __grid_constant__ WgradParams p) {
   pdl_prologue();
-  __shared__ float sm[kRedG][kRedJ][kRedI * B2SEG_MAX_TAPS + 1];
+  __shared__ __align__(16) float sm[kRedG][kRedI * B2SEG_MAX_TAPS][kRedPitch];
   const int cchunk = blockIdx.x, j0 = blockIdx.y * kRedJ, i0 = blockIdx.z * kRedI;
   const size_t split_stride = (size_t)p.npairs * 128 * p.ncols_pad;
-  const int n1 = p.ntaps * kRedI * kRedJ;
-  for (int e = threadIdx.x; e < n1 * kRedG; e += blockDim.x) {
-    const int g = e / n1, o = e % n1;
-    const int jj = o % kRedJ, i = (o / kRedJ) % kRedI, tap = o / (kRedJ * kRedI);
+  const int nrows = kRedI * p.ntaps;
+  const int j4 = threadIdx.x & 7, slot = threadIdx.x >> 3;
+  const int j = j0 + j4 * 4;
+  for (int u = slot; u < nrows * kRedG; u += 32) {
+    const int g = u % kRedG, r = u / kRedG;
+    const int i = r / p.ntaps, tap = r % p.ntaps;
     int pair, row;
     if (p.halo) {
       const int q = p.slot[tap];
@@ -333,24 +337,35 @@ __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const __grid_constant
       pair = chunk >> 1;
       row = (chunk & 1) * 64 + i0 + i;
     }
-    const int j = j0 + jj;
-    float acc = 0.0f;
+    float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     if (j < p.b_channels) {
-      const float* src = p.ws + ((size_t)pair * 128 + row) * p.ncols_pad + j;
-      for (int s = g; s < p.nsplit; s += kRedG) acc += __ldg(src + (size_t)s * split_stride);
+      const float4* src = reinterpret_cast<const float4*>(p.ws + ((size_t)pair * 128 + row) * p.ncols_pad + j);
+      const size_t st4 = split_stride / 4;
+      int sidx = g;
+      for (; sidx + 3 * kRedG < p.nsplit; sidx += 4 * kRedG) {  // four loads in flight per step
+        const float4 a = __ldg(src + (size_t)sidx * st4), b = __ldg(src + (size_t)(sidx + kRedG) * st4),
+                     c = __ldg(src + (size_t)(sidx + 2 * kRedG) * st4), d = __ldg(src + (size_t)(sidx + 3 * kRedG) * st4);
+        acc.x = (((acc.x + a.x) + b.x) + c.x) + d.x;
+        acc.y = (((acc.y + a.y) + b.y) + c.y) + d.y;
+        acc.z = (((acc.z + a.z) + b.z) + c.z) + d.z;
+        acc.w = (((acc.w + a.w) + b.w) + c.w) + d.w;
+      }
+      for (; sidx < p.nsplit; sidx += kRedG) {
+        const float4 a = __ldg(src + (size_t)sidx * st4);
+        acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w;
+      }
     }
-    sm[g][jj][i * p.ntaps + tap] = acc;
+    *reinterpret_cast<float4*>(&sm[g][r][j4 * 4]) = acc;
   }
   __syncthreads();
-  const int run = kRedI * p.ntaps;
-  for (int e = threadIdx.x; e < kRedJ * run; e += blockDim.x) {
-    const int jj = e / run, r = e % run;
+  for (int e = threadIdx.x; e < kRedJ * nrows; e += blockDim.x) {
+    const int jj = e / nrows, r = e % nrows;
     const int i = r / p.ntaps, tap = r % p.ntaps;
-    const int ch = cchunk * 64 + i0 + i, j = j0 + jj;
-    if (ch >= p.a_channels || j >= p.b_channels) continue;
-    float* dst = p.grad + p.taps[tap].out_base + (long long)ch * p.row_stride +
-                 (long long)j * p.col_stride;
-    const float v = (sm[0][jj][r] + sm[1][jj][r]) + (sm[2][jj][r] + sm[3][jj][r]);
+    const int ch = cchunk * 64 + i0 + i, jo = j0 + jj;
+    if (ch >= p.a_channels || jo >= p.b_channels) continue;
+    float* dst = p.grad + p.taps[tap].out_base + (long long)ch * p.row_stride + (long long)jo * p.col_stride;
+    const float v = ((sm[0][r][jj] + sm[1][r][jj]) + (sm[2][r][jj] + sm[3][r][jj])) +
+                    ((sm[4][r][jj] + sm[5][r][jj]) + (sm[6][r][jj] + sm[7][r][jj]));
     *dst = p.accumulate ? *dst + v : v;
   }
 }
