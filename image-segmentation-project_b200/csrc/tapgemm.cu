@@ -23,6 +23,25 @@
 
 namespace {
 
+// Division by a run-time constant as multiply-high + shift (dividends here are tile indices < 2^24).
+struct FastDiv {
+  uint32_t mul, shift, d;
+};
+static inline FastDiv make_fastdiv(uint32_t d) {
+  FastDiv f;
+  f.d = d;
+  uint32_t l = 0;
+  while ((1u << l) < d) ++l;
+  f.shift = l;
+  f.mul = (uint32_t)(((uint64_t)1 << 32) * (((uint64_t)1 << l) - d) / d + 1);
+  return f;
+}
+#ifdef __CUDACC__
+__device__ __forceinline__ uint32_t fdiv(uint32_t n, const FastDiv& f) {
+  return (__umulhi(n, f.mul) + n) >> f.shift;
+}
+#endif
+
 struct TapSub {
   int ntaps;
   int8_t src[B2SEG_MAX_TAPS], dh[B2SEG_MAX_TAPS], dw[B2SEG_MAX_TAPS], wt[B2SEG_MAX_TAPS];
@@ -44,7 +63,24 @@ struct alignas(64) TapGemmParams {
   float* stats;
   int accumulate;
   int nsub, stat_rows;
+  // TMA epilogue (nsub == 1): every epilogue warp stages its 32 pixels x 32 columns in shared memory and
+  // stores / reduce-adds them as a pixel box; with a pixel shuffle there is one map per output phase
+  CUtensorMap tmO[4];
+  int tma_out, epi_off;
+  int box_ch;            // channels per store: 32, or 16 when a 32-column chunk spans two shuffle phases
+  int box_h, box_n;      // the warp's 32 pixels = wt x box_h x box_n
+  FastDiv dv_mtiles, dv_w, dv_hw;  // / mtiles, / tilesW, / (tilesW * tilesH)
+  long long* trace;      // -DTG_TRACE_ENABLE + B2SEG_TG_TRACE=file: CTA 0's per-tile clock64 timeline (debug)
 };
+
+#ifndef TG_TRACE_ENABLE
+#define TG_TRACE(k, tileidx) do {} while (0)
+#else
+#define TG_TRACE(k, tileidx)                                                                 \
+  do {                                                                                       \
+    if (p.trace && blockIdx.x == 0 && lane == 0 && (tileidx) < 64) p.trace[(tileidx) * 8 + (k)] = clock64(); \
+  } while (0)
+#endif
 
 constexpr int kThreadsTG = 192;
 constexpr int A_BYTES = 128 * 128;  // 128 pixels x 64 bf16
@@ -57,7 +93,11 @@ struct TGSmem {
   // full[NS], empty[NS], tmem_full[2], tmem_empty[2], tmem slot
   // [4 warps][2][BLOCK_N] f32 per-tile sums + [2][BLOCK_N] f32 running totals
   static constexpr int STAT_OFF = BAR_OFF + (2 * NSTAGES + 4) * 8 + 16;
-  static constexpr int TOTAL = STAT_OFF + 5 * 2 * BLOCK_N * 4 + 1024 /*align slack*/;
+  // TMA-epilogue staging: 2 KB slots per epilogue warp; two slots where two CTAs still fit an SM with them
+  static constexpr int EPI_SLOTS = BLOCK_N == 32 ? 2 : 1;
+  static constexpr int EPI_OFF = (STAT_OFF + 5 * 2 * BLOCK_N * 4 + 1023) / 1024 * 1024;
+  static constexpr int TOTAL = EPI_OFF + 4 * EPI_SLOTS * 2048 + 1024 /*align slack*/;
+  static_assert(2 * (TOTAL + 1024) <= 233472, "two CTAs per SM");
 };
 
 // A CTA keeps ONE column tile (blockIdx.x % ntiles; neighbouring CTAs share the A bricks through
@@ -77,7 +117,7 @@ __device__ __forceinline__ TGItem tg_item(int j, int mtiles) {
 // buffered in TMEM (2 x BLOCK_N columns), so the TMA producer and the MMA issuer run ahead
 // into the next item while the four epilogue warps drain the previous one.
 template <int BLOCK_N, int NSTAGES>
-__global__ void __launch_bounds__(kThreadsTG)
+__global__ void __launch_bounds__(kThreadsTG, 2)
     tapgemm_kernel(const __grid_constant__ TapGemmParams p) {
   pdl_trigger();
   using L = TGSmem<BLOCK_N, NSTAGES>;
@@ -108,6 +148,7 @@ __global__ void __launch_bounds__(kThreadsTG)
     fence_barrier_init();
     tma_prefetch_desc(&p.tmB);
     tma_prefetch_desc(&p.tmA[0]);
+    if (p.tma_out) tma_prefetch_desc(&p.tmO[0]);
   }
   if (warp == 1) tmem_alloc<2 * BLOCK_N>(tmem_slot);
   tcgen05_fence_before();
@@ -120,7 +161,8 @@ __global__ void __launch_bounds__(kThreadsTG)
     // ===================== TMA producer (converged warp, elected issue) =====================
     {
       uint32_t s = 0, ph = 1;  // ring slot and the parity a free slot shows
-      for (int j = grp; j < njobs; j += groups) {
+      uint32_t ptile = 0;
+      for (int j = grp; j < njobs; j += groups, ++ptile) {
         const TGItem w = tg_item(j, p.mtiles);
         const TapSub& sub = p.sub[w.sub];
         const int tw = w.mtile % p.tilesW, th = (w.mtile / p.tilesW) % p.tilesH,
@@ -138,6 +180,7 @@ __global__ void __launch_bounds__(kThreadsTG)
               tma_load_3d(sa + A_BYTES, &p.tmB, &full_bar[s], kc * 64, col0, wtap);
             }
             __syncwarp();
+            if (t == 0 && kc == 0) TG_TRACE(0, ptile);
             if (++s == NSTAGES) { s = 0; ph ^= 1u; }
           }
         }
@@ -157,10 +200,12 @@ __global__ void __launch_bounds__(kThreadsTG)
         const uint32_t acc = tile & 1u, aph = (tile >> 1) & 1u;
         mbar_wait(&tmem_empty[acc], aph ^ 1u);  // epilogue has drained this accumulator
         tcgen05_fence_after();
+        TG_TRACE(6, tile);
         const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
         for (int i = 0; i < iters; ++i) {
           mbar_wait(&full_bar[s], ph);
           tcgen05_fence_after();
+          if (i == 0) TG_TRACE(1, tile);
           const uint64_t so = (uint64_t)(s * (uint32_t)(L::STAGE >> 4));
           const uint64_t adesc = adesc0 + so, bdesc = bdesc0 + so;
           if (elect_one_sync()) {
@@ -174,6 +219,7 @@ __global__ void __launch_bounds__(kThreadsTG)
           __syncwarp();
           if (++s == NSTAGES) { s = 0; ph ^= 1u; }
         }
+        TG_TRACE(2, tile);
       }
     }
   } else {
@@ -186,14 +232,32 @@ __global__ void __launch_bounds__(kThreadsTG)
     float* stat_sm = reinterpret_cast<float*>(smem + L::STAT_OFF) + wq * 2 * BLOCK_N;
     // running (sum, sumsq) of this CTA over all its tiles: entry e is owned by one thread
     float* run_sm = reinterpret_cast<float*>(smem + L::STAT_OFF) + 8 * BLOCK_N;
+    // BatchNorm partial sums: for BLOCK_N == 32 they stay in registers across all tiles of the CTA and the
+    // cross-lane reduction runs once after the loop (conv3x3.cu); the N = 128 tiles (deep-K layers, where
+    // the epilogue is not the bottleneck) keep the per-tile fold through shared memory.  The per-tile fold
+    // cost the thin 1x1 layers ~1500 of their ~2300 epilogue cycles per tile (profiles/r02_tapgemm_timeline.txt).
+    constexpr bool REGSTATS = BLOCK_N == 32;  // 64 accumulators per thread at N = 64 spill (ptxas: 444 B)
+    constexpr int RCH = REGSTATS ? BLOCK_N / 32 : 1;
+    float rs1[RCH][32], rs2[RCH][32];
+    if (REGSTATS) {
+#pragma unroll
+      for (int c = 0; c < RCH; ++c)
+#pragma unroll
+        for (int jx = 0; jx < 32; ++jx) rs1[c][jx] = rs2[c][jx] = 0.0f;
+    }
     if (p.stats)
       for (int e = threadIdx.x - 64; e < 2 * BLOCK_N; e += 128) run_sm[e] = 0.0f;
-    uint32_t tile = 0;
+    uint32_t tile = 0, nstore = 0;
+    uint8_t* epi_sm = smem + L::EPI_OFF + wq * (L::EPI_SLOTS * 2048);  // this warp's 2 KB staging slots
+    const int r0 = wq * 32, ln0 = r0 / hw, lh0 = (r0 % hw) / p.wt;  // first pixel of this warp's box
     for (int j = grp; j < njobs; j += groups, ++tile) {
-      const TGItem w = tg_item(j, p.mtiles);
+      TGItem w;
+      w.sub = (int)fdiv((uint32_t)j, p.dv_mtiles);
+      w.mtile = j - w.sub * p.mtiles;
       const TapSub& sub = p.sub[w.sub];
-      const int tw = w.mtile % p.tilesW, th = (w.mtile / p.tilesW) % p.tilesH,
-                tn = w.mtile / (p.tilesW * p.tilesH);
+      const int tn = (int)fdiv((uint32_t)w.mtile, p.dv_hw);
+      const int rem = w.mtile - tn * (p.tilesW * p.tilesH);
+      const int th = (int)fdiv((uint32_t)rem, p.dv_w), tw = rem - th * p.tilesW;
       const int pn = tn * p.nt + ln, phh = th * p.ht + lh, pw = tw * p.wt + lw;
       const bool row_ok = pn < p.on && phh < p.oh && pw < p.ow;
       const long long row_off =
@@ -202,7 +266,7 @@ __global__ void __launch_bounds__(kThreadsTG)
       // accumulate mode: fetch the old output values BEFORE waiting for the accumulator, so
       // their (uncoalesced, one pixel row per lane) latency hides behind the MMAs
       uint4 old[BLOCK_N / 32][4];
-      if (p.accumulate && row_ok) {
+      if (p.accumulate && row_ok && !p.tma_out) {
 #pragma unroll
         for (int c = 0; c < BLOCK_N / 32; ++c)
 #pragma unroll
@@ -215,11 +279,13 @@ __global__ void __launch_bounds__(kThreadsTG)
       }
       mbar_wait(&tmem_full[acc], aph);
       tcgen05_fence_after();
+      if (warp == 2) TG_TRACE(3, tile);
       const uint32_t tmem_d = tmem_base + acc * BLOCK_N + ((uint32_t)(wq * 32) << 16);
 #pragma unroll
       for (int c = 0; c < BLOCK_N / 32; ++c) {
         float v[32];
         tmem_ld_32x32b_x32(tmem_d + (uint32_t)(c * 32), v);
+        if (warp == 2 && c == 0) TG_TRACE(4, tile);
         if (c == BLOCK_N / 32 - 1) {  // accumulator fully read: hand it back to the MMA issuer
           tcgen05_fence_before();
           __syncwarp();
@@ -230,7 +296,44 @@ __global__ void __launch_bounds__(kThreadsTG)
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + ((colc + j) & cq_mask));
         }
-        if (row_ok) {
+        if (p.tma_out) {
+          // stage 32 pixels x 32 columns and let TMA write (or reduce-add) the pixel box: the warp's
+          // scattered 16-byte global accesses cost 32 L1 wavefronts per instruction (conv3x3.cu)
+          uint8_t* sb = epi_sm + ((nstore & (uint32_t)(L::EPI_SLOTS - 1)) << 11);
+          if (lane == 0) bulk_wait_group_read<L::EPI_SLOTS - 1>();  // the store that last used this slot has read it
+          __syncwarp();
+          uint4 pk[4];
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            pk[g].x = f2_to_bf2(v[g * 8 + 0], v[g * 8 + 1]);
+            pk[g].y = f2_to_bf2(v[g * 8 + 2], v[g * 8 + 3]);
+            pk[g].z = f2_to_bf2(v[g * 8 + 4], v[g * 8 + 5]);
+            pk[g].w = f2_to_bf2(v[g * 8 + 6], v[g * 8 + 7]);
+          }
+          if (p.box_ch == 32) {  // 64 B rows, 64 B swizzle
+            const int sw = (lane >> 1) & 3;
+#pragma unroll
+            for (int g = 0; g < 4; ++g) sts_u4(sb + lane * 64 + ((g ^ sw) << 4), pk[g]);
+          } else {               // two 16-channel boxes of 32 B rows, no swizzle
+#pragma unroll
+            for (int g = 0; g < 4; ++g) sts_u4(sb + (g >> 1) * 1024 + lane * 32 + ((g & 1) << 4), pk[g]);
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            const int cw = tw * p.wt, chh = th * p.ht + lh0, cn = tn * p.nt + ln0;
+            for (int hh = 0; hh * p.box_ch < 32; ++hh) {
+              const int col = colc + hh * p.box_ch;
+              const int q = col >> p.cq_shift;
+              const void* tm = &p.tmO[q & 3];
+              const uint8_t* src = sb + hh * 1024;
+              if (p.accumulate) tma_reduce_add_4d(tm, src, col & cq_mask, cw, chh, cn);
+              else tma_store_4d(tm, src, col & cq_mask, cw, chh, cn);
+            }
+            bulk_commit_group();
+          }
+          ++nstore;
+        } else if (row_ok) {
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             const int col = colc + g * 8;
@@ -255,7 +358,15 @@ __global__ void __launch_bounds__(kThreadsTG)
             *reinterpret_cast<uint4*>(dst) = pk;
           }
         }
-        if (p.stats) {
+        if (REGSTATS) {
+          if (p.stats && row_ok) {
+#pragma unroll
+            for (int jx = 0; jx < 32; ++jx) {
+              rs1[c < RCH ? c : 0][jx] += v[jx];
+              rs2[c < RCH ? c : 0][jx] = fmaf(v[jx], v[jx], rs2[c < RCH ? c : 0][jx]);
+            }
+          }
+        } else if (p.stats) {
           float s1[32], s2[32];
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
@@ -269,13 +380,28 @@ __global__ void __launch_bounds__(kThreadsTG)
           stat_sm[BLOCK_N + c * 32 + lane] = b;
         }
       }
-      if (p.stats) {  // fold the four warps' sums into the CTA's running totals
+      if (!REGSTATS && p.stats) {  // fold the four warps' sums into the CTA's running totals
         asm volatile("bar.sync 1, 128;" ::: "memory");
         const float* sm0 = reinterpret_cast<const float*>(smem + L::STAT_OFF);
         for (int e = threadIdx.x - 64; e < 2 * BLOCK_N; e += 128)
           run_sm[e] += (sm0[e] + sm0[2 * BLOCK_N + e]) + (sm0[4 * BLOCK_N + e] + sm0[6 * BLOCK_N + e]);
         asm volatile("bar.sync 1, 128;" ::: "memory");  // stat_sm is rewritten by the next item
       }
+      if (warp == 2) TG_TRACE(5, tile);
+    }
+    if (p.tma_out && lane == 0) bulk_wait_group<0>();  // this warp's stores have completed
+    if (REGSTATS && p.stats) {  // one transposing reduction per warp and chunk, then the four warps' rows
+#pragma unroll
+      for (int c = 0; c < RCH; ++c) {
+        const float a = warp_transpose_sum32(rs1[c], lane);
+        const float b = warp_transpose_sum32(rs2[c], lane);
+        stat_sm[c * 32 + lane] = a;
+        stat_sm[BLOCK_N + c * 32 + lane] = b;
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      const float* sm0 = reinterpret_cast<const float*>(smem + L::STAT_OFF);
+      for (int e = threadIdx.x - 64; e < 2 * BLOCK_N; e += 128)
+        run_sm[e] = (sm0[e] + sm0[2 * BLOCK_N + e]) + (sm0[4 * BLOCK_N + e] + sm0[6 * BLOCK_N + e]);
     }
     if (p.stats) {  // one (sum, sumsq) row per CTA group; rows no group owns are zero-filled
       for (int e = threadIdx.x - 64; e < 2 * BLOCK_N; e += 128) {
@@ -308,6 +434,25 @@ struct TapGemmOp : b2seg_op {
     else TG_LAUNCH(32, 4);
 #undef TG_LAUNCH
     B2_CHECK_CUDA(cudaGetLastError());
+#ifdef TG_TRACE_ENABLE
+    if (p.trace) {
+      B2_CHECK_CUDA(cudaStreamSynchronize(st));
+      long long h[64 * 8];
+      B2_CHECK_CUDA(cudaMemcpy(h, p.trace, sizeof(h), cudaMemcpyDeviceToHost));
+      if (FILE* f = fopen(getenv("B2SEG_TG_TRACE"), "a")) {
+        fprintf(f, "# tapgemm BN=%d kchunks=%d mtiles=%d grid=%d nsub=%d tma_out=%d  columns: tile prodA mma_full mma_issued epi_full epi_ld epi_done mma_tmem_empty\n",
+                block_n, p.kchunks, p.mtiles, grid.x, p.nsub, p.tma_out);
+        const long long t0 = h[0];
+        for (int i = 0; i < 64 && h[i * 8 + 1]; ++i) {
+          fprintf(f, "%2d", i);
+          for (int k = 0; k < 7; ++k) fprintf(f, " %8lld", h[i * 8 + k] ? h[i * 8 + k] - t0 : -1LL);
+          fprintf(f, "\n");
+        }
+        fclose(f);
+      }
+      B2_CHECK_CUDA(cudaMemset(p.trace, 0, sizeof(h)));
+    }
+#endif
     return B2SEG_OK;
   }
 };
@@ -440,6 +585,31 @@ extern "C" int b2seg_tapgemm_create(const b2seg_tapgemm_desc* d, b2seg_op** out)
   p.accumulate = d->accumulate;
   p.nsub = d->nsub;
   p.stat_rows = b2seg_tapgemm_stat_rows(d->on, d->oh, d->ow);
+  p.dv_mtiles = make_fastdiv((uint32_t)p.mtiles);
+  p.dv_w = make_fastdiv((uint32_t)p.tilesW);
+  p.dv_hw = make_fastdiv((uint32_t)(p.tilesW * p.tilesH));
+  {  // TMA epilogue: one output map (no shuffle) or one per shuffle phase; not for phase-split outputs
+    const char* e = getenv("B2SEG_TG_TMA_OUT");
+    const bool want = !(e && e[0] == '0');
+    const int cq = cq_shift < 30 ? (1 << cq_shift) : d->ngemm;
+    p.box_ch = cq >= 32 ? 32 : 16;
+    p.box_h = p.ht < 32 / p.wt ? p.ht : 32 / p.wt;
+    p.box_n = 32 / (p.wt * p.box_h);
+    p.tma_out = want && d->nsub == 1 && d->sub[0].out_offset == 0 && cq >= 16 && cq % p.box_ch == 0 &&
+                (cq_shift == 30 || d->ngemm <= 4 * cq);
+    if (p.tma_out) {
+      const int nq = cq_shift < 30 ? d->ngemm / cq : 1;
+      for (int q = 0; q < 4; ++q) {
+        const int qq = q < nq ? q : 0;
+        const bf16* base = (const bf16*)d->out + (long long)(qq >> 1) * d->oqh + (long long)(qq & 1) * d->oqw;
+        const uint64_t dims[4] = {(uint64_t)cq, (uint64_t)d->ow, (uint64_t)d->oh, (uint64_t)d->on};
+        const uint64_t strides[3] = {(uint64_t)d->osw * 2, (uint64_t)d->osh * 2, (uint64_t)d->osn * 2};
+        const uint32_t box[4] = {(uint32_t)p.box_ch, (uint32_t)p.wt, (uint32_t)p.box_h, (uint32_t)p.box_n};
+        int rc = b2_encode_tmap_bf16(&p.tmO[q], base, 4, dims, strides, box, p.box_ch == 32 ? 2 : 0);
+        if (rc != B2SEG_OK) { p.tma_out = 0; break; }  // e.g. a stride that TMA cannot express: direct stores
+      }
+    }
+  }
   {  // persistent grid: two CTAs per SM (96 KB of shared memory and <= 256 TMEM columns each),
      // a multiple of the column-tile count so that a CTA keeps one column tile
     const int ntiles = d->ngemm / bn;
@@ -448,6 +618,12 @@ extern "C" int b2seg_tapgemm_create(const b2seg_tapgemm_desc* d, b2seg_op** out)
     if (groups < 1) groups = 1;
     op->grid = dim3(groups * ntiles, 1, 1);
   }
+#ifdef TG_TRACE_ENABLE
+  if (const char* tr = getenv("B2SEG_TG_TRACE")) {
+    if (tr[0] && cudaMalloc(&p.trace, 64 * 8 * 8) == cudaSuccess) cudaMemset(p.trace, 0, 64 * 8 * 8);
+    else p.trace = nullptr;
+  }
+#endif
   int rc;
   if (bn == 128) rc = set_smem_attr<128, 3>();
   else if (bn == 64) rc = set_smem_attr<64, 4>();
