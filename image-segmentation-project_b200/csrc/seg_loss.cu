@@ -68,8 +68,8 @@ __device__ __forceinline__ PixelTerms pixel_terms(float x, float t) {
     if (SOFT) {
       r.one_m_pt = 1.0f - ex2_approx(r.bce * -1.44269504f);
     } else {
-      const float omp = x >= 0.0f ? small : inv;  // 1 - p
-      r.one_m_pt = t == 1.0f ? omp : r.p;
+      // 1 - pt = sigmoid(-z) with z = x for t = 1 and -x for t = 0: min(p, 1-p) when z >= 0
+      r.one_m_pt = ((x >= 0.0f) == (t == 1.0f)) ? small : inv;
     }
   } else {
     r.one_m_pt = 0.0f;
@@ -79,6 +79,14 @@ __device__ __forceinline__ PixelTerms pixel_terms(float x, float t) {
 __device__ __forceinline__ bool is_hard4(const float4& t) {
   return (t.x == 0.0f || t.x == 1.0f) && (t.y == 0.0f || t.y == 1.0f) &&
          (t.z == 0.0f || t.z == 1.0f) && (t.w == 0.0f || t.w == 1.0f);
+}
+// Eight targets are all hard iff sum(t^2 - t) == 0: every term is <= 0 on [0, 1] and zero only at 0 and 1
+// (exactly, in floating point: t*t - t rounds to 0 only for t in {0, 1}).  8 FFMA + 7 FADD instead of 16
+// compares and their predicate logic -- the focal forward pass is issue bound, every slot per pixel counts.
+__device__ __forceinline__ bool is_hard8(const float4& a, const float4& b) {
+  const float s = ((fmaf(a.x, a.x, -a.x) + fmaf(a.y, a.y, -a.y)) + (fmaf(a.z, a.z, -a.z) + fmaf(a.w, a.w, -a.w))) +
+                  ((fmaf(b.x, b.x, -b.x) + fmaf(b.y, b.y, -b.y)) + (fmaf(b.z, b.z, -b.z) + fmaf(b.w, b.w, -b.w)));
+  return s == 0.0f;
 }
 
 __device__ __forceinline__ float pow_pos(float base, float g) {
@@ -110,7 +118,8 @@ __device__ __forceinline__ float explog_df(float om, float g) {
 }
 
 // MODE selects what accumulator 5 carries: 0 nothing, 1 the focal term, 2 the exp-log term.
-template <int MODE, bool HAS_WMAP, bool SOFT = true>
+// G2: 1 = gamma is 2 (compile time), 0 = it is not, -1 = decided per call from gamma_is_two.
+template <int MODE, bool HAS_WMAP, bool SOFT = true, int G2 = -1>
 __device__ __forceinline__ void accumulate(float (&acc)[kAcc], float x, float t, float w,
                                            float gamma, bool gamma_is_two) {
   constexpr bool NEED_FOCAL = MODE == 1;
@@ -122,7 +131,8 @@ __device__ __forceinline__ void accumulate(float (&acc)[kAcc], float x, float t,
   acc[3] += bce_w;
   acc[4] = fmaf(q.bce, t, acc[4]);
   if (NEED_FOCAL) {
-    const float m = gamma_is_two ? q.one_m_pt * q.one_m_pt : pow_pos(q.one_m_pt, gamma);
+    const bool sq = G2 < 0 ? gamma_is_two : G2 == 1;
+    const float m = sq ? q.one_m_pt * q.one_m_pt : pow_pos(q.one_m_pt, gamma);
     acc[5] = fmaf(m, q.bce, acc[5]);
   }
   if (MODE == 2) acc[5] += explog_f(explog_om(q.p, t), gamma);
@@ -291,13 +301,13 @@ __device__ void finish_loss(const b2seg_loss_spec& s, const double* tot, double 
 }
 
 // ---- forward kernel -----------------------------------------------------------
-template <int NEED_FOCAL, bool HAS_WMAP, bool SOFT>
+template <int NEED_FOCAL, bool HAS_WMAP, bool SOFT, int G2 = -1>
 __device__ __forceinline__ void accumulate4(float (&acc)[kAcc], const float4& x, const float4& t,
                                             const float4& w, float gamma, bool g2) {
-  accumulate<NEED_FOCAL, HAS_WMAP, SOFT>(acc, x.x, t.x, w.x, gamma, g2);
-  accumulate<NEED_FOCAL, HAS_WMAP, SOFT>(acc, x.y, t.y, w.y, gamma, g2);
-  accumulate<NEED_FOCAL, HAS_WMAP, SOFT>(acc, x.z, t.z, w.z, gamma, g2);
-  accumulate<NEED_FOCAL, HAS_WMAP, SOFT>(acc, x.w, t.w, w.w, gamma, g2);
+  accumulate<NEED_FOCAL, HAS_WMAP, SOFT, G2>(acc, x.x, t.x, w.x, gamma, g2);
+  accumulate<NEED_FOCAL, HAS_WMAP, SOFT, G2>(acc, x.y, t.y, w.y, gamma, g2);
+  accumulate<NEED_FOCAL, HAS_WMAP, SOFT, G2>(acc, x.z, t.z, w.z, gamma, g2);
+  accumulate<NEED_FOCAL, HAS_WMAP, SOFT, G2>(acc, x.w, t.w, w.w, gamma, g2);
 }
 
 template <int NEED_FOCAL, bool HAS_WMAP, bool VEC4>
@@ -328,9 +338,14 @@ __global__ void __launch_bounds__(kThreads)
         wa = ldg_stream_f4(w4 + i);
         wb = ldg_stream_f4(w4 + i + nthreads);
       }
-      if (NEED_FOCAL == 1 && is_hard4(ta) && is_hard4(tb)) {
-        accumulate4<NEED_FOCAL, HAS_WMAP, false>(acc, xa, ta, wa, gamma, g2);
-        accumulate4<NEED_FOCAL, HAS_WMAP, false>(acc, xb, tb, wb, gamma, g2);
+      if (NEED_FOCAL == 1 && is_hard8(ta, tb)) {
+        if (g2) {  // the factory default (losses.py:68): (1 - pt)^2 is one multiply
+          accumulate4<NEED_FOCAL, HAS_WMAP, false, 1>(acc, xa, ta, wa, gamma, true);
+          accumulate4<NEED_FOCAL, HAS_WMAP, false, 1>(acc, xb, tb, wb, gamma, true);
+        } else {
+          accumulate4<NEED_FOCAL, HAS_WMAP, false, 0>(acc, xa, ta, wa, gamma, false);
+          accumulate4<NEED_FOCAL, HAS_WMAP, false, 0>(acc, xb, tb, wb, gamma, false);
+        }
       } else {
         accumulate4<NEED_FOCAL, HAS_WMAP, true>(acc, xa, ta, wa, gamma, g2);
         accumulate4<NEED_FOCAL, HAS_WMAP, true>(acc, xb, tb, wb, gamma, g2);
@@ -427,7 +442,7 @@ __device__ __forceinline__ void seg_loss_bwd_body(const float* __restrict__ x, c
         wb = ldg_stream_f4(w4 + i + nthreads);
       }
       float4 ga, gb;
-      if (NEED_FOCAL == 1 && is_hard4(ta) && is_hard4(tb)) {
+      if (NEED_FOCAL == 1 && is_hard8(ta, tb)) {
         ga = pixel_grad4<NEED_FOCAL, HAS_WMAP, false>(xa, ta, wa, c);
         gb = pixel_grad4<NEED_FOCAL, HAS_WMAP, false>(xb, tb, wb, c);
       } else {
