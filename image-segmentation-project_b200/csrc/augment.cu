@@ -135,6 +135,47 @@ __global__ void __launch_bounds__(256)
   __stcs(reinterpret_cast<uint4*>(dst + plane_off + drow * h + dcol), v);
 }
 
+// Same family on 64 (rows) x 128 (columns) byte tiles: a warp reads 128 contiguous bytes of a source row
+// (full lines instead of 64-byte halves) and every thread has eight 32-bit loads in flight instead of four.
+__global__ void __launch_bounds__(256)
+    transpose64x128_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int h, int w, int mode) {
+  __shared__ uint32_t T[128][17];
+  const int t = threadIdx.x;
+  const size_t plane_off = (size_t)blockIdx.z * h * w;
+  const int r0 = blockIdx.y * 64, c0 = blockIdx.x * 128;  // source tile origin
+  {
+    const int l = t & 31, g = t >> 5;
+    uint32_t a[2][4];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const uint8_t* s = src + plane_off + (size_t)(r0 + 4 * (g + 8 * u)) * w + c0 + 4 * l;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) a[u][k] = __ldcs(reinterpret_cast<const uint32_t*>(s + k * (size_t)w));
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const uint32_t t0 = __byte_perm(a[u][0], a[u][1], 0x5140), t1 = __byte_perm(a[u][2], a[u][3], 0x5140);
+      const uint32_t t2 = __byte_perm(a[u][0], a[u][1], 0x7362), t3 = __byte_perm(a[u][2], a[u][3], 0x7362);
+      T[4 * l + 0][g + 8 * u] = __byte_perm(t0, t1, 0x5410);  // source column 4l+0, rows 4g'..4g'+3
+      T[4 * l + 1][g + 8 * u] = __byte_perm(t0, t1, 0x7632);
+      T[4 * l + 2][g + 8 * u] = __byte_perm(t2, t3, 0x5410);
+      T[4 * l + 3][g + 8 * u] = __byte_perm(t2, t3, 0x7632);
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int u = 0; u < 2; ++u) {
+    const int e = t + 256 * u;
+    const int c = e >> 2, q = e & 3;  // transposed-tile row (= source column), 16-byte quarter
+    uint4 v = make_uint4(T[c][4 * q], T[c][4 * q + 1], T[c][4 * q + 2], T[c][4 * q + 3]);
+    size_t drow, dcol;  // destination is [w][h]
+    if (mode == 5) { drow = c0 + c; dcol = r0 + 16 * q; }
+    else if (mode == 3) { drow = w - 1 - (c0 + c); dcol = r0 + 16 * q; }
+    else { drow = c0 + c; dcol = h - r0 - 16 * q - 16; v = rev16(v); }
+    __stcs(reinterpret_cast<uint4*>(dst + plane_off + drow * h + dcol), v);
+  }
+}
+
 // ---- cv2 border rule (borderInterpolate) ------------------------------------------
 __device__ __forceinline__ int border_index(int p, int len, int border) {
   if ((unsigned)p < (unsigned)len) return p;
@@ -471,6 +512,12 @@ extern "C" int b2seg_aug_permute_u8(const uint8_t* src, uint8_t* dst, int planes
     else
       flip16_kernel<unsigned long long><<<blocks, 256, 0, (cudaStream_t)stream>>>(
           reinterpret_cast<const uint4*>(src), reinterpret_cast<uint4*>(dst), h, w / 16, total, km);
+    B2_CHECK_CUDA(cudaGetLastError());
+    return B2SEG_OK;
+  }
+  if (aligned && swap && w % 128 == 0 && h % 64 == 0) {
+    dim3 grid128(w / 128, h / 64, planes);
+    transpose64x128_kernel<<<grid128, 256, 0, (cudaStream_t)stream>>>(src, dst, h, w, km);
     B2_CHECK_CUDA(cudaGetLastError());
     return B2SEG_OK;
   }

@@ -14,7 +14,7 @@ def _img(rng, h, w):
     return cv2.GaussianBlur(rng.integers(0, 256, (h, w), dtype=np.uint8), (5, 5), 1.5)
 
 
-@pytest.mark.parametrize("h,w", [(1, 1), (5, 37), (64, 64), (97, 131), (256, 256), (1024, 1024)])
+@pytest.mark.parametrize("h,w", [(1, 1), (5, 37), (64, 64), (97, 131), (256, 256), (192, 384), (128, 64), (1024, 1024)])
 def test_permutations_bit_exact(cuda, h, w):
     from b2seg import augment
     rng = np.random.default_rng(h * 1000 + w)
