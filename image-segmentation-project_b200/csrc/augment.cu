@@ -429,11 +429,11 @@ __global__ void __launch_bounds__(256)
       }
       int out = v00;
       if (lin) {
-        // cv2 BilinearTab_i: (32-fy)(32-fx)*32 etc., sum 32768; FixedPtCast<15>
-        const int w00 = (32 - fy[e]) * (32 - fx[e]) * 32, w01 = (32 - fy[e]) * fx[e] * 32;
-        const int w10 = fy[e] * (32 - fx[e]) * 32, w11 = fy[e] * fx[e] * 32;
-        out = (v00 * w00 + v01 * w01 + v10 * w10 + v11 * w11 + (1 << 14)) >> 15;
-        out = max(0, min(255, out));
+        // cv2 BilinearTab_i weights are (32-fy)(32-fx)*32 etc. (sum 32768) with FixedPtCast<15>:
+        //   (sum v*w + 2^14) >> 15  ==  ((32-fy)*top + fy*bot + 2^9) >> 10   exactly (the sum is 32 * (...)),
+        // a convex combination of bytes, so no clamp is needed.
+        const int top = v00 * (32 - fx[e]) + v01 * fx[e], bot = v10 * (32 - fx[e]) + v11 * fx[e];
+        out = ((32 - fy[e]) * top + fy[e] * bot + 512) >> 10;
       }
       packed |= (uint32_t)out << (8 * e);
     }
