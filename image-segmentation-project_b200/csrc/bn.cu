@@ -110,19 +110,21 @@ __global__ void __launch_bounds__(kEwThreads) bn_apply_kernel(const EwArgs a) {
       ch.rf = ld_f8(rbnp + C + c0);
     }
     long long p = (long long)blockIdx.x * ppb + threadIdx.x / cv;
-    // two pixels in flight per thread: all loads of a pair are issued before the first store
-    for (; p + pstep < P; p += 2 * pstep) {
-      const long long q = p + pstep;
-      const uint4 y0 = bn_ld_raw8(y + p * ldy + c0), y1 = bn_ld_raw8(y + q * ldy + c0);
-      uint4 r0 = make_uint4(0, 0, 0, 0), r1 = r0;
-      if (res) {
-        r0 = bn_ld_raw8(res + p * ldr + c0);
-        r1 = bn_ld_raw8(res + q * ldr + c0);
+    // four pixels in flight per thread: all loads of a group are issued before the first store
+    constexpr int NB = 4;
+    for (; p + (NB - 1) * pstep < P; p += NB * pstep) {
+      uint4 yv[NB], rv[NB];
+#pragma unroll
+      for (int b = 0; b < NB; ++b) {
+        yv[b] = bn_ld_raw8(y + (p + b * pstep) * ldy + c0);
+        rv[b] = make_uint4(0, 0, 0, 0);
+        if (res) rv[b] = bn_ld_raw8(res + (p + b * pstep) * ldr + c0);
       }
-      st_bf8(out + p * ldo + c0, bn_apply_one(y0, r0, res != nullptr, ch, rbnp != nullptr, relu));
-      st_bf8(out + q * ldo + c0, bn_apply_one(y1, r1, res != nullptr, ch, rbnp != nullptr, relu));
+#pragma unroll
+      for (int b = 0; b < NB; ++b)
+        st_bf8(out + (p + b * pstep) * ldo + c0, bn_apply_one(yv[b], rv[b], res != nullptr, ch, rbnp != nullptr, relu));
     }
-    if (p < P) {
+    for (; p < P; p += pstep) {
       const uint4 y0 = bn_ld_raw8(y + p * ldy + c0);
       uint4 r0 = make_uint4(0, 0, 0, 0);
       if (res) r0 = bn_ld_raw8(res + p * ldr + c0);
@@ -218,16 +220,17 @@ __global__ void __launch_bounds__(kEwThreads) bn_bwd_reduce_kernel(const EwArgs 
     sc = ld_f8(s.bnp + c0t);
     sf = ld_f8(s.bnp + s.C + c0t);
   }
-  ew_channel_reduce<2>(0, a.i[0], s.C, (float*)a.p[5], red,
-                       [&](long long p, int c0, float (&acc)[2][8]) {
-                         F8 dz, y;
-                         bn_bwd_dz(s, sc, sf, bn_bwd_fetch(s, p, c0), dz, y);
+  ew_channel_reduce_batched<2, 4>(
+      0, a.i[0], s.C, (float*)a.p[5], red, [&](long long p, int c0) { return bn_bwd_fetch(s, p, c0); },
+      [&](const BnBwdRaw& r, int, float (&acc)[2][8]) {
+        F8 dz, y;
+        bn_bwd_dz(s, sc, sf, r, dz, y);
 #pragma unroll
-                         for (int j = 0; j < 8; ++j) {
-                           acc[0][j] += dz.v[j];
-                           acc[1][j] = fmaf(dz.v[j], y.v[j], acc[1][j]);
-                         }
-                       });
+        for (int j = 0; j < 8; ++j) {
+          acc[0][j] += dz.v[j];
+          acc[1][j] = fmaf(dz.v[j], y.v[j], acc[1][j]);
+        }
+      });
 }
 
 __global__ void __launch_bounds__(1024) bn_bwd_finalize_kernel(const EwArgs a) {
@@ -954,7 +957,7 @@ int ew_plan_bn(const b2seg_ew_desc* d, EwPlan* pl) {
                  "bn_bwd: leading dimensions / pointers must be 16-byte aligned");
       if (d->kind == B2SEG_EW_BN_BWD_REDUCE) {
         pl->fn = launch_bn_bwd_reduce;
-        pl->grid = dim3(ew_rows(i[0], (int)i[1]));
+        pl->grid = dim3(ew_rows(i[0], (int)i[1], kBnBwdReduceBlocksPerSm));
         pl->block = dim3(kEwThreads);
         pl->smem = (size_t)2 * ew_pl((int)i[1]) * i[1] * sizeof(float);
       } else {

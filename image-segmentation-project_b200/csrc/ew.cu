@@ -68,7 +68,9 @@ extern "C" int b2seg_ew_create(const b2seg_ew_desc* d, b2seg_op** out) {
 
 extern "C" int b2seg_ew_partial_rows(int kind, int64_t P, int C) {
   switch (kind) {
-    case B2SEG_EW_BN_BWD_REDUCE: case B2SEG_EW_COLSUM:
+    case B2SEG_EW_BN_BWD_REDUCE:
+      return (C >= 8 && C % 8 == 0 && P >= 1) ? ew_rows(P, C, kBnBwdReduceBlocksPerSm) : 0;
+    case B2SEG_EW_COLSUM:
       return (C >= 8 && C % 8 == 0 && P >= 1) ? ew_rows(P, C) : 0;
     case B2SEG_EW_DOT1_FWD: case B2SEG_EW_DOT1_BWD: case B2SEG_EW_GATE_BWD:
       return (C >= 8 && C % 8 == 0 && P >= 1) ? ew_dot_rows(P, C) : 0;

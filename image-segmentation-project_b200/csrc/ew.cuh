@@ -30,19 +30,21 @@ int ew_plan_attn(const b2seg_ew_desc* d, EwPlan* plan);
 int ew_plan_se(const b2seg_ew_desc* d, EwPlan* plan);
 
 constexpr int kEwThreads = 256;
+// bn_bwd_reduce keeps four pixels' operands in registers (119 registers): two resident blocks per SM
+constexpr int kBnBwdReduceBlocksPerSm = 2;
 
 static inline int ew_pl(int C) {  // pixel lanes of a 256-thread block whose threads own 8 channels
   const int cv = C / 8;
   const int pl = kEwThreads / (cv > 0 ? cv : 1);
   return pl < 1 ? 1 : pl;
 }
-static inline int ew_rows(long long P, int C) {
+static inline int ew_rows(long long P, int C, int blocks_per_sm = 3) {
   const long long per = (long long)ew_pl(C) * 8;
   long long r = (P + per - 1) / per;
   if (r < 1) r = 1;
   // one block per partial row: at most 3 resident 256-thread blocks per SM (76-101 registers),
   // so more rows than 3 x SMs would run as a second, mostly empty wave
-  long long cap = 3ll * b2_num_sms();
+  long long cap = (long long)blocks_per_sm * b2_num_sms();
   if (cap > B2SEG_EW_MAX_PARTIAL_ROWS) cap = B2SEG_EW_MAX_PARTIAL_ROWS;
   if (r > cap) r = cap;
   return (int)r;
@@ -206,6 +208,47 @@ __device__ __forceinline__ void ew_rows_reduce(const float* partial, int rows, l
 // Block-level per-channel reduction.  Thread t owns channel vector t % cv and pixel lane
 // t / cv; `body(p, c0, acc)` adds pixel p's contribution for channels [c0, c0+8) into
 // acc[NACC][8].  Row `blockIdx.x` of `partial` ([gridDim.x][NACC][C]) receives the block sums.
+// Batched form: `fetch(p, c0)` only loads (returns the raw operands of one pixel), `consume(raw, c0, acc)`
+// does the arithmetic.  NB pixels are fetched before the first is consumed, so a thread keeps NB x (32-64) bytes
+// in flight: with one pixel per iteration the BatchNorm-backward reduce had ~24 KB in flight per SM and ran at
+// 3.6-4.1 TB/s -- Little's law, not HBM.
+template <int NACC, int NB, class Fetch, class Consume>
+__device__ __forceinline__ void ew_channel_reduce_batched(long long P0, long long P1, int C, float* partial,
+                                                          float* red /* smem NACC*pl*C */, Fetch fetch,
+                                                          Consume consume) {
+  const int cv = C >> 3;
+  const int pl = blockDim.x / cv > 0 ? blockDim.x / cv : 1;
+  const int lc = threadIdx.x % cv, lp = threadIdx.x / cv;
+  float acc[NACC][8];
+#pragma unroll
+  for (int k = 0; k < NACC; ++k)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[k][j] = 0.0f;
+  if (lp < pl) {
+    const long long step = (long long)gridDim.x * pl;
+    long long p = P0 + (long long)blockIdx.x * pl + lp;
+    for (; p + (NB - 1) * step < P1; p += NB * step) {
+      decltype(fetch(p, 0)) raw[NB];
+#pragma unroll
+      for (int b = 0; b < NB; ++b) raw[b] = fetch(p + b * step, lc * 8);
+#pragma unroll
+      for (int b = 0; b < NB; ++b) consume(raw[b], lc * 8, acc);
+    }
+    for (; p < P1; p += step) consume(fetch(p, lc * 8), lc * 8, acc);
+#pragma unroll
+    for (int k = 0; k < NACC; ++k)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) red[((size_t)k * pl + lp) * C + lc * 8 + j] = acc[k][j];
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < NACC * C; idx += blockDim.x) {
+    const int k = idx / C, c = idx % C;
+    float s = 0.0f;
+    for (int l = 0; l < pl; ++l) s += red[((size_t)k * pl + l) * C + c];
+    partial[((size_t)blockIdx.x * NACC + k) * C + c] = s;
+  }
+}
+
 template <int NACC, class Body>
 __device__ __forceinline__ void ew_channel_reduce(long long P0, long long P1, int C, float* partial,
                                                   float* red /* smem NACC*pl*C */, Body body) {
