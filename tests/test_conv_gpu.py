@@ -173,3 +173,59 @@ def test_seq_replays_ops(cuda):
     ref = F.conv2d(F.conv2d(x.float().permute(0, 3, 1, 2), w1.float().reshape(3, 3, 64, 64).permute(2, 3, 0, 1), None, 1, 1)
                    .to(torch.bfloat16).float(), w1.float().reshape(3, 3, 64, 64).permute(2, 3, 0, 1), None, 1, 1)
     _close(y2.float().permute(0, 3, 1, 2).cpu(), ref.cpu(), "seq")
+
+
+# ---- round 2: the TMA-store / reduce-add epilogue and the second MMA issuer against the plain paths ----
+VARIANT_CASES = [
+    # n, h, w, cin, cout, k, stride
+    (8, 64, 64, 64, 64, 3, 1),     # resident weights, two issuers, TMA epilogue
+    (2, 40, 24, 96, 32, 3, 1),     # ragged tiles (TMA clips), partial last K chunk, N = 32
+    (4, 16, 16, 256, 256, 3, 1),   # streamed weights (one issuer), N = 128
+    (2, 32, 32, 64, 32, 1, 1),     # tapgemm: 1x1, N = 32 (register statistics)
+    (2, 16, 16, 128, 64, 1, 1),    # tapgemm: N = 64 (single staging slot)
+]
+
+
+@pytest.mark.parametrize("n,h,w,cin,cout,k,stride", VARIANT_CASES)
+def test_epilogue_and_issuer_variants_agree(cuda, monkeypatch, n, h, w, cin, cout, k, stride):
+    """B2SEG_HALO_TMA_OUT / B2SEG_TG_TMA_OUT / B2SEG_HALO_ISSUERS are read when an op is created: the same
+    problem planned with the TMA epilogue + two issuers (default) and with direct stores + one issuer must give
+    bit-identical outputs and statistics; in accumulate mode the TMA reduce-add rounds the new term to bf16
+    before the L2 adds it (one extra rounding), so it is compared within bf16 resolution."""
+    from b2seg import convops as co
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(7 * n + h + cin + cout + k)
+    x = torch.randn(n, h, w, cin, generator=g).to(torch.bfloat16).to(dev)
+    dy = torch.randn(n, h // stride, w // stride, cout, generator=g).to(torch.bfloat16).to(dev)
+    wt = (torch.randn(cout, cin, k, k, generator=g) / (cin * k * k) ** 0.5).to(dev)
+    base = torch.randn(n, h, w, cin, generator=g).to(torch.bfloat16).to(dev)
+    ho, wo = h // stride, w // stride
+
+    def run(plain):
+        for name in ("B2SEG_HALO_TMA_OUT", "B2SEG_TG_TMA_OUT"):
+            if plain:
+                monkeypatch.setenv(name, "0")
+            else:
+                monkeypatch.delenv(name, raising=False)
+        if plain:
+            monkeypatch.setenv("B2SEG_HALO_ISSUERS", "1")
+        else:
+            monkeypatch.delenv("B2SEG_HALO_ISSUERS", raising=False)
+        y = torch.zeros(n, ho, wo, cout, dtype=torch.bfloat16, device=dev)
+        stats = torch.zeros(co.stat_rows(n, ho, wo), 2, cout, device=dev)
+        dx = torch.zeros(n, h, w, cin, dtype=torch.bfloat16, device=dev)
+        dxa = base.clone()
+        co.conv_fprop(co.View(x), co.pack_conv_fprop(wt), k, stride, co.View(y), stats=stats).run()
+        co.conv_dgrad(co.View(dy), co.pack_conv_dgrad(wt), k, stride, co.View(dx)).run()
+        co.conv_dgrad(co.View(dy), co.pack_conv_dgrad(wt), k, stride, co.View(dxa), accumulate=True).run()
+        torch.cuda.synchronize()
+        return y, stats.sum(0), dx, dxa
+
+    y0, s0, dx0, dxa0 = run(plain=True)
+    y1, s1, dx1, dxa1 = run(plain=False)
+    assert torch.equal(y0, y1)
+    assert torch.equal(dx0, dx1)
+    assert torch.allclose(s0, s1, rtol=1e-5, atol=1e-3)  # rows are dealt to CTA groups differently, sums agree
+    d = (dxa0.float() - dxa1.float()).abs()
+    tol = 2.0 ** -7 * dxa0.float().abs() + 2.0 ** -8 * (dxa0.float() - base.float()).abs() + 1e-6
+    assert not (d > tol).any(), float(d.max())
