@@ -23,6 +23,7 @@ Printed JSON (one line, rank 0):
   sustained    the same resident step repeated for >= 3 s (clocks sampled), so the roofline
                fraction is also quoted at the clocks the sustained peak was measured at
   c1_batch4    BASELINE config 1's real shape (batch 4 x 256^2) and the scripts' (4 x 128^2)
+  batch_sweep  the headline step at 128 and 256 images per step (N = 1 only)
   loss_hbm     loss forward / backward / metrics kernels at [64,1,1024,1024]: us, GB/s, frac of HBM peak
   dp_c5        config 5: 1024^2 tiles, global batch 64 split over the ranks, data parallel with the
                NCCL gradient all-reduce (at N = 1 the same step without a collective)
@@ -589,6 +590,16 @@ def run_b200(a):
     if extras and rank == 0:
         rec["loss_hbm"] = _loss_hbm(dev, peaks)
         rec["c1_batch4"] = {"256": _small_batch(a, dev, 4, 256), "128": _small_batch(a, dev, 4, 128)}
+        if world == 1:
+            # the same step at 128 and 256 images: the ~10 us of fixed cost per conv launch amortise with the batch
+            fpi = rec.get("roofline", {}).get("flops_per_step", 0.0) / max(1, a.batch)
+            sweep = {}
+            for b, st in ((128, 20), (256, 12)):
+                r = _small_batch(a, dev, b, a.size, steps=st)
+                if fpi and peaks.get("tensor"):
+                    r["whole_step_frac_of_peak"] = r["images_per_sec"] * fpi / (peaks["tensor"] * 1e12)
+                sweep[str(b)] = r
+            rec["batch_sweep"] = sweep
     if extras:
         if world > 1:
             dist.barrier()
