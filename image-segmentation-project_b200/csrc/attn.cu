@@ -340,7 +340,7 @@ int ew_plan_attn(const b2seg_ew_desc* d, EwPlan* pl) {
                      al16(p[2]) && al16(p[3]),
                  "gate_apply: bad arguments");
       pl->fn = launch_gate_apply;
-      pl->grid = dim3(ew_blocks(i[0] * (C / 8)));
+      pl->grid = dim3(ew_resident_blocks(gate_apply_kernel, i[0] * (C / 8)));
       return B2SEG_OK;
     case B2SEG_EW_GATE_BWD:
       B2_REQUIRE(p[0] && p[1] && p[2] && p[3] && p[4] && p[5] && p[6] && p[7] && i[2] % 8 == 0 &&

@@ -880,24 +880,6 @@ __global__ void __launch_bounds__(kEwThreads) fill_kernel(const EwArgs a) {
     B2_CHECK_CUDA(cudaGetLastError());                                                    \
     return B2SEG_OK;                                                                      \
   }
-// Grid of a grid-stride streaming kernel as ONE resident wave (occupancy API): with more blocks than fit,
-// the blocks run in several waves of a few items per thread each and the batched loads never get going
-// (bn_bwd_apply: 124 registers -> 2 blocks per SM, the old cap of 12 blocks per SM meant 6 waves).
-// B2SEG_EW_WAVE=0 restores the capped grid.
-template <typename K>
-static int ew_resident_blocks(K kernel, long long work_items) {
-  int per_sm = 0;  // queried per op creation (both kernels share one function type: no static cache)
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kEwThreads, 0) != cudaSuccess || per_sm < 1) {
-    cudaGetLastError();
-    per_sm = 2;
-  }
-  const char* e = getenv("B2SEG_EW_WAVE");
-  if (e && e[0] == '0') return ew_blocks(work_items);
-  long long b = (work_items + kEwThreads - 1) / kEwThreads;
-  const long long cap = (long long)per_sm * b2_num_sms();
-  if (b > cap) b = cap;
-  return (int)(b < 1 ? 1 : b);
-}
 EW_LAUNCHER(launch_bn_finalize, bn_finalize_kernel)
 EW_LAUNCHER(launch_bn_apply, bn_apply_kernel)
 EW_LAUNCHER(launch_bn_bwd_reduce, bn_bwd_reduce_kernel)

@@ -5,6 +5,7 @@
 // reductions are two-phase: each block writes one row of fp32 partials, a
 // finalize kernel sums the rows in fixed order (fp64) -> bit-reproducible.
 #pragma once
+#include <stdlib.h>
 #include "ops.cuh"
 
 struct EwArgs {
@@ -56,6 +57,26 @@ static inline int ew_blocks(long long work_items) {  // elementwise grid: 256 th
   if (b < 1) b = 1;
   return (int)b;
 }
+// Grid of a grid-stride streaming kernel as ONE resident wave (occupancy API): with more blocks than fit,
+// the blocks run in several waves of a few items per thread each and the batched loads never get going
+// (bn_bwd_apply: 124 registers -> 2 blocks per SM, the old cap of 12 blocks per SM meant 6 waves).
+// B2SEG_EW_WAVE=0 restores the capped grid.
+#ifdef __CUDACC__
+template <typename K>
+static inline int ew_resident_blocks(K kernel, long long work_items) {
+  int per_sm = 0;  // queried per op creation (both kernels share one function type: no static cache)
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kEwThreads, 0) != cudaSuccess || per_sm < 1) {
+    cudaGetLastError();
+    per_sm = 2;
+  }
+  const char* e = getenv("B2SEG_EW_WAVE");
+  if (e && e[0] == '0') return ew_blocks(work_items);
+  long long b = (work_items + kEwThreads - 1) / kEwThreads;
+  const long long cap = (long long)per_sm * b2_num_sms();
+  if (b > cap) b = cap;
+  return (int)(b < 1 ? 1 : b);
+}
+#endif
 // Number of row slices (gridDim.y) of a column-reduce finalize kernel: each (32 x 32)-thread
 // block then walks <= ~32 rows per thread (independent loads, one L2 round trip); block-partial
 // buffers have <= 592 rows, so these kernels are single-phase -- no ticket, no second fold.

@@ -349,7 +349,7 @@ int ew_plan_se(const b2seg_ew_desc* d, EwPlan* pl) {
     case B2SEG_EW_SE_SCALE:
       B2_REQUIRE(p[0] && p[1] && p[2] && i[3] % 8 == 0 && i[4] % 8 == 0, "se_scale: bad arguments");
       pl->fn = launch_se_scale;
-      pl->grid = dim3(ew_blocks((long long)N * HW * (C / 8)));
+      pl->grid = dim3(ew_resident_blocks(se_scale_kernel, (long long)N * HW * (C / 8)));
       return B2SEG_OK;
     case B2SEG_EW_SE_BWD_REDUCE:
       B2_REQUIRE(p[0] && p[1] && p[2] && i[3] % 8 == 0 && i[4] % 8 == 0, "se_bwd_reduce: bad arguments");
@@ -368,7 +368,7 @@ int ew_plan_se(const b2seg_ew_desc* d, EwPlan* pl) {
     case B2SEG_EW_SE_BWD_APPLY:
       B2_REQUIRE(p[0] && p[1] && p[2] && p[3] && i[3] % 8 == 0 && i[4] % 8 == 0, "se_bwd_apply: bad arguments");
       pl->fn = launch_se_bwd_apply;
-      pl->grid = dim3(ew_blocks((long long)N * HW * (C / 8)));
+      pl->grid = dim3(ew_resident_blocks(se_bwd_apply_kernel, (long long)N * HW * (C / 8)));
       return B2SEG_OK;
   }
   b2seg_set_error("ew_plan_se: kind %d not handled here", d->kind);

@@ -347,7 +347,8 @@ int ew_plan_stem(const b2seg_ew_desc* d, EwPlan* pl) {
       const bool fwd = d->kind == B2SEG_EW_MAXPOOL_FWD;
       pl->fn = fwd ? launch_maxpool_fwd : launch_maxpool_bwd;
       const long long px = fwd ? i[0] * (i[1] / 2) * (i[2] / 2) : i[0] * i[1] * i[2];
-      pl->grid = dim3(ew_blocks(px * (i[3] / 8)));
+      pl->grid = dim3(fwd ? ew_resident_blocks(maxpool_fwd_kernel, px * (i[3] / 8))
+                          : ew_resident_blocks(maxpool_bwd_kernel, px * (i[3] / 8)));
       pl->block = dim3(kEwThreads);
       return B2SEG_OK;
     }
