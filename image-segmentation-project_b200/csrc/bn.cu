@@ -364,16 +364,17 @@ constexpr int kBnT = 512;
 template <int NACC>
 __device__ __forceinline__ void bn_fold_rows(const float* partial, int rows, int C, double* sm_sum,
                                              double* sm_tmp /* blockDim doubles */) {
+  constexpr int U = 32;  // loads in flight per thread and step: the fold is L2-latency bound
   const int cols = NACC * C, T = blockDim.x, t = threadIdx.x;
   if (cols >= T) {
     for (int q = t; q < cols; q += T) {
       double acc = 0.0;
-      for (int r = 0; r < rows; r += 8) {
-        float v[8];
+      for (int r = 0; r < rows; r += U) {
+        float v[U];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) v[u] = r + u < rows ? __ldcg(partial + (size_t)(r + u) * cols + q) : 0.0f;
+        for (int u = 0; u < U; ++u) v[u] = r + u < rows ? __ldcg(partial + (size_t)(r + u) * cols + q) : 0.0f;
 #pragma unroll
-        for (int u = 0; u < 8; ++u) acc += (double)v[u];
+        for (int u = 0; u < U; ++u) acc += (double)v[u];
       }
       sm_sum[q] = acc;
     }
@@ -383,12 +384,12 @@ __device__ __forceinline__ void bn_fold_rows(const float* partial, int rows, int
   const int nl = T / cols, lane = t / cols, q = t - lane * cols;
   double acc = 0.0;
   if (lane < nl) {
-    for (int r = lane; r < rows; r += 8 * nl) {
-      float v[8];
+    for (int r = lane; r < rows; r += U * nl) {
+      float v[U];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) v[u] = r + u * nl < rows ? __ldcg(partial + (size_t)(r + u * nl) * cols + q) : 0.0f;
+      for (int u = 0; u < U; ++u) v[u] = r + u * nl < rows ? __ldcg(partial + (size_t)(r + u * nl) * cols + q) : 0.0f;
 #pragma unroll
-      for (int u = 0; u < 8; ++u) acc += (double)v[u];
+      for (int u = 0; u < U; ++u) acc += (double)v[u];
     }
     sm_tmp[t] = acc;
   }
