@@ -117,6 +117,7 @@ _SIGS = {
     "b2seg_seg_loss_finish": (C.c_int, [C.POINTER(LossSpec), _i64, _vp, _vp, _vp, _vp]),
     "b2seg_seg_loss_bwd": (C.c_int, [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp]),
     "b2seg_seg_metrics_from_probs": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _vp]),
+    "b2seg_seg_metrics_from_probs_noalloc": (C.c_int, [_vp, _vp, _i64, _vp, _vp]),
     "b2seg_loss_boundary_weight_map": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _i, C.POINTER(C.c_float), C.c_float, _vp]),
     "b2seg_loss_edt_workspace_bytes": (C.c_size_t, [_i, _i, _i]),
     "b2seg_loss_edt_f32": (C.c_int, [_vp, _vp, _i, _i, _i, _i, C.c_float, _vp, _vp]),

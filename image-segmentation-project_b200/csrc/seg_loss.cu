@@ -9,6 +9,9 @@
 // backward kernel is a second streaming pass (12 B/px).
 #include "common.cuh"
 
+#include <cstddef>
+#include <mutex>
+
 namespace {
 
 constexpr int kThreads = 256;
@@ -670,6 +673,68 @@ extern "C" int b2seg_seg_metrics_from_probs(const float* probs, const float* tar
   else
     seg_metrics_probs_kernel<false>
         <<<pick_blocks(n, 16, resident_blocks<seg_metrics_probs_kernel<false>>()), kThreads, 0, st>>>(probs, target, n, ws, stats);
+  B2_CHECK_CUDA(cudaGetLastError());
+  return B2SEG_OK;
+}
+
+// ---- allocation-free variant -------------------------------------------------------------------
+// b2seg_seg_metrics_from_probs with its reduction scratch in library-owned static device memory,
+// for callers that may not call cudaMalloc (code under graph capture, serving loops, harnesses
+// that forbid it).  No counterpart in the reference.
+//
+// g_noalloc_ws is one ReduceWs (75 792 B: a ticket plus kMaxBlocks x kAcc fp64 block partials) that
+// every GPU loading the library holds until exit.  In HOST code the name is only a stand-in for
+// the symbol: the device address comes from cudaGetSymbolAddress, looked up once per device with
+// that device current, and that pointer is what the kernel gets.  All calls on a device share the
+// array, so two calls that overlap on the GPU (different streams, no ordering) race on it.
+namespace {
+static __device__ __align__(256) unsigned char g_noalloc_ws[sizeof(ReduceWs)];
+
+constexpr int kNoallocMaxDevices = 64;
+ReduceWs* g_noalloc_ptr[kNoallocMaxDevices];  // device address of g_noalloc_ws, per device
+std::mutex g_noalloc_mu;
+
+// Device address of the static scratch on the CURRENT device (looked up on first use there).
+int noalloc_ws(ReduceWs** out) {
+  int dev = -1;
+  B2_CHECK_CUDA(cudaGetDevice(&dev));
+  B2_REQUIRE(dev >= 0 && dev < kNoallocMaxDevices, "seg_metrics_noalloc: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (!g_noalloc_ptr[dev]) {
+    void* ptr = nullptr;
+    B2_CHECK_CUDA(cudaGetSymbolAddress(&ptr, g_noalloc_ws));
+    B2_REQUIRE(ptr != nullptr, "seg_metrics_noalloc: cudaGetSymbolAddress returned a null address");
+    g_noalloc_ptr[dev] = (ReduceWs*)ptr;
+  }
+  *out = g_noalloc_ptr[dev];
+  return B2SEG_OK;
+}
+}  // namespace
+
+extern "C" int b2seg_seg_metrics_from_probs_noalloc(const float* probs, const float* target,
+                                                    int64_t n, double* stats, void* stream) {
+  B2_REQUIRE(probs && target && stats, "seg_metrics_noalloc: null argument");
+  B2_REQUIRE(n > 0, "seg_metrics_noalloc: n must be positive (got %lld)", (long long)n);
+  B2_REQUIRE(n <= (int64_t)B2SEG_NOALLOC_MAX_PIXELS,
+             "seg_metrics_noalloc: n = %lld is beyond the static-scratch entry point's maximum of %lld "
+             "pixels; use b2seg_seg_metrics_from_probs with a caller workspace",
+             (long long)n, (long long)B2SEG_NOALLOC_MAX_PIXELS);
+  ReduceWs* ws = nullptr;
+  const int rc = noalloc_ws(&ws);
+  if (rc != B2SEG_OK) return rc;
+  const bool vec = aligned16(probs) && aligned16(target);
+  cudaStream_t st = (cudaStream_t)stream;
+  // The array keeps whatever the previous call (possibly an aborted one) left: the arrival ticket
+  // must start at zero; the partial rows are overwritten before they are read.
+  B2_CHECK_CUDA(cudaMemsetAsync(ws, 0, offsetof(ReduceWs, partial), st));
+  int blocks;
+  if (vec) {
+    blocks = pick_blocks(n, 16, resident_blocks<seg_metrics_probs_kernel<true>>());
+    seg_metrics_probs_kernel<true><<<blocks, kThreads, 0, st>>>(probs, target, n, ws, stats);
+  } else {
+    blocks = pick_blocks(n, 16, resident_blocks<seg_metrics_probs_kernel<false>>());
+    seg_metrics_probs_kernel<false><<<blocks, kThreads, 0, st>>>(probs, target, n, ws, stats);
+  }
   B2_CHECK_CUDA(cudaGetLastError());
   return B2SEG_OK;
 }

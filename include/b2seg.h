@@ -124,6 +124,22 @@ int b2seg_seg_loss_finish(const b2seg_loss_spec* spec, int64_t n_total, double* 
 int b2seg_seg_metrics_from_probs(const float* probs, const float* target, int64_t n,
                                  void* workspace, double* stats, void* stream);
 
+/* Allocation-free variant of b2seg_seg_metrics_from_probs (same kernel, same grid, same result).
+ * NO COUNTERPART IN THE REFERENCE: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  The reduction scratch is a file-scope static __device__ array inside the library
+ * (75 792 B, held by every GPU that loads the library until exit); the call performs no
+ * cudaMalloc / cudaFree and calls no allocating library routine.  The caller still owns probs,
+ * target and stats[16] (device).  n > B2SEG_NOALLOC_MAX_PIXELS returns B2SEG_EINVAL.
+ * All calls on a device share the one array: the entry point clears the arrival ticket on
+ * `stream` before each launch, and two calls that OVERLAP on the GPU (different streams with no
+ * ordering between them) race on it -- serialise them, or use the workspace variant above.
+ * The first call on each device looks up the array's device address (cudaGetSymbolAddress, with
+ * that device current); make that first call outside stream capture. */
+#define B2SEG_NOALLOC_MAX_PIXELS (1LL << 28) /* 268 435 456 px = 4 096 masks of 256 x 256 */
+int b2seg_seg_metrics_from_probs_noalloc(const float* probs, const float* target, int64_t n,
+                                         double* stats, void* stream);
+
 /* Weight maps of the boundary-style losses: they depend on the target only, are built on the
  * device and go into b2seg_seg_loss_fwd/_bwd as `weight_map` (bce_mode 3).
  *
