@@ -14,6 +14,7 @@
 // Permutations: 16-byte chunk moves (flips) and register/shared-memory 64x64 byte-tile
 // transposes (rot90 / transpose); odd sizes take the scalar tile kernel.
 #include "common.cuh"
+#include <type_traits>
 
 namespace {
 
@@ -280,7 +281,7 @@ constexpr int FPITCH = FOOT + 8;  // bytes; multiple of 4 so footprint rows take
 // interpolation and constant -- image (bilinear) and mask (nearest) of ALL augmented copies of a
 // batch are one launch.
 __global__ void __launch_bounds__(256)
-    warp_u8_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, WarpArgs a,
+    warp_u8_v1_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, WarpArgs a,
                    int planes, int pz, int vec_ok, const b2seg_warp_item* __restrict__ items, int ppi,
                    long long map_stride) {
   __shared__ __align__(16) uint8_t foot[FOOT][FPITCH];
@@ -447,32 +448,355 @@ __global__ void __launch_bounds__(256)
   }
 }
 
-int launch_warp(const uint8_t* src, uint8_t* dst, int planes, const WarpArgs& a, void* stream) {
-  const int tx = (a.w + TILE - 1) / TILE, ty = (a.h + TILE - 1) / TILE;
-  // enough CTAs for ~8 per SM; the rest of the planes are walked inside the CTA
-  int gz = (148 * 8 + tx * ty - 1) / (tx * ty);
-  gz = gz < 1 ? 1 : (gz > planes ? planes : gz);
-  const int pz = (planes + gz - 1) / gz;
-  gz = (planes + pz - 1) / pz;
-  const int vec_ok = (a.w % 4 == 0) && (reinterpret_cast<uintptr_t>(src) % 4 == 0) &&
-                     (reinterpret_cast<uintptr_t>(dst) % 4 == 0);
+// ---- warp kernel, second form (default) ---------------------------------------------------------
+// Same tiling and the same cv2 arithmetic as warp_u8_v1_kernel, rebuilt around the instruction count
+// (v1 issues 59 instructions per pixel and is issue bound at 9-11 % of the HBM roofline):
+//  * a destination tile is TW x TH = 64 x 16 or 32 x 32 pixels (template), a thread still owns 4 adjacent pixels;
+//  * every thread owns up to four fixed words of the footprint (word index -> row by ONE division per CTA,
+//    offsets kept in registers), loads them unpredicated, and fetches the NEXT plane's words before the
+//    current plane is gathered, so the global latency of plane p+1 hides behind the arithmetic of plane p;
+//  * bilinear planes keep a second copy of the footprint shifted by two bytes.  Whatever the parity
+//    of the source column, one aligned 32-bit shared-memory word then holds both horizontal
+//    neighbours: copy (lx >> 1) & 1, word lx >> 2, bytes (lx & 1) and (lx & 1) + 1.  The horizontal
+//    blend v0 * (32 - fx) + v1 * fx is ONE dp4a against a per-pixel weight word that is zero in the
+//    other two byte lanes (computed once per CTA: all planes of a call share the transform), so a
+//    pixel costs 2 LDS.32 + 2 IDP4A + 2 IMAD + shift + pack instead of 4 LDS.U8 + 9 integer ops.
+constexpr int NSLOT = 4;               // footprint words per thread: a staged footprint has <= 1024 words
+constexpr int FCOPY = FOOT * FPITCH;   // byte offset of the shifted copy
+
+// Footprint word with the border rule applied per byte (tiles that touch the image edge, or unaligned planes).
+__device__ __noinline__ uint32_t foot_word_border(const uint8_t* __restrict__ s, int h, int w, int gy, int gx,
+                                                  int border, int cval) {
+  const int yy = border_index(gy, h, border);
+  uint32_t word = 0;
+#pragma unroll
+  for (int b = 0; b < 4; ++b) {
+    const int xx = border_index(gx + b, w, border);
+    const uint32_t v = (xx < 0 || yy < 0) ? (uint32_t)cval : (uint32_t)s[(size_t)yy * w + xx];
+    word |= v << (8 * b);
+  }
+  return word;
+}
+
+__device__ __forceinline__ uint32_t foot_word(const uint8_t* __restrict__ s, int h, int w, int gy, int gx,
+                                              int border, int cval, int vec_ok) {
+  if (vec_ok && (unsigned)gy < (unsigned)h && gx >= 0 && gx + 3 < w)
+    return __ldg(reinterpret_cast<const uint32_t*>(s + (size_t)gy * w + gx));
+  return foot_word_border(s, h, w, gy, gx, border, cval);
+}
+
+template <int TW, int TH>
+__global__ void __launch_bounds__(256, 4)
+    warp_u8_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, WarpArgs a, int planes, int pz,
+                   int vec_ok, const b2seg_warp_item* __restrict__ items, int ppi, long long map_stride) {
+  static_assert(TW * TH == 1024 && TW % 4 == 0 && TW + TH <= 256, "256 threads x 4 pixels");
+  constexpr int TPR = TW / 4;  // threads per destination row
+  __shared__ __align__(16) uint8_t foot[2 * FCOPY];  // second half = first half shifted by two bytes (bilinear only)
+  if (items != nullptr) {
+    const int item = blockIdx.z / ppi, pl = blockIdx.z - item * ppi;
+    const b2seg_warp_item& it = items[item];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) a.m[i] = it.minv[i];
+    a.interp = it.interp[pl];
+    a.cval = it.cval[pl] & 255;
+    a.border = it.border;
+    if (a.map_x != nullptr) {
+      a.map_x += (size_t)item * map_stride;
+      a.map_y += (size_t)item * map_stride;
+    }
+  }
+  __shared__ int s_ad[TW], s_bd[TW], s_X0[TH], s_Y0[TH];
+  __shared__ int s_box[4];
+  const int h = a.h, w = a.w;
+  const int tid = threadIdx.x;
+  const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TH;
+  const int r = tid / TPR, xg = (tid % TPR) * 4;
+  const int y = y0 + r, x = x0 + xg;
+  const bool lin = a.interp == B2SEG_INTERP_LINEAR;
+  const bool affine = a.map_x == nullptr;
+
+  int sx[4], sy[4], fx[4], fy[4];
+  int bx0, by0, bx1, by1;  // inclusive box of the integer source coordinates
+  if (affine) {
+    if (tid < TW) {
+      const double xd = (double)(x0 + tid);
+      s_ad[tid] = __double2int_rn(__dmul_rn(__dmul_rn(a.m[0], xd), 1024.0));
+      s_bd[tid] = __double2int_rn(__dmul_rn(__dmul_rn(a.m[3], xd), 1024.0));
+    } else if (tid < TW + TH) {
+      const double yd = (double)(y0 + tid - TW);
+      const int round_delta = a.interp == B2SEG_INTERP_NEAREST ? 512 : 16;
+      s_X0[tid - TW] =
+          __double2int_rn(__dmul_rn(__dadd_rn(__dmul_rn(a.m[1], yd), a.m[2]), 1024.0)) + round_delta;
+      s_Y0[tid - TW] =
+          __double2int_rn(__dmul_rn(__dadd_rn(__dmul_rn(a.m[4], yd), a.m[5]), 1024.0)) + round_delta;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int e = 0; e < 4; ++e)
+      affine_from_tables(a.interp, s_ad[xg + e], s_bd[xg + e], s_X0[r], s_Y0[r], sx[e], sy[e], fx[e], fy[e]);
+    // corners of the valid part of the tile bound every pixel's coordinate (monotone in x and y)
+    const int cx1 = min(TW - 1, w - 1 - x0), cy1 = min(TH - 1, h - 1 - y0);
+    bx0 = by0 = INT_MAX; bx1 = by1 = INT_MIN;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const int cx = (c & 1) ? cx1 : 0, cy = (c & 2) ? cy1 : 0;
+      int qx, qy, q0, q1;
+      affine_from_tables(a.interp, s_ad[cx], s_bd[cx], s_X0[cy], s_Y0[cy], qx, qy, q0, q1);
+      bx0 = min(bx0, qx); bx1 = max(bx1, qx);
+      by0 = min(by0, qy); by1 = max(by1, qy);
+    }
+  } else {
+    int mnx = INT_MAX, mny = INT_MAX, mxx = INT_MIN, mxy = INT_MIN;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      if (x + e < w && y < h) {
+        src_coord(a, x + e, y, sx[e], sy[e], fx[e], fy[e]);
+        mnx = min(mnx, sx[e]); mxx = max(mxx, sx[e]);
+        mny = min(mny, sy[e]); mxy = max(mxy, sy[e]);
+      } else {
+        sx[e] = sy[e] = fx[e] = fy[e] = 0;
+      }
+    }
+    if (tid == 0) { s_box[0] = INT_MAX; s_box[1] = INT_MAX; s_box[2] = INT_MIN; s_box[3] = INT_MIN; }
+    __syncthreads();
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      mnx = min(mnx, __shfl_xor_sync(0xffffffffu, mnx, o));
+      mny = min(mny, __shfl_xor_sync(0xffffffffu, mny, o));
+      mxx = max(mxx, __shfl_xor_sync(0xffffffffu, mxx, o));
+      mxy = max(mxy, __shfl_xor_sync(0xffffffffu, mxy, o));
+    }
+    if ((tid & 31) == 0) {
+      atomicMin(&s_box[0], mnx); atomicMin(&s_box[1], mny);
+      atomicMax(&s_box[2], mxx); atomicMax(&s_box[3], mxy);
+    }
+    __syncthreads();
+    bx0 = s_box[0]; by0 = s_box[1]; bx1 = s_box[2]; by1 = s_box[3];
+  }
+  if (a.border == B2SEG_BORDER_CONSTANT) {
+    // anything at or beyond one pixel outside the image reads only the constant
+    bx0 = max(-2, min(w, bx0)); bx1 = max(-2, min(w, bx1));
+    by0 = max(-2, min(h, by0)); by1 = max(-2, min(h, by1));
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      sx[e] = max(-2, min(w, sx[e]));
+      sy[e] = max(-2, min(h, sy[e]));
+    }
+  }
+  const int bxa = bx0 & ~3;  // footprint columns start on a 4-byte boundary of the source row
+  const int bw = bx1 + (lin ? 1 : 0) - bxa + 1, bh = by1 + (lin ? 1 : 0) - by0 + 1;
+  const int bwords = (bw + 3) >> 2;
+  const int nwords = bh * bwords;
+  const bool staged = bx0 != INT_MAX && bw > 0 && bh > 0 && bwords * 4 <= FPITCH && bh <= FOOT && nwords <= 256 * NSLOT;
+  const bool valid_row = y < h;
+
+  const int p_begin = items ? (int)blockIdx.z : blockIdx.z * pz;
+  const int p_end = items ? p_begin + 1 : min(planes, p_begin + pz);
+  if (!staged) {  // footprint larger than the staging buffer (strong zoom-out): gather from global memory
+    if (!valid_row) return;
+    for (int plane = p_begin; plane < p_end; ++plane) {
+      const uint8_t* s = src + (size_t)plane * h * w;
+      uint8_t* d = dst + (size_t)plane * h * w;
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        if (x + e >= w) continue;
+        int out = fetch_global(s, h, w, sx[e], sy[e], a.border, a.cval);
+        if (lin) {
+          const int v01 = fetch_global(s, h, w, sx[e] + 1, sy[e], a.border, a.cval);
+          const int v10 = fetch_global(s, h, w, sx[e], sy[e] + 1, a.border, a.cval);
+          const int v11 = fetch_global(s, h, w, sx[e] + 1, sy[e] + 1, a.border, a.cval);
+          const int top = out * (32 - fx[e]) + v01 * fx[e], bot = v10 * (32 - fx[e]) + v11 * fx[e];
+          out = ((32 - fy[e]) * top + fy[e] * bot + 512) >> 10;
+        }
+        d[(size_t)y * w + x + e] = (uint8_t)out;
+      }
+    }
+    return;
+  }
+
+  // Per-pixel shared-memory byte offset and (bilinear) dp4a weight word; fixed for every plane.
+  uint32_t goff[4], wsel[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    int lx = sx[e] - bxa, ly = sy[e] - by0;
+    if (!valid_row || x + e >= w) lx = ly = 0;  // never stored; keep the address inside the array
+    if (lin) {
+      goff[e] = (uint32_t)(((lx >> 1) & 1) * FCOPY + ly * FPITCH + (lx >> 2) * 4);
+      wsel[e] = (uint32_t)((32 - fx[e]) | (fx[e] << 8)) << ((lx & 1) * 8);
+    } else {
+      goff[e] = (uint32_t)(ly * FPITCH + lx);
+      wsel[e] = 0;
+    }
+  }
+  const uint8_t* const f0 = foot;
+  auto gather_store = [&](uint8_t* __restrict__ d, auto lin_c) {
+    constexpr bool LIN = decltype(lin_c)::value;
+    if (!valid_row) return;
+    uint32_t packed = 0;
+    if (LIN) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const uint32_t wt = *reinterpret_cast<const uint32_t*>(f0 + goff[e]);
+        const uint32_t wb = *reinterpret_cast<const uint32_t*>(f0 + goff[e] + FPITCH);
+        // cv2 BilinearTab_i weights are (32-fy)(32-fx)*32 etc. (sum 32768) with FixedPtCast<15>:
+        //   (sum v*w + 2^14) >> 15  ==  ((32-fy)*top + fy*bot + 2^9) >> 10   exactly (the sum is 32 * (...)),
+        // a convex combination of bytes, so no clamp is needed.
+        const uint32_t top = __dp4a(wt, wsel[e], 0u), bot = __dp4a(wb, wsel[e], 0u);
+        const uint32_t out = ((32u - (uint32_t)fy[e]) * top + (uint32_t)fy[e] * bot + 512u) >> 10;
+        packed |= out << (8 * e);
+      }
+    } else {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) packed |= (uint32_t)f0[goff[e]] << (8 * e);
+    }
+    if (vec_ok && x + 3 < w) {
+      __stcs(reinterpret_cast<uint32_t*>(d + (size_t)y * w + x), packed);
+    } else {
+#pragma unroll
+      for (int e = 0; e < 4; ++e)
+        if (x + e < w) d[(size_t)y * w + x + e] = (uint8_t)(packed >> (8 * e));
+    }
+  };
+
+  // Footprint words of this thread: word i = tid + 256 j sits in footprint row i / bwords.  Slots past the end
+  // re-load slot 0's word and park it in a corner of the buffer that a <= 1024-word footprint never uses, so
+  // the per-plane loop carries no predicates.
+  uint32_t gsrc[NSLOT], sdst[NSLOT];
+  bool ok = vec_ok != 0;
+#pragma unroll
+  for (int j = 0; j < NSLOT; ++j) {
+    const int i = tid + 256 * j;
+    const int fr = i / bwords, fc = i - fr * bwords;
+    const int gy = by0 + fr, gx = bxa + 4 * fc;
+    if (i < nwords) {
+      // the +4 neighbour read of the last word of a row must stay inside the plane
+      ok = ok && (unsigned)gy < (unsigned)h && gx >= 0 && gx + 3 < w && (gx + 7 < w || gy + 1 < h);
+      gsrc[j] = (uint32_t)(gy * w + gx);
+      sdst[j] = (uint32_t)(fr * FPITCH + 4 * fc);
+    } else {
+      gsrc[j] = (uint32_t)(by0 * w + bxa);
+      sdst[j] = (uint32_t)((FOOT - 1) * FPITCH + FPITCH - 4);
+    }
+  }
+  const bool interior = __syncthreads_and(ok) != 0;  // also orders the coordinate tables before the first store
+  const int nslots = (nwords + 255) >> 8;            // 1..NSLOT, CTA-uniform
+
+  if (interior) {
+    auto run = [&](auto lin_c) {
+      constexpr bool LIN = decltype(lin_c)::value;
+      uint32_t wa[NSLOT], wn[NSLOT];
+      const uint8_t* s = src + (size_t)p_begin * h * w;
+#pragma unroll
+      for (int j = 0; j < NSLOT; ++j)
+        if (j < nslots) {
+          const uint32_t* g = reinterpret_cast<const uint32_t*>(s + gsrc[j]);
+          wa[j] = __ldg(g);
+          if (LIN) wn[j] = __ldg(g + 1);
+        }
+      for (int plane = p_begin; plane < p_end; ++plane) {
+        if (plane != p_begin) __syncthreads();  // previous plane's gathers are done
+#pragma unroll
+        for (int j = 0; j < NSLOT; ++j)
+          if (j < nslots) {
+            *reinterpret_cast<uint32_t*>(foot + sdst[j]) = wa[j];
+            if (LIN) *reinterpret_cast<uint32_t*>(foot + sdst[j] + FCOPY) = __funnelshift_r(wa[j], wn[j], 16);
+          }
+        if (plane + 1 < p_end) {  // next plane's words fly while this plane is gathered
+          s += (size_t)h * w;
+#pragma unroll
+          for (int j = 0; j < NSLOT; ++j)
+            if (j < nslots) {
+              const uint32_t* g = reinterpret_cast<const uint32_t*>(s + gsrc[j]);
+              wa[j] = __ldg(g);
+              if (LIN) wn[j] = __ldg(g + 1);
+            }
+        }
+        __syncthreads();
+        gather_store(dst + (size_t)plane * h * w, lin_c);
+      }
+    };
+    if (lin) run(std::true_type{}); else run(std::false_type{});
+    return;
+  }
+
+  // Tiles that touch the image edge (or planes without 4-byte alignment): border rule per byte, then the
+  // shifted copy from shared memory.
+  for (int plane = p_begin; plane < p_end; ++plane) {
+    const uint8_t* s = src + (size_t)plane * h * w;
+    if (plane != p_begin) __syncthreads();
+    for (int i = tid; i < nwords; i += 256) {
+      const int fr = i / bwords, fc = i - fr * bwords;
+      *reinterpret_cast<uint32_t*>(foot + fr * FPITCH + 4 * fc) =
+          foot_word(s, h, w, by0 + fr, bxa + 4 * fc, a.border, a.cval, vec_ok);
+    }
+    __syncthreads();
+    if (lin) {
+      for (int i = tid; i < nwords; i += 256) {
+        const int fr = i / bwords, fc = i - fr * bwords;
+        const uint32_t* p = reinterpret_cast<const uint32_t*>(foot + fr * FPITCH + 4 * fc);
+        const uint32_t nx = fc + 1 < bwords ? p[1] : 0u;
+        *reinterpret_cast<uint32_t*>(foot + FCOPY + fr * FPITCH + 4 * fc) = __funnelshift_r(p[0], nx, 16);
+      }
+      __syncthreads();
+    }
+    if (lin) gather_store(dst + (size_t)plane * h * w, std::true_type{});
+    else gather_store(dst + (size_t)plane * h * w, std::false_type{});
+  }
+}
+
+// B2SEG_WARP_KERNEL = 1: round-1/2 kernel (32 x 32 tiles, byte gathers); 2: second form on 32 x 32 tiles;
+// 3 (default): second form on 64 x 16 tiles.
+int warp_kernel_choice() {
+  static const int c = [] {
+    const char* e = getenv("B2SEG_WARP_KERNEL");
+    const int v = e ? atoi(e) : 3;
+    return v >= 1 && v <= 3 ? v : 3;
+  }();
+  return c;
+}
+
+int launch_warp_any(const uint8_t* src, uint8_t* dst, const WarpArgs& a, int planes, int pz, int gz, int vec_ok,
+                    const b2seg_warp_item* items, int ppi, long long map_stride, void* stream) {
+  const int choice = warp_kernel_choice();
+  const int tw = choice == 3 ? 64 : 32, th = choice == 3 ? 16 : 32;
+  const int tx = (a.w + tw - 1) / tw, ty = (a.h + th - 1) / th;
+  B2_REQUIRE(ty <= 65535 && gz <= 65535, "aug_warp: image too tall for the launch grid (%d rows)", a.h);
   dim3 grid(tx, ty, gz);
-  warp_u8_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, dst, a, planes, pz, vec_ok, nullptr, 1, 0);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (choice == 1)
+    warp_u8_v1_kernel<<<grid, 256, 0, st>>>(src, dst, a, planes, pz, vec_ok, items, ppi, map_stride);
+  else if (choice == 2)
+    warp_u8_kernel<32, 32><<<grid, 256, 0, st>>>(src, dst, a, planes, pz, vec_ok, items, ppi, map_stride);
+  else
+    warp_u8_kernel<64, 16><<<grid, 256, 0, st>>>(src, dst, a, planes, pz, vec_ok, items, ppi, map_stride);
   B2_CHECK_CUDA(cudaGetLastError());
   return B2SEG_OK;
 }
 
+int launch_warp(const uint8_t* src, uint8_t* dst, int planes, const WarpArgs& a, void* stream) {
+  // ~48 CTAs per SM over the call (short CTAs, no tail) as long as a CTA still walks >= 8 planes with one set
+  // of source coordinates; v1 keeps its original split (~8 CTAs per SM)
+  const int tiles = ((a.w + 31) / 32) * ((a.h + 31) / 32);
+  const int per_sm = warp_kernel_choice() == 1 ? 8 : 48;
+  int gz = (148 * per_sm + tiles - 1) / tiles;
+  gz = gz < 1 ? 1 : (gz > planes ? planes : gz);
+  int pz = (planes + gz - 1) / gz;
+  if (warp_kernel_choice() != 1 && pz < 8) {
+    for (int cand = 8; cand > pz; cand >>= 1)
+      if ((long long)tiles * ((planes + cand - 1) / cand) >= 148 * 8) { pz = cand; break; }
+  }
+  gz = (planes + pz - 1) / pz;
+  const int vec_ok = (a.w % 4 == 0) && (reinterpret_cast<uintptr_t>(src) % 4 == 0) &&
+                     (reinterpret_cast<uintptr_t>(dst) % 4 == 0);
+  return launch_warp_any(src, dst, a, planes, pz, gz, vec_ok, nullptr, 1, 0, stream);
+}
+
 int launch_warp_batch(const uint8_t* src, uint8_t* dst, int n_items, int ppi, WarpArgs a,
                       const b2seg_warp_item* items, long long map_stride, void* stream) {
-  const int tx = (a.w + TILE - 1) / TILE, ty = (a.h + TILE - 1) / TILE;
   const size_t plane_bytes = (size_t)a.h * a.w;
   const int vec_ok = (a.w % 4 == 0) && (plane_bytes % 4 == 0) && (reinterpret_cast<uintptr_t>(src) % 4 == 0) &&
                      (reinterpret_cast<uintptr_t>(dst) % 4 == 0);
-  dim3 grid(tx, ty, n_items * ppi);
-  warp_u8_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, dst, a, n_items * ppi, 1, vec_ok, items, ppi,
-                                                           map_stride);
-  B2_CHECK_CUDA(cudaGetLastError());
-  return B2SEG_OK;
+  return launch_warp_any(src, dst, a, n_items * ppi, 1, n_items * ppi, vec_ok, items, ppi, map_stride, stream);
 }
 
 }  // namespace

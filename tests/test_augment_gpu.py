@@ -78,6 +78,33 @@ def test_remap_matches_cv2(cuda, h, w):
                 assert np.array_equal(got, ref), (it, bt, np.abs(got.astype(int) - ref).max())
 
 
+@pytest.mark.parametrize("h,w,planes", [(512, 512, 40), (200, 328, 24), (1024, 1024, 12)])
+def test_warp_many_planes_large_rotations(cuda, h, w, planes):
+    """A CTA walks several planes with one set of source coordinates (the next plane's footprint is fetched while
+    the current one is gathered), and rotations up to 90 degrees give tall / wide footprints."""
+    cv2 = pytest.importorskip("cv2")
+    from b2seg import augment
+    rng = np.random.default_rng(planes)
+    host = rng.integers(0, 256, (planes, h, w), dtype=np.uint8)
+    d = torch.from_numpy(host).to(cuda)
+    for angle, scale in ((8.0, 1.02), (31.0, 0.97), (45.0, 1.05), (90.0, 1.0), (-63.0, 0.9)):
+        M = augment.affine_matrix(h, w, scale, (0.01, -0.02), angle, (2.5, -1.5))
+        Mn = np.array(M)
+        for it, cf in ((augment.LINEAR, cv2.INTER_LINEAR), (augment.NEAREST, cv2.INTER_NEAREST)):
+            for bt, cb in ((augment.REFLECT, cv2.BORDER_REFLECT), (augment.CONSTANT, cv2.BORDER_CONSTANT)):
+                got = augment.warp_affine(d, M, it, bt, 7).cpu().numpy()
+                for p in range(planes):
+                    ref = cv2.warpAffine(host[p], Mn, (w, h), flags=cf, borderMode=cb, borderValue=7)
+                    assert np.array_equal(got[p], ref), (angle, it, bt, p)
+    yy, xx = np.meshgrid(np.arange(h, dtype=np.float32), np.arange(w, dtype=np.float32), indexing="ij")
+    mx = (xx + 3.0 * np.sin(yy / 17.0)).astype(np.float32)
+    my = (yy + 3.0 * np.cos(xx / 13.0)).astype(np.float32)
+    got = augment.remap(d, torch.from_numpy(mx).to(cuda), torch.from_numpy(my).to(cuda)).cpu().numpy()
+    for p in range(planes):
+        ref = cv2.remap(host[p], mx, my, cv2.INTER_LINEAR, borderMode=cv2.BORDER_REFLECT)
+        assert np.array_equal(got[p], ref), p
+
+
 def test_errors(cuda):
     from b2seg import augment
     with pytest.raises(TypeError):

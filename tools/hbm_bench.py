@@ -37,6 +37,7 @@ def main():
     ap.add_argument("--n", type=int, default=64)
     ap.add_argument("--size", type=int, default=1024)
     ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--only", default="", help="'aug': skip the loss / metric kernels")
     a = ap.parse_args()
     from b2seg import lossfn, augment
     import losses
@@ -57,25 +58,26 @@ def main():
         out["kernels"][name] = {"us": round(ms * 1e3, 2), "bytes_per_px": bytes_px,
                                 "gbs": round(gbs, 1), "frac_of_peak": round(gbs / peak, 4)}
 
-    for name in ("combo", "dice", "bce", "focal", "tversky"):
-        crit = losses.get_loss_function({"loss_fn": name})
-        spec = crit._spec()
-        saved = {}
+    if a.only != "aug":
+        for name in ("combo", "dice", "bce", "focal", "tversky"):
+            crit = losses.get_loss_function({"loss_fn": name})
+            spec = crit._spec()
+            saved = {}
 
-        def fwd(i, spec=spec):
-            saved["r"] = lossfn.loss_forward(xs[i & 1], ts[i & 1], spec)
+            def fwd(i, spec=spec):
+                saved["r"] = lossfn.loss_forward(xs[i & 1], ts[i & 1], spec)
 
-        rec(f"seg_loss_fwd[{name}]", timed(fwd, a.iters), 8)
-        _, _, coef, sv = saved["r"]
+            rec(f"seg_loss_fwd[{name}]", timed(fwd, a.iters), 8)
+            _, _, coef, sv = saved["r"]
 
-        def bwd(i, coef=coef, sv=sv):
-            lossfn.loss_backward(sv, coef, None, shape)
+            def bwd(i, coef=coef, sv=sv):
+                lossfn.loss_backward(sv, coef, None, shape)
 
-        rec(f"seg_loss_bwd[{name}]", timed(bwd, a.iters), 12)
+            rec(f"seg_loss_bwd[{name}]", timed(bwd, a.iters), 12)
 
-    ps = [torch.sigmoid(x) for x in xs]
-    rec("seg_metrics_from_probs", timed(lambda i: lossfn.metrics_from_probs(ps[i & 1], ts[i & 1]), a.iters), 8)
-    del ps
+        ps = [torch.sigmoid(x) for x in xs]
+        rec("seg_metrics_from_probs", timed(lambda i: lossfn.metrics_from_probs(ps[i & 1], ts[i & 1]), a.iters), 8)
+        del ps
 
     # augmentation: image + mask planes, uint8
     planes = [torch.randint(0, 256, (2 * a.n, a.size, a.size), generator=g, dtype=torch.uint8).to(dev)
