@@ -8,9 +8,10 @@
 // / reflect / reflect101 borders).
 //
 // Warps: one CTA produces a 32x32 destination tile of several planes.  It computes the
-// source footprint of the tile, stages it (border rule already applied) in shared memory
-// with coalesced 32-bit loads and gathers from shared memory; each thread emits 4 adjacent
-// pixels as one 32-bit store.  Footprints that do not fit fall back to direct global gathers.
+// source footprint of the tile, stages it in shared memory (border rule already applied, next
+// planes prefetched in registers, bank-conflict-aware pitch) and gathers from shared memory with
+// one dp4a per pixel row; each thread emits 4 adjacent pixels as one 32-bit store.  Footprints
+// that do not fit fall back to direct global gathers.
 // Permutations: 16-byte chunk moves (flips) and register/shared-memory 64x64 byte-tile
 // transposes (rot90 / transpose); odd sizes take the scalar tile kernel.
 #include "common.cuh"
@@ -19,7 +20,6 @@
 namespace {
 
 constexpr int TILE = 32;
-constexpr int FOOT = 72;  // staged footprint is at most FOOT x FOOT source pixels
 
 // ---- exact permutations -----------------------------------------------------------
 // dst(i,j) = src(si,sj); for transposing modes the tile is staged through smem so
@@ -268,201 +268,41 @@ __device__ __forceinline__ void affine_from_tables(int interp, int adx, int bdx,
   sy = max(-32768, min(32767, sy));
 }
 
-constexpr int FPITCH = FOOT + 8;  // bytes; multiple of 4 so footprint rows take 32-bit stores
-
-// One CTA = one 32x32 destination tile of `pz` consecutive planes (all planes of a call share the
-// transform, so source coordinates are computed once and kept in registers).  Thread = 4
-// horizontally adjacent pixels -> one 32-bit store.  Affine coordinates come from four 32-entry
-// integer tables (the double-precision products are evaluated once per tile row / column, not per
-// pixel); the source footprint of an affine tile is the bounding box of its four corners.
+// ---- warp kernel ----------------------------------------------------------------------------------
+// One CTA = one TW x TH = 32 x 32 (or 64 x 16) destination tile of `pz` consecutive planes (all planes of a call
+// share the transform, so source coordinates, shared-memory addresses and blend weights are computed once and kept
+// in registers).  Thread = 4 horizontally adjacent pixels -> one 32-bit store.  Affine coordinates come from four
+// integer tables (the double-precision products are evaluated once per tile row / column, not per pixel); the
+// source footprint of an affine tile is the bounding box of its four corners.
 //
-// Table mode (`items` != NULL): blockIdx.z = item * ppi + plane; every item brings its own matrix
-// (or its own pair of maps, `map_stride` floats apart) and every plane of an item its own
-// interpolation and constant -- image (bilinear) and mask (nearest) of ALL augmented copies of a
-// batch are one launch.
-__global__ void __launch_bounds__(256)
-    warp_u8_v1_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, WarpArgs a,
-                   int planes, int pz, int vec_ok, const b2seg_warp_item* __restrict__ items, int ppi,
-                   long long map_stride) {
-  __shared__ __align__(16) uint8_t foot[FOOT][FPITCH];
-  if (items != nullptr) {
-    const int item = blockIdx.z / ppi, pl = blockIdx.z - item * ppi;
-    const b2seg_warp_item& it = items[item];
-#pragma unroll
-    for (int i = 0; i < 6; ++i) a.m[i] = it.minv[i];
-    a.interp = it.interp[pl];
-    a.cval = it.cval[pl] & 255;
-    a.border = it.border;
-    if (a.map_x != nullptr) {
-      a.map_x += (size_t)item * map_stride;
-      a.map_y += (size_t)item * map_stride;
-    }
-  }
-  __shared__ int s_ad[TILE], s_bd[TILE], s_X0[TILE], s_Y0[TILE];
-  __shared__ int s_box[4];
-  const int h = a.h, w = a.w;
-  const int tid = threadIdx.x;
-  const int x0 = blockIdx.x * TILE, y0 = blockIdx.y * TILE;
-  const int r = tid >> 3, xg = (tid & 7) * 4;
-  const int y = y0 + r, x = x0 + xg;
-  const bool lin = a.interp == B2SEG_INTERP_LINEAR;
-  const bool affine = a.map_x == nullptr;
-
-  int sx[4], sy[4], fx[4], fy[4];
-  int bx0, by0, bx1, by1;  // inclusive box of the integer source coordinates
-  if (affine) {
-    if (tid < TILE) {
-      const double xd = (double)(x0 + tid);
-      s_ad[tid] = __double2int_rn(__dmul_rn(__dmul_rn(a.m[0], xd), 1024.0));
-      s_bd[tid] = __double2int_rn(__dmul_rn(__dmul_rn(a.m[3], xd), 1024.0));
-    } else if (tid < 2 * TILE) {
-      const double yd = (double)(y0 + tid - TILE);
-      const int round_delta = a.interp == B2SEG_INTERP_NEAREST ? 512 : 16;
-      s_X0[tid - TILE] =
-          __double2int_rn(__dmul_rn(__dadd_rn(__dmul_rn(a.m[1], yd), a.m[2]), 1024.0)) + round_delta;
-      s_Y0[tid - TILE] =
-          __double2int_rn(__dmul_rn(__dadd_rn(__dmul_rn(a.m[4], yd), a.m[5]), 1024.0)) + round_delta;
-    }
-    __syncthreads();
-#pragma unroll
-    for (int e = 0; e < 4; ++e)
-      affine_from_tables(a.interp, s_ad[xg + e], s_bd[xg + e], s_X0[r], s_Y0[r], sx[e], sy[e], fx[e], fy[e]);
-    // corners of the valid part of the tile bound every pixel's coordinate (monotone in x and y)
-    const int cx1 = min(TILE - 1, w - 1 - x0), cy1 = min(TILE - 1, h - 1 - y0);
-    bx0 = by0 = INT_MAX; bx1 = by1 = INT_MIN;
-#pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      const int cx = (c & 1) ? cx1 : 0, cy = (c & 2) ? cy1 : 0;
-      int qx, qy, q0, q1;
-      affine_from_tables(a.interp, s_ad[cx], s_bd[cx], s_X0[cy], s_Y0[cy], qx, qy, q0, q1);
-      bx0 = min(bx0, qx); bx1 = max(bx1, qx);
-      by0 = min(by0, qy); by1 = max(by1, qy);
-    }
-  } else {
-    int mnx = INT_MAX, mny = INT_MAX, mxx = INT_MIN, mxy = INT_MIN;
-#pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      if (x + e < w && y < h) {
-        src_coord(a, x + e, y, sx[e], sy[e], fx[e], fy[e]);
-        mnx = min(mnx, sx[e]); mxx = max(mxx, sx[e]);
-        mny = min(mny, sy[e]); mxy = max(mxy, sy[e]);
-      } else {
-        sx[e] = sy[e] = fx[e] = fy[e] = 0;
-      }
-    }
-    if (tid == 0) { s_box[0] = INT_MAX; s_box[1] = INT_MAX; s_box[2] = INT_MIN; s_box[3] = INT_MIN; }
-    __syncthreads();
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      mnx = min(mnx, __shfl_xor_sync(0xffffffffu, mnx, o));
-      mny = min(mny, __shfl_xor_sync(0xffffffffu, mny, o));
-      mxx = max(mxx, __shfl_xor_sync(0xffffffffu, mxx, o));
-      mxy = max(mxy, __shfl_xor_sync(0xffffffffu, mxy, o));
-    }
-    if ((tid & 31) == 0) {
-      atomicMin(&s_box[0], mnx); atomicMin(&s_box[1], mny);
-      atomicMax(&s_box[2], mxx); atomicMax(&s_box[3], mxy);
-    }
-    __syncthreads();
-    bx0 = s_box[0]; by0 = s_box[1]; bx1 = s_box[2]; by1 = s_box[3];
-  }
-  if (a.border == B2SEG_BORDER_CONSTANT) {
-    // anything at or beyond one pixel outside the image reads only the constant
-    bx0 = max(-2, min(w, bx0)); bx1 = max(-2, min(w, bx1));
-    by0 = max(-2, min(h, by0)); by1 = max(-2, min(h, by1));
-#pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      sx[e] = max(-2, min(w, sx[e]));
-      sy[e] = max(-2, min(h, sy[e]));
-    }
-  }
-  const int bxa = bx0 & ~3;  // footprint columns start on a 4-byte boundary of the source row
-  const int bw = bx1 + (lin ? 1 : 0) - bxa + 1, bh = by1 + (lin ? 1 : 0) - by0 + 1;
-  const int bwords = (bw + 3) >> 2;
-  const bool staged = bx0 != INT_MAX && bw > 0 && bh > 0 && bwords * 4 <= FPITCH && bh <= FOOT;
-  const bool valid_row = y < h;
-
-  const int p_begin = items ? (int)blockIdx.z : blockIdx.z * pz;
-  const int p_end = items ? p_begin + 1 : min(planes, p_begin + pz);
-  for (int plane = p_begin; plane < p_end; ++plane) {
-    const uint8_t* s = src + (size_t)plane * h * w;
-    uint8_t* d = dst + (size_t)plane * h * w;
-    if (staged) {
-      if (plane != p_begin) __syncthreads();  // previous plane's gathers are done
-      // coalesced footprint load, border rule applied once per source byte
-      for (int idx = tid; idx < bh * bwords; idx += 256) {
-        const int fr = idx / bwords, fc = idx - fr * bwords;
-        const int gy = by0 + fr, gx = bxa + 4 * fc;
-        uint32_t word;
-        if (vec_ok && (unsigned)gy < (unsigned)h && gx >= 0 && gx + 3 < w) {
-          word = __ldg(reinterpret_cast<const uint32_t*>(s + (size_t)gy * w + gx));
-        } else {
-          const int yy = border_index(gy, h, a.border);
-          word = 0;
-#pragma unroll
-          for (int b = 0; b < 4; ++b) {
-            const int xx = border_index(gx + b, w, a.border);
-            const uint32_t v = (xx < 0 || yy < 0) ? (uint32_t)a.cval : (uint32_t)s[(size_t)yy * w + xx];
-            word |= v << (8 * b);
-          }
-        }
-        reinterpret_cast<uint32_t*>(&foot[fr][0])[fc] = word;
-      }
-      __syncthreads();
-    }
-    if (!valid_row) continue;
-    uint32_t packed = 0;
-#pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      if (x + e >= w) continue;
-      int v00, v01 = 0, v10 = 0, v11 = 0;
-      if (staged) {
-        const int lx = sx[e] - bxa, ly = sy[e] - by0;
-        v00 = foot[ly][lx];
-        if (lin) { v01 = foot[ly][lx + 1]; v10 = foot[ly + 1][lx]; v11 = foot[ly + 1][lx + 1]; }
-      } else {
-        v00 = fetch_global(s, h, w, sx[e], sy[e], a.border, a.cval);
-        if (lin) {
-          v01 = fetch_global(s, h, w, sx[e] + 1, sy[e], a.border, a.cval);
-          v10 = fetch_global(s, h, w, sx[e], sy[e] + 1, a.border, a.cval);
-          v11 = fetch_global(s, h, w, sx[e] + 1, sy[e] + 1, a.border, a.cval);
-        }
-      }
-      int out = v00;
-      if (lin) {
-        // cv2 BilinearTab_i weights are (32-fy)(32-fx)*32 etc. (sum 32768) with FixedPtCast<15>:
-        //   (sum v*w + 2^14) >> 15  ==  ((32-fy)*top + fy*bot + 2^9) >> 10   exactly (the sum is 32 * (...)),
-        // a convex combination of bytes, so no clamp is needed.
-        const int top = v00 * (32 - fx[e]) + v01 * fx[e], bot = v10 * (32 - fx[e]) + v11 * fx[e];
-        out = ((32 - fy[e]) * top + fy[e] * bot + 512) >> 10;
-      }
-      packed |= (uint32_t)out << (8 * e);
-    }
-    if (vec_ok && x + 3 < w) {
-      *reinterpret_cast<uint32_t*>(d + (size_t)y * w + x) = packed;
-    } else {
-#pragma unroll
-      for (int e = 0; e < 4; ++e)
-        if (x + e < w) d[(size_t)y * w + x + e] = (uint8_t)(packed >> (8 * e));
-    }
-  }
-}
-
-// ---- warp kernel, second form (default) ---------------------------------------------------------
-// Same tiling and the same cv2 arithmetic as warp_u8_v1_kernel, rebuilt around the instruction count
-// (v1 issues 59 instructions per pixel and is issue bound at 9-11 % of the HBM roofline):
-//  * a destination tile is TW x TH = 64 x 16 or 32 x 32 pixels (template), a thread still owns 4 adjacent pixels;
-//  * every thread owns up to four fixed words of the footprint (word index -> row by ONE division per CTA,
-//    offsets kept in registers), loads them unpredicated, and fetches the NEXT plane's words before the
-//    current plane is gathered, so the global latency of plane p+1 hides behind the arithmetic of plane p;
-//  * bilinear planes keep a second copy of the footprint shifted by two bytes.  Whatever the parity
-//    of the source column, one aligned 32-bit shared-memory word then holds both horizontal
-//    neighbours: copy (lx >> 1) & 1, word lx >> 2, bytes (lx & 1) and (lx & 1) + 1.  The horizontal
-//    blend v0 * (32 - fx) + v1 * fx is ONE dp4a against a per-pixel weight word that is zero in the
-//    other two byte lanes (computed once per CTA: all planes of a call share the transform), so a
-//    pixel costs 2 LDS.32 + 2 IDP4A + 2 IMAD + shift + pack instead of 4 LDS.U8 + 9 integer ops.
-constexpr int NSLOT = 4;               // footprint words per thread: a staged footprint has <= 1024 words
-constexpr int FCOPY = FOOT * FPITCH;   // byte offset of the shifted copy
+// Table mode (`items` != NULL): blockIdx.z = item * ppi + plane; every item brings its own matrix (or its own pair
+// of maps, `map_stride` floats apart) and every plane of an item its own interpolation and constant -- image
+// (bilinear) and mask (nearest) of ALL augmented copies of a batch are one launch.
+//
+// Built around the instruction count and the shared-memory wavefronts (the round-1 kernel: byte gathers, 59
+// instructions per pixel, issue bound at 9-11 % of the HBM roofline; profiles/r02_warp_kernel_notes.txt):
+//  * every thread owns up to three fixed 32-bit words of the footprint (word index -> row by ONE division per
+//    CTA, offsets kept in registers) and loads them unpredicated into registers FOUR planes ahead of the plane
+//    that is being gathered (cp.async instead of registers was measured and lost: a 4-byte LDGSTS costs ~4.5
+//    shared-memory wavefronts per warp, an STS one);
+//  * two staging buffers: plane k + 1 is stored while plane k is gathered, one barrier per plane;
+//  * the row pitch of the staged footprint is chosen per CTA: every warp counts, for two of the pitches that
+//    fit, the bank conflicts of its own gather addresses (match.any on bank and on address) and the CTA keeps the
+//    best.  With a fixed pitch a rotated tile spreads a warp's 32 words pseudo-randomly over the banks (3.5
+//    wavefronts per LDS measured, shared memory 75 % busy; 1.8 with the chosen pitch);
+//  * bilinear planes keep a second copy of the footprint shifted by two bytes (built with one shuffle per word).
+//    Whatever the parity of the source column, one aligned 32-bit shared-memory word then holds both horizontal
+//    neighbours: copy (lx >> 1) & 1, word lx >> 2, bytes (lx & 1) and (lx & 1) + 1.  The horizontal blend
+//    v0 * (32 - fx) + v1 * fx is ONE dp4a against a per-pixel weight word that is zero in the other two byte
+//    lanes, so a pixel costs 2 LDS.32 + 2 IDP4A + 2 IMAD + shift + pack instead of 4 LDS.U8 + 9 integer ops;
+//  * the border rule is folded into the description of a word once per CTA (see `esel` below).
+// Footprints of more than 744 words (strong zoom-out) are gathered from global memory.
+constexpr int NSLOT = 3;      // footprint words per thread
+constexpr int SEGW = 31;      // new words per warp and slot: lane 31 re-loads its neighbour's word for the shifted copy
+constexpr int FWORDS = 1280;  // words of one staged footprint (rows x chosen pitch); word FWORDS is a dump for idle lanes
+constexpr int CWORDS = 1312;  // distance of the shifted copy in words (a multiple of 32: same banks)
+constexpr int PDEPTH = 4;     // planes whose footprint words are in flight in registers (6 measured: no gain)
+constexpr int FBUF = 2 * CWORDS;  // words of one staging buffer (footprint + shifted copy); there are two
 
 // Footprint word with the border rule applied per byte (tiles that touch the image edge, or unaligned planes).
 __device__ __noinline__ uint32_t foot_word_border(const uint8_t* __restrict__ s, int h, int w, int gy, int gx,
@@ -478,20 +318,14 @@ __device__ __noinline__ uint32_t foot_word_border(const uint8_t* __restrict__ s,
   return word;
 }
 
-__device__ __forceinline__ uint32_t foot_word(const uint8_t* __restrict__ s, int h, int w, int gy, int gx,
-                                              int border, int cval, int vec_ok) {
-  if (vec_ok && (unsigned)gy < (unsigned)h && gx >= 0 && gx + 3 < w)
-    return __ldg(reinterpret_cast<const uint32_t*>(s + (size_t)gy * w + gx));
-  return foot_word_border(s, h, w, gy, gx, border, cval);
-}
-
 template <int TW, int TH>
 __global__ void __launch_bounds__(256, 4)
     warp_u8_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, WarpArgs a, int planes, int pz,
                    int vec_ok, const b2seg_warp_item* __restrict__ items, int ppi, long long map_stride) {
   static_assert(TW * TH == 1024 && TW % 4 == 0 && TW + TH <= 256, "256 threads x 4 pixels");
   constexpr int TPR = TW / 4;  // threads per destination row
-  __shared__ __align__(16) uint8_t foot[2 * FCOPY];  // second half = first half shifted by two bytes (bilinear only)
+  __shared__ __align__(16) uint32_t foot[2 * FBUF];  // two buffers of (footprint | footprint shifted by two bytes)
+  __shared__ int s_pitch;
   if (items != nullptr) {
     const int item = blockIdx.z / ppi, pl = blockIdx.z - item * ppi;
     const b2seg_warp_item& it = items[item];
@@ -587,7 +421,7 @@ __global__ void __launch_bounds__(256, 4)
   const int bw = bx1 + (lin ? 1 : 0) - bxa + 1, bh = by1 + (lin ? 1 : 0) - by0 + 1;
   const int bwords = (bw + 3) >> 2;
   const int nwords = bh * bwords;
-  const bool staged = bx0 != INT_MAX && bw > 0 && bh > 0 && bwords * 4 <= FPITCH && bh <= FOOT && nwords <= 256 * NSLOT;
+  const bool staged = bx0 != INT_MAX && bw > 0 && bh > 0 && nwords <= 8 * SEGW * NSLOT;
   const bool valid_row = y < h;
 
   const int p_begin = items ? (int)blockIdx.z : blockIdx.z * pz;
@@ -614,6 +448,33 @@ __global__ void __launch_bounds__(256, 4)
     return;
   }
 
+  // Row pitch of the staged footprint (words): every warp tries two of the (up to 16) pitches that fit and counts,
+  // over its own gather addresses of pixels 0 and 2, the lanes that share a bank without sharing the word;
+  // the CTA keeps the pitch with the fewest (ties: the smallest).
+  const int wi = tid >> 5, lane = tid & 31;
+  if (tid == 0) s_pitch = INT_MAX;
+  __syncthreads();
+  {
+    const int pmax = min(bwords + 15, FWORDS / bh);
+    for (int P = bwords + wi; P <= pmax; P += 8) {
+      int c = 0;
+#pragma unroll
+      for (int e = 0; e < 4; e += 2) {
+        const bool v = valid_row && x + e < w;
+        const unsigned vm = __ballot_sync(0xffffffffu, v);
+        const int lx = sx[e] - bxa, ly = sy[e] - by0;
+        const int aw = (lin ? ((lx >> 1) & 1) * CWORDS : 0) + ly * P + (lx >> 2);
+        const unsigned same_bank = __match_any_sync(0xffffffffu, aw & 31);
+        const unsigned same_word = __match_any_sync(0xffffffffu, aw);
+        c += v ? __popc(same_bank & vm) - __popc(same_word & vm) : 0;
+      }
+      c = __reduce_add_sync(0xffffffffu, c);
+      if (lane == 0) atomicMin(&s_pitch, (c << 12) | P);
+    }
+  }
+  __syncthreads();
+  const int P = s_pitch & 4095;
+
   // Per-pixel shared-memory byte offset and (bilinear) dp4a weight word; fixed for every plane.
   uint32_t goff[4], wsel[4];
 #pragma unroll
@@ -621,23 +482,24 @@ __global__ void __launch_bounds__(256, 4)
     int lx = sx[e] - bxa, ly = sy[e] - by0;
     if (!valid_row || x + e >= w) lx = ly = 0;  // never stored; keep the address inside the array
     if (lin) {
-      goff[e] = (uint32_t)(((lx >> 1) & 1) * FCOPY + ly * FPITCH + (lx >> 2) * 4);
+      goff[e] = (uint32_t)((((lx >> 1) & 1) * CWORDS + ly * P + (lx >> 2)) * 4);
       wsel[e] = (uint32_t)((32 - fx[e]) | (fx[e] << 8)) << ((lx & 1) * 8);
     } else {
-      goff[e] = (uint32_t)(ly * FPITCH + lx);
+      goff[e] = (uint32_t)(ly * P * 4 + lx);
       wsel[e] = 0;
     }
   }
-  const uint8_t* const f0 = foot;
-  auto gather_store = [&](uint8_t* __restrict__ d, auto lin_c) {
+  const uint8_t* const f0 = reinterpret_cast<const uint8_t*>(foot);
+  const int pitch_b = P * 4;
+  auto gather_store = [&](const uint8_t* __restrict__ fb, uint8_t* __restrict__ d, auto lin_c) {  // d -> pixel (y, x)
     constexpr bool LIN = decltype(lin_c)::value;
     if (!valid_row) return;
     uint32_t packed = 0;
     if (LIN) {
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
-        const uint32_t wt = *reinterpret_cast<const uint32_t*>(f0 + goff[e]);
-        const uint32_t wb = *reinterpret_cast<const uint32_t*>(f0 + goff[e] + FPITCH);
+        const uint32_t wt = *reinterpret_cast<const uint32_t*>(fb + goff[e]);
+        const uint32_t wb = *reinterpret_cast<const uint32_t*>(fb + goff[e] + pitch_b);
         // cv2 BilinearTab_i weights are (32-fy)(32-fx)*32 etc. (sum 32768) with FixedPtCast<15>:
         //   (sum v*w + 2^14) >> 15  ==  ((32-fy)*top + fy*bot + 2^9) >> 10   exactly (the sum is 32 * (...)),
         // a convex combination of bytes, so no clamp is needed.
@@ -647,141 +509,186 @@ __global__ void __launch_bounds__(256, 4)
       }
     } else {
 #pragma unroll
-      for (int e = 0; e < 4; ++e) packed |= (uint32_t)f0[goff[e]] << (8 * e);
+      for (int e = 0; e < 4; ++e) packed |= (uint32_t)fb[goff[e]] << (8 * e);
     }
     if (vec_ok && x + 3 < w) {
-      __stcs(reinterpret_cast<uint32_t*>(d + (size_t)y * w + x), packed);
+      __stcs(reinterpret_cast<uint32_t*>(d), packed);
     } else {
 #pragma unroll
       for (int e = 0; e < 4; ++e)
-        if (x + e < w) d[(size_t)y * w + x + e] = (uint8_t)(packed >> (8 * e));
+        if (x + e < w) d[e] = (uint8_t)(packed >> (8 * e));
     }
   };
 
-  // Footprint words of this thread: word i = tid + 256 j sits in footprint row i / bwords.  Slots past the end
-  // re-load slot 0's word and park it in a corner of the buffer that a <= 1024-word footprint never uses, so
-  // the per-plane loop carries no predicates.
+  // Footprint words of this thread: in slot j, warp wi owns words (8 j + wi) * 31 .. + 30; lane 31 loads the
+  // first word of the next run only to hand it to lane 30 for the shifted copy.  Idle lanes re-load the plane's
+  // first word and store to the dump word, so the per-plane loop of an interior tile carries no predicates.
   uint32_t gsrc[NSLOT], sdst[NSLOT];
-  bool ok = vec_ok != 0;
+  uint32_t oob = 0;
 #pragma unroll
   for (int j = 0; j < NSLOT; ++j) {
-    const int i = tid + 256 * j;
+    const int i = (8 * j + wi) * SEGW + lane;
     const int fr = i / bwords, fc = i - fr * bwords;
     const int gy = by0 + fr, gx = bxa + 4 * fc;
+    gsrc[j] = 0;
     if (i < nwords) {
-      // the +4 neighbour read of the last word of a row must stay inside the plane
-      ok = ok && (unsigned)gy < (unsigned)h && gx >= 0 && gx + 3 < w && (gx + 7 < w || gy + 1 < h);
-      gsrc[j] = (uint32_t)(gy * w + gx);
-      sdst[j] = (uint32_t)(fr * FPITCH + 4 * fc);
-    } else {
-      gsrc[j] = (uint32_t)(by0 * w + bxa);
-      sdst[j] = (uint32_t)((FOOT - 1) * FPITCH + FPITCH - 4);
+      if (vec_ok && (unsigned)gy < (unsigned)h && gx >= 0 && gx + 3 < w) gsrc[j] = (uint32_t)(gy * w + gx);
+      else oob |= 1u << j;
+    }
+    sdst[j] = (i < nwords && lane < SEGW) ? (uint32_t)(fr * P + fc) : (uint32_t)FWORDS;
+  }
+  const bool interior = __syncthreads_and(oob == 0) != 0;
+  const int nslots = (nwords + 8 * SEGW - 1) / (8 * SEGW);  // 1..NSLOT, CTA-uniform
+
+  // Tiles on the image edge.  The border rule is the same for every plane, so it is folded into the word's
+  // description once: a row outside the image is another row (reflect) or the constant, and the four bytes of a
+  // word that crosses the left / right edge come from at most two aligned words of that row -- two loads and
+  // two byte permutes per plane, prefetched like any other word (calling the per-byte rule inside the plane
+  // loop exposed a full memory latency per word and plane: edge CTAs set the kernel's duration).
+  //   gsrc bit 0: the second aligned word is the next one (else the same);  esel: low half = PRMT selector over
+  //   the two words, high half = PRMT selector that replaces bytes by the constant.
+  // Words that do not fit this form (planes without 4-byte alignment, images narrower than the overhang) keep
+  // their oob flag and take foot_word_border.
+  uint32_t esel[NSLOT];
+  if (!interior) {
+#pragma unroll
+    for (int j = 0; j < NSLOT; ++j) {
+      esel[j] = 0x32103210u;
+      if (!((oob >> j) & 1) || !vec_ok) continue;
+      const int i = (8 * j + wi) * SEGW + lane;
+      const int fr = i / bwords, fc = i - fr * bwords;
+      const int gy = by0 + fr, gx = bxa + 4 * fc;
+      const int yy = border_index(gy, h, a.border);
+      int xx[4], lo = INT_MAX, hi = INT_MIN;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        xx[q] = yy < 0 ? -1 : border_index(gx + q, w, a.border);
+        if (xx[q] >= 0) { lo = min(lo, xx[q]); hi = max(hi, xx[q]); }
+      }
+      if (hi < 0) {  // nothing but the constant
+        esel[j] = 0x76543210u;
+        oob &= ~(1u << j);
+        continue;
+      }
+      const int base = lo & ~3;
+      if (hi > base + 7) continue;  // stays on the per-byte path
+      uint32_t s1 = 0, s2 = 0;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        s1 |= (uint32_t)(xx[q] >= 0 ? xx[q] - base : 0) << (4 * q);
+        s2 |= (uint32_t)(xx[q] >= 0 ? q : 4 + q) << (4 * q);
+      }
+      esel[j] = s1 | (s2 << 16);
+      gsrc[j] = (uint32_t)(yy * w + base) | (hi >= base + 4 ? 1u : 0u);
+      oob &= ~(1u << j);
     }
   }
-  const bool interior = __syncthreads_and(ok) != 0;  // also orders the coordinate tables before the first store
-  const int nslots = (nwords + 255) >> 8;            // 1..NSLOT, CTA-uniform
+  const uint32_t cval4 = (uint32_t)a.cval * 0x01010101u;
 
-  if (interior) {
-    auto run = [&](auto lin_c) {
-      constexpr bool LIN = decltype(lin_c)::value;
-      uint32_t wa[NSLOT], wn[NSLOT];
-      const uint8_t* s = src + (size_t)p_begin * h * w;
+  // One barrier per plane: plane k + 1 is stored into the other buffer while plane k is gathered.
+  auto run = [&](auto lin_c, auto ns_c, auto edge_c) {
+    constexpr bool LIN = decltype(lin_c)::value;
+    constexpr int NS = decltype(ns_c)::value;
+    constexpr bool EDGE = decltype(edge_c)::value;
+    const int np = p_end - p_begin;
+    const size_t hw = (size_t)h * w;
+    const uint8_t* sp = src + (size_t)p_begin * hw;                // plane whose words are loaded next
+    uint8_t* dp = dst + (size_t)p_begin * hw + (size_t)y * w + x;  // this thread's four pixels
+    constexpr int PD = PDEPTH;  // planes in flight; even (buffer parity = plane parity)
+    uint32_t pre[PD][NS];
+    auto load = [&](uint32_t (&r)[NS]) {
 #pragma unroll
-      for (int j = 0; j < NSLOT; ++j)
-        if (j < nslots) {
-          const uint32_t* g = reinterpret_cast<const uint32_t*>(s + gsrc[j]);
-          wa[j] = __ldg(g);
-          if (LIN) wn[j] = __ldg(g + 1);
+      for (int j = 0; j < NS; ++j) {
+        if (EDGE && ((oob >> j) & 1)) {
+          const int i = (8 * j + wi) * SEGW + lane;
+          const int fr = i / bwords, fc = i - fr * bwords;
+          r[j] = foot_word_border(sp, h, w, by0 + fr, bxa + 4 * fc, a.border, a.cval);
+        } else if (!EDGE) {
+          r[j] = __ldg(reinterpret_cast<const uint32_t*>(sp + gsrc[j]));
+        } else if (vec_ok) {
+          const uint32_t* g = reinterpret_cast<const uint32_t*>(sp + (gsrc[j] & ~3u));
+          const uint32_t two = __byte_perm(__ldg(g), __ldg(g + (gsrc[j] & 1u)), esel[j] & 0xffffu);
+          r[j] = __byte_perm(two, cval4, esel[j] >> 16);
+        } else {
+          r[j] = 0;  // idle lane of an unaligned plane (every real word took the border path)
         }
-      for (int plane = p_begin; plane < p_end; ++plane) {
-        if (plane != p_begin) __syncthreads();  // previous plane's gathers are done
+      }
+      sp += hw;
+    };
+    auto store = [&](const uint32_t (&r)[NS], int buf) {
 #pragma unroll
-        for (int j = 0; j < NSLOT; ++j)
-          if (j < nslots) {
-            *reinterpret_cast<uint32_t*>(foot + sdst[j]) = wa[j];
-            if (LIN) *reinterpret_cast<uint32_t*>(foot + sdst[j] + FCOPY) = __funnelshift_r(wa[j], wn[j], 16);
-          }
-        if (plane + 1 < p_end) {  // next plane's words fly while this plane is gathered
-          s += (size_t)h * w;
-#pragma unroll
-          for (int j = 0; j < NSLOT; ++j)
-            if (j < nslots) {
-              const uint32_t* g = reinterpret_cast<const uint32_t*>(s + gsrc[j]);
-              wa[j] = __ldg(g);
-              if (LIN) wn[j] = __ldg(g + 1);
-            }
-        }
-        __syncthreads();
-        gather_store(dst + (size_t)plane * h * w, lin_c);
+      for (int j = 0; j < NS; ++j) {
+        foot[buf * FBUF + sdst[j]] = r[j];
+        if (LIN) foot[buf * FBUF + sdst[j] + CWORDS] = __funnelshift_r(r[j], __shfl_down_sync(0xffffffffu, r[j], 1), 16);
       }
     };
-    if (lin) run(std::true_type{}); else run(std::false_type{});
-    return;
-  }
-
-  // Tiles that touch the image edge (or planes without 4-byte alignment): border rule per byte, then the
-  // shifted copy from shared memory.
-  for (int plane = p_begin; plane < p_end; ++plane) {
-    const uint8_t* s = src + (size_t)plane * h * w;
-    if (plane != p_begin) __syncthreads();
-    for (int i = tid; i < nwords; i += 256) {
-      const int fr = i / bwords, fc = i - fr * bwords;
-      *reinterpret_cast<uint32_t*>(foot + fr * FPITCH + 4 * fc) =
-          foot_word(s, h, w, by0 + fr, bxa + 4 * fc, a.border, a.cval, vec_ok);
-    }
+#pragma unroll
+    for (int u = 0; u < PD; ++u)
+      if (u < np) load(pre[u]);
+    store(pre[0], 0);
+    if (PD < np) load(pre[0]);
     __syncthreads();
-    if (lin) {
-      for (int i = tid; i < nwords; i += 256) {
-        const int fr = i / bwords, fc = i - fr * bwords;
-        const uint32_t* p = reinterpret_cast<const uint32_t*>(foot + fr * FPITCH + 4 * fc);
-        const uint32_t nx = fc + 1 < bwords ? p[1] : 0u;
-        *reinterpret_cast<uint32_t*>(foot + FCOPY + fr * FPITCH + 4 * fc) = __funnelshift_r(p[0], nx, 16);
+    for (int k0 = 0; k0 < np; k0 += PD) {
+#pragma unroll
+      for (int u = 0; u < PD; ++u) {
+        const int k = k0 + u;
+        if (k < np) {
+          if (k + 1 < np) {
+            store(pre[(u + 1) % PD], (u + 1) & 1);
+            if (k + 1 + PD < np) load(pre[(u + 1) % PD]);
+          }
+          gather_store(f0 + (u & 1) * (FBUF * 4), dp, lin_c);
+          dp += hw;
+          __syncthreads();
+        }
       }
-      __syncthreads();
     }
-    if (lin) gather_store(dst + (size_t)plane * h * w, std::true_type{});
-    else gather_store(dst + (size_t)plane * h * w, std::false_type{});
+  };
+  auto pick_ns = [&](auto lin_c, auto edge_c) {
+    if (nslots == 1) run(lin_c, std::integral_constant<int, 1>{}, edge_c);
+    else if (nslots == 2) run(lin_c, std::integral_constant<int, 2>{}, edge_c);
+    else run(lin_c, std::integral_constant<int, 3>{}, edge_c);
+  };
+  if (interior) {
+    if (lin) pick_ns(std::true_type{}, std::false_type{}); else pick_ns(std::false_type{}, std::false_type{});
+  } else {
+    if (lin) pick_ns(std::true_type{}, std::true_type{}); else pick_ns(std::false_type{}, std::true_type{});
   }
 }
 
-// B2SEG_WARP_KERNEL = 1: round-1/2 kernel (32 x 32 tiles, byte gathers); 2: second form on 32 x 32 tiles;
-// 3 (default): second form on 64 x 16 tiles.
-int warp_kernel_choice() {
-  static const int c = [] {
-    const char* e = getenv("B2SEG_WARP_KERNEL");
-    const int v = e ? atoi(e) : 3;
-    return v >= 1 && v <= 3 ? v : 3;
+// B2SEG_WARP_TILE = 64x16 selects the wide tile (same speed at small angles, 194 vs 191 us at 128 x 1024^2; its
+// footprint outgrows the staging buffer beyond ~30 degrees); default 32 x 32.
+bool warp_wide_tile() {
+  static const bool wide = [] {
+    const char* e = getenv("B2SEG_WARP_TILE");
+    return e && e[0] == '6';
   }();
-  return c;
+  return wide;
 }
 
 int launch_warp_any(const uint8_t* src, uint8_t* dst, const WarpArgs& a, int planes, int pz, int gz, int vec_ok,
                     const b2seg_warp_item* items, int ppi, long long map_stride, void* stream) {
-  const int choice = warp_kernel_choice();
-  const int tw = choice == 3 ? 64 : 32, th = choice == 3 ? 16 : 32;
+  const bool wide = warp_wide_tile();
+  const int tw = wide ? 64 : 32, th = wide ? 16 : 32;
   const int tx = (a.w + tw - 1) / tw, ty = (a.h + th - 1) / th;
   B2_REQUIRE(ty <= 65535 && gz <= 65535, "aug_warp: image too tall for the launch grid (%d rows)", a.h);
   dim3 grid(tx, ty, gz);
   cudaStream_t st = (cudaStream_t)stream;
-  if (choice == 1)
-    warp_u8_v1_kernel<<<grid, 256, 0, st>>>(src, dst, a, planes, pz, vec_ok, items, ppi, map_stride);
-  else if (choice == 2)
-    warp_u8_kernel<32, 32><<<grid, 256, 0, st>>>(src, dst, a, planes, pz, vec_ok, items, ppi, map_stride);
-  else
-    warp_u8_kernel<64, 16><<<grid, 256, 0, st>>>(src, dst, a, planes, pz, vec_ok, items, ppi, map_stride);
+  if (wide) warp_u8_kernel<64, 16><<<grid, 256, 0, st>>>(src, dst, a, planes, pz, vec_ok, items, ppi, map_stride);
+  else warp_u8_kernel<32, 32><<<grid, 256, 0, st>>>(src, dst, a, planes, pz, vec_ok, items, ppi, map_stride);
   B2_CHECK_CUDA(cudaGetLastError());
   return B2SEG_OK;
 }
 
 int launch_warp(const uint8_t* src, uint8_t* dst, int planes, const WarpArgs& a, void* stream) {
-  // ~48 CTAs per SM over the call (short CTAs, no tail) as long as a CTA still walks >= 8 planes with one set
-  // of source coordinates; v1 keeps its original split (~8 CTAs per SM)
+  // ~16 CTAs per SM over the call (4 are resident: four waves) as long as a CTA still walks >= 8 planes with one
+  // set of source coordinates and one pitch search (~590 instructions per warp, as much as 9 planes of the loop;
+  // 8 / 32 CTAs per SM measured: 192 / 196 us against 191)
   const int tiles = ((a.w + 31) / 32) * ((a.h + 31) / 32);
-  const int per_sm = warp_kernel_choice() == 1 ? 8 : 48;
-  int gz = (148 * per_sm + tiles - 1) / tiles;
+  int gz = (148 * 16 + tiles - 1) / tiles;
   gz = gz < 1 ? 1 : (gz > planes ? planes : gz);
   int pz = (planes + gz - 1) / gz;
-  if (warp_kernel_choice() != 1 && pz < 8) {
+  if (pz < 8) {
     for (int cand = 8; cand > pz; cand >>= 1)
       if ((long long)tiles * ((planes + cand - 1) / cand) >= 148 * 8) { pz = cand; break; }
   }

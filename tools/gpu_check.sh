@@ -2,7 +2,7 @@
 # One parameterised GPU recipe (run under gpurun):  tools/gpu_check.sh [tests] [bench] [ops] [ncu] [hbm] [dp]
 #   tests  pytest -m gpu (+ smoke)          bench  default bench.py + reference arm
 #   ops    per-op / per-segment / in-graph timings   ncu   launch list + DRAM bytes per kernel of one step
-#   hbm    tools/hbm_bench.py ([64,1,1024,1024] loss / metric / augment kernels)   warp   B2SEG_WARP_KERNEL=1/2/3 A/B
+#   hbm    tools/hbm_bench.py ([64,1,1024,1024] loss / metric / augment kernels)   warp / warpncu   warp kernel: both tile shapes, ncu --set full
 # Outputs land in gpurun_out/ (scratch); copy what should be judged into profiles/.
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm --format=csv > gpurun_out/gpu.txt 2>&1
@@ -54,12 +54,15 @@ PY
 hbm)
   timeout 600 python tools/hbm_bench.py > gpurun_out/hbm_kernels.json 2> gpurun_out/hbm_kernels.err; echo "hbm rc=$?"; tail -3 gpurun_out/hbm_kernels.err;;
 warp)
-  # the three forms of the warp kernel: bit-exactness against cv2, then [128 planes, 1024^2] timings
-  for k in 3 2 1; do
-    B2SEG_WARP_KERNEL=$k timeout 900 python -m pytest tests/test_augment_gpu.py tests/test_augment_ops_gpu.py -q -m gpu -x \
-        > gpurun_out/pytest_warp_k$k.log 2>&1; echo "warp kernel $k pytest rc=$?"; tail -3 gpurun_out/pytest_warp_k$k.log
-    B2SEG_WARP_KERNEL=$k timeout 300 python tools/hbm_bench.py --only aug > gpurun_out/hbm_aug_k$k.json 2> gpurun_out/hbm_aug_k$k.err
-    echo "hbm k=$k rc=$?"; grep -A1 "warp\|remap" gpurun_out/hbm_aug_k$k.json | grep -o '"aug[a-z_]*"\|"us": [0-9.]*\|"frac_of_peak": [0-9.]*' | paste - - -
+  # warp kernel, both tile shapes: bit-exactness against cv2, then [128 planes, 1024^2] timings
+  for t in 32x32 64x16; do
+    B2SEG_WARP_TILE=$t timeout 900 python -m pytest tests/test_augment_gpu.py tests/test_augment_ops_gpu.py -q -m gpu -x \
+        > gpurun_out/pytest_warp_$t.log 2>&1; echo "warp tile $t pytest rc=$?"; tail -1 gpurun_out/pytest_warp_$t.log
+    B2SEG_WARP_TILE=$t timeout 300 python tools/hbm_bench.py --only aug > gpurun_out/hbm_aug_$t.json 2> gpurun_out/hbm_aug_$t.err
+    echo "hbm tile $t rc=$?"; grep -A1 "warp\|remap" gpurun_out/hbm_aug_$t.json | grep -o '"aug[a-z_]*"\|"us": [0-9.]*' | paste - - - - - -
   done;;
+warpncu)
+  timeout 600 ncu --set full --clock-control none --import-source on -k regex:warp_u8 -s 4 -c 3 -f -o gpurun_out/warp \
+      python tools/warp_profile.py > gpurun_out/warp_ncu.log 2>&1; echo "warp ncu rc=$?"; tail -2 gpurun_out/warp_ncu.log;;
 esac; done
 ls gpurun_out | wc -l
