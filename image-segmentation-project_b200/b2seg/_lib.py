@@ -8,7 +8,7 @@ from __future__ import annotations
 import ctypes as C
 import os
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 _HERE = os.path.dirname(os.path.abspath(__file__))
 # B2SEG_LIB_PATH: development A/B runs against another build of the same ABI (never a fallback)
 LIB_PATH = os.environ.get("B2SEG_LIB_PATH") or os.path.join(_HERE, "libb2seg.so")
@@ -66,6 +66,7 @@ class TapGemmDesc(C.Structure):
         ("out", C.c_void_p), ("osn", C.c_int64), ("osh", C.c_int64), ("osw", C.c_int64),
         ("cq", C.c_int32), ("oqh", C.c_int64), ("oqw", C.c_int64),
         ("bias", C.c_void_p), ("stats", C.c_void_p), ("accumulate", C.c_int32),
+        ("stats_fixed", C.c_int32),
     ]
 
 

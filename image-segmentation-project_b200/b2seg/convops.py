@@ -198,7 +198,8 @@ def stat_rows(n, h, w) -> int:
 
 
 def conv_fprop(x: View, wp: torch.Tensor, k: int, stride: int, out: View, bias=None, stats=None):
-    """out = conv(x, W) (+bias); optional per-channel partial (sum, sumsq) rows in `stats`."""
+    """out = conv(x, W) (+bias); optional per-channel partial (sum, sumsq) rows in `stats` (fp32
+    [rows][2][C]), or -- an int64 `stats` [2][C], zeroed by the caller -- fixed-point sums added with atomics."""
     d = L.TapGemmDesc()
     views = [x] if stride == 1 else ([x.phase(0, 0)] if k == 1 else
                                      [x.phase(a, b) for a in (0, 1) for b in (0, 1)])
@@ -214,7 +215,11 @@ def conv_fprop(x: View, wp: torch.Tensor, k: int, stride: int, out: View, bias=N
     d.cq = 0
     d.bias = bias.data_ptr() if bias is not None else None
     d.stats = stats.data_ptr() if stats is not None else None
-    if stats is not None:
+    d.stats_fixed = 0
+    if stats is not None and stats.dtype == torch.int64:
+        assert stats.numel() >= 2 * out.c
+        d.stats_fixed = 1
+    elif stats is not None:
         assert stats.dtype == torch.float32 and stats.numel() >= stat_rows(out.n, out.h, out.w) * 2 * out.c
     return _create_tapgemm(d, (x.t, wp, out.t, bias, stats), f"conv{k}x{k}s{stride}")
 

@@ -59,12 +59,19 @@ class BNRef:
         self.rows, self.count, self.ready = rows, count, ready
 
 
+_BN_FUSED_FWD_DEFAULT = "2"
+_FX_CAP = 1 << 18  # int64 words of fixed-point BatchNorm accumulators per plan (2 x the BatchNorm channels)
+
+
 def _fused_bn_fwd():
-    """EW_BN_APPLY_FUSED (the consumer folds the conv epilogue's partial statistics itself).  Off by
-    default: every block re-reads all partial rows (<= 296 x 2C floats), which costs more than the
-    finalize launch it saves (measured: DESIGN 3.7); B2SEG_BN_FUSED_FWD=1 turns it on."""
+    """EW_BN_APPLY_FUSED: no finalize launch, the consumer of a BatchNorm derives scale / shift itself.
+    B2SEG_BN_FUSED_FWD = 0: finalize kernel (fp32 partial rows, one per CTA of the conv);
+    1: the consumer folds those <= 296 x 2C floats in every block (costs more than the launch it saves,
+       DESIGN 3.7);
+    2: the conv epilogues add their partial sums as fixed-point integers into ONE int64 row with atomics
+       (exact and order-independent, so still bit-reproducible) and the consumer reads 2C words."""
     import os
-    return os.environ.get("B2SEG_BN_FUSED_FWD", "0") == "1"
+    return os.environ.get("B2SEG_BN_FUSED_FWD", _BN_FUSED_FWD_DEFAULT)
 
 
 def _fused_bn_bwd_max_bytes():
@@ -148,6 +155,18 @@ class UNetPlan:
         self.keep.append(t)
         return t
 
+    def _fx_alloc(self, n):
+        """n int64 words of the plan's fixed-point accumulator arena (zeroed by ONE fill at the head of
+        every forward pass, `_fx_fill_op`)."""
+        if getattr(self, "_fx", None) is None:
+            self._fx = self._alloc((_FX_CAP,), torch.int64, zero=True)
+            self._fx_used = 0
+        o = self._fx_used
+        self._fx_used = o + ((n + 1) & ~1)  # 16-byte granules
+        if self._fx_used > _FX_CAP:
+            raise RuntimeError("fixed-point BatchNorm accumulator arena exhausted")
+        return self._fx[o:o + n]
+
     def act(self, n, h, w, c, grad=None):
         """New dense activation (and gradient buffer when a backward pass is planned)."""
         v = View(self._alloc((n, h, w, c), BF16))
@@ -213,8 +232,9 @@ class UNetPlan:
         if self.training and count <= 1:
             raise ValueError(f"Expected more than 1 value per channel when training ({prefix})")
         bnp = self._alloc((4, C_), F32)
-        if defer and self.training and C_ % 8 == 0 and _fused_bn_fwd():
+        if defer and self.training and C_ % 8 == 0 and (rows < 0 or _fused_bn_fwd() == "1"):
             return BNRef(prefix, C_, bnp, partial, rows, count, False)
+        assert rows >= 0, "fixed-point statistics have no finalize kernel"
         self._emit_finalize(prefix, C_, rows, count, partial, bnp)
         return BNRef(prefix, C_, bnp, partial, rows, count, True)
 
@@ -259,7 +279,10 @@ class UNetPlan:
         N, ho, wo = x.n, x.h // stride, x.w // stride
         y = View(self._alloc((N, ho, wo, cout), BF16))
         rows = co.stat_rows(N, ho, wo)
-        stats = self._alloc((rows, 2, cout), F32) if self.training else None
+        if self.training and cout % 8 == 0 and _fused_bn_fwd() == "2":
+            rows, stats = -1, self._fx_alloc(2 * cout)
+        else:
+            stats = self._alloc((rows, 2, cout), F32) if self.training else None
         bias = self.params[biasname] if biasname else None
         self.F(co.conv_fprop(x, self.packed(wname, "fprop"), k, stride, y, bias=bias, stats=stats))
         self.wgrad_ws(x.c, cout, k * k, N, ho, wo)
@@ -457,6 +480,8 @@ class UNetPlan:
         self.keep.append(raw)
         self.pack_op = eo.ew(L.EW_PACK, p=[raw], i=[len(self.pack_jobs), start])
         self.fwd_ops.insert(0, self.pack_op)
+        if getattr(self, "_fx", None) is not None:  # fixed-point BatchNorm accumulators start every pass at zero
+            self.fwd_ops.insert(0, eo.ew(L.EW_FILL, p=[self._fx], i=[self._fx_used * 8, 0]))
 
     def upconv_backward(self, name, dprev: Act, dy: View):
         """ConvTranspose2d(k=2,s=2) backward: weight, bias and (accumulating) input gradient."""

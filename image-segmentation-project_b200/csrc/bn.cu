@@ -402,6 +402,19 @@ __device__ __forceinline__ void bn_fold_rows(const float* partial, int rows, int
   __syncthreads();
 }
 
+// rows < 0: `partial` is the int64 [2][C] fixed-point accumulator the conv epilogues added to with atomics
+// (b2seg_tapgemm_desc::stats_fixed): nothing to fold.
+__device__ __forceinline__ void bn_fold_stats(const float* partial, int rows, int C, double* sm_sum, double* sm_tmp) {
+  if (rows >= 0) {
+    bn_fold_rows<2>(partial, rows, C, sm_sum, sm_tmp);
+    return;
+  }
+  const long long* acc = reinterpret_cast<const long long*>(partial);
+  for (int q = threadIdx.x; q < 2 * C; q += blockDim.x)
+    sm_sum[q] = (double)__ldcg(acc + q) * (q < C ? 1.0 / (double)B2SEG_STATS_FIX_SUM : 1.0 / (double)B2SEG_STATS_FIX_SQ);
+  __syncthreads();
+}
+
 // (sum, sumsq) -> scale / shift in shared memory; block 0 also publishes bnp = scale, shift, mean,
 // invstd and updates the running statistics: the arithmetic of bn_finalize_kernel, verbatim.
 __device__ __forceinline__ void bn_affine_from_sums(const double* sm_sum, int C, double count, float eps,
@@ -450,12 +463,12 @@ __global__ void __launch_bounds__(kBnT, 2) bn_apply_fused_kernel(const EwArgs a)
   double* sm_tmp = sm_sum + 2 * C;
   float* sm_aff = reinterpret_cast<float*>(sm_tmp + kBnT);
   const float eps = a.f[0], mom = a.f[1];
-  bn_fold_rows<2>((const float*)a.p[3], (int)a.i[6], C, sm_sum, sm_tmp);
+  bn_fold_stats((const float*)a.p[3], (int)a.i[6], C, sm_sum, sm_tmp);
   bn_affine_from_sums(sm_sum, C, (double)a.i[7], eps, mom, (const float*)a.p[4], (const float*)a.p[5],
                       (float*)a.p[6], (float*)a.p[7], (long long*)a.p[8], (float*)a.p[9], sm_aff, sm_aff + C);
   __syncthreads();
   if (rnorm) {
-    bn_fold_rows<2>((const float*)a.p[10], (int)a.i[8], C, sm_sum, sm_tmp);
+    bn_fold_stats((const float*)a.p[10], (int)a.i[8], C, sm_sum, sm_tmp);
     bn_affine_from_sums(sm_sum, C, (double)a.i[7], eps, mom, (const float*)a.p[11], (const float*)a.p[12],
                         (float*)a.p[13], (float*)a.p[14], (long long*)a.p[15], (float*)a.p[16],
                         sm_aff + 2 * C, sm_aff + 3 * C);
@@ -1007,8 +1020,8 @@ int ew_plan_bn(const b2seg_ew_desc* d, EwPlan* pl) {
     }
     case B2SEG_EW_BN_APPLY_FUSED: {
       EW_REQ_VEC(i[1]);
-      B2_REQUIRE(p[0] && p[1] && p[3] && p[9] && i[0] >= 1 && i[6] >= 1 && i[7] >= 1, "bn_apply_fused: null argument");
-      B2_REQUIRE(!p[10] || (p[2] && p[16] && i[8] >= 1), "bn_apply_fused: residual BatchNorm needs res, bnp and rows");
+      B2_REQUIRE(p[0] && p[1] && p[3] && p[9] && i[0] >= 1 && i[6] != 0 && i[7] >= 1, "bn_apply_fused: null argument");
+      B2_REQUIRE(!p[10] || (p[2] && p[16] && i[8] != 0), "bn_apply_fused: residual BatchNorm needs res, bnp and rows");
       B2_REQUIRE(i[2] % 8 == 0 && i[3] % 8 == 0 && i[4] % 8 == 0 && aligned16(p[0]) &&
                      aligned16(p[1]) && aligned16(p[2]),
                  "bn_apply_fused: leading dimensions / pointers must be 16-byte aligned");

@@ -442,6 +442,11 @@ __global__ void __launch_bounds__(kThreadsH, 1)
       for (int e = threadIdx.x - 32 * kEpiWarp0; e < 2 * BLOCK_N; e += 256) {
         const float x = (sm0[e] + sm0[2 * BLOCK_N + e]) + (sm0[4 * BLOCK_N + e] + sm0[6 * BLOCK_N + e]);
         const int k = e / BLOCK_N, cc = e % BLOCK_N;
+        if (p.stat_rows == 0) {  // fixed-point accumulators (b2seg_tapgemm_desc::stats_fixed)
+          atomicAdd(reinterpret_cast<unsigned long long*>(p.stats) + (size_t)k * p.ngemm + col0 + cc,
+                    (unsigned long long)__float2ll_rn(x * (k ? B2SEG_STATS_FIX_SQ : B2SEG_STATS_FIX_SUM)));
+          continue;
+        }
         p.stats[((size_t)mt0 * 2 + k) * p.ngemm + col0 + cc] = x;
         for (int rr = mt0 + mstep; rr < p.stat_rows; rr += mstep)
           p.stats[((size_t)rr * 2 + k) * p.ngemm + col0 + cc] = 0.0f;
@@ -610,7 +615,7 @@ int b2_halo3x3_try_create(const b2seg_tapgemm_desc* d, b2seg_op** out) {
   p.bias = d->bias;
   p.stats = d->stats;
   p.accumulate = d->accumulate;
-  p.stat_rows = b2seg_tapgemm_stat_rows(d->on, d->oh, d->ow);
+  p.stat_rows = d->stats_fixed ? 0 : b2seg_tapgemm_stat_rows(d->on, d->oh, d->ow);
   p.resident = resident; p.a_stages = a_stages; p.b_slots = b_slots;
   {
     const char* e = getenv("B2SEG_PROBE");

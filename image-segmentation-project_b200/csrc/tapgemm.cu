@@ -406,6 +406,11 @@ __global__ void __launch_bounds__(kThreadsTG, 2)
     if (p.stats) {  // one (sum, sumsq) row per CTA group; rows no group owns are zero-filled
       for (int e = threadIdx.x - 64; e < 2 * BLOCK_N; e += 128) {
         const int k = e / BLOCK_N, cc = e % BLOCK_N;
+        if (p.stat_rows == 0) {  // fixed-point accumulators (b2seg_tapgemm_desc::stats_fixed)
+          atomicAdd(reinterpret_cast<unsigned long long*>(p.stats) + (size_t)k * p.ngemm + col0 + cc,
+                    (unsigned long long)__float2ll_rn(run_sm[e] * (k ? B2SEG_STATS_FIX_SQ : B2SEG_STATS_FIX_SUM)));
+          continue;
+        }
         p.stats[((size_t)grp * 2 + k) * p.ngemm + col0 + cc] = run_sm[e];
         for (int rr = grp + groups; rr < p.stat_rows; rr += groups)
           p.stats[((size_t)rr * 2 + k) * p.ngemm + col0 + cc] = 0.0f;
@@ -584,7 +589,7 @@ extern "C" int b2seg_tapgemm_create(const b2seg_tapgemm_desc* d, b2seg_op** out)
   p.stats = d->stats;
   p.accumulate = d->accumulate;
   p.nsub = d->nsub;
-  p.stat_rows = b2seg_tapgemm_stat_rows(d->on, d->oh, d->ow);
+  p.stat_rows = d->stats_fixed ? 0 : b2seg_tapgemm_stat_rows(d->on, d->oh, d->ow);
   p.dv_mtiles = make_fastdiv((uint32_t)p.mtiles);
   p.dv_w = make_fastdiv((uint32_t)p.tilesW);
   p.dv_hw = make_fastdiv((uint32_t)(p.tilesW * p.tilesH));

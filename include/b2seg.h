@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define B2SEG_ABI_VERSION 2
+#define B2SEG_ABI_VERSION 3
 
 #define B2SEG_OK 0
 #define B2SEG_EINVAL (-1)  /* bad argument / unsupported shape            */
@@ -344,7 +344,13 @@ typedef struct b2seg_tapgemm_desc {
   const float* bias;            /* fp32 [cq ? cq : ngemm] or NULL */
   float* stats;                 /* fp32 [stat_rows][2][ngemm] partial (sum, sumsq) or NULL */
   int32_t accumulate;           /* out += result instead of out = result */
+  int32_t stats_fixed;          /* 1: `stats` is int64 [2][ngemm] instead -- every CTA adds its partial sums as
+                                   fixed-point integers (sum x 2^20, sumsq x 2^16) with 64-bit atomics: exact,
+                                   order-independent, one row; the caller zeroes it before the launch and the
+                                   BatchNorm consumer reads it with rows = -1 (B2SEG_EW_BN_APPLY_FUSED) */
 } b2seg_tapgemm_desc;
+#define B2SEG_STATS_FIX_SUM 1048576.0f   /* 2^20 */
+#define B2SEG_STATS_FIX_SQ 65536.0f      /* 2^16 */
 
 int b2seg_tapgemm_create(const b2seg_tapgemm_desc* desc /*host*/, b2seg_op** out);
 /* number of partial-statistics rows a tapgemm op with this iteration grid writes */

@@ -71,6 +71,21 @@ def test_conv_fprop_dgrad_wgrad(cuda, n, h, w, cin, cout, k, stride):
     np.testing.assert_allclose(s[0].numpy(), y_ref.double().sum((0, 2, 3)).numpy(), rtol=1e-3,
                                atol=1e-2 * float(y_ref.abs().max()) * (n * ho * wo) ** 0.5)
     np.testing.assert_allclose(s[1].numpy(), (y_ref.double() ** 2).sum((0, 2, 3)).numpy(), rtol=2e-3)
+    # fixed-point accumulators (stats_fixed): the same per-CTA partial sums, added as integers with atomics into
+    # one int64 row -> equal to the fp64 sum of the partial rows up to the 2^-20 / 2^-16 quantum per CTA, and
+    # bit-identical from run to run (integer addition commutes)
+    acc = torch.zeros(2, cout, dtype=torch.int64, device=cuda)
+    opf = co.conv_fprop(co.View(xd), wp, k, stride, co.View(yd), bias=bias.to(cuda), stats=acc)
+    opf.run()
+    torch.cuda.synchronize()
+    first = acc.clone()
+    sf = torch.stack([first[0].double() / 2.0 ** 20, first[1].double() / 2.0 ** 16]).cpu()
+    assert float((sf[0] - s[0]).abs().max()) <= rows * 2.0 ** -21 + 1e-9, "fixed-point sum"
+    assert float((sf[1] - s[1]).abs().max()) <= rows * 2.0 ** -17 + 1e-9, "fixed-point sumsq"
+    acc.zero_()
+    opf.run()
+    torch.cuda.synchronize()
+    assert torch.equal(acc, first)
 
     # ---------------- dgrad ----------------
     dy = _rb(torch.randn(n, cout, ho, wo, generator=g))

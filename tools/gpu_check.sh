@@ -64,5 +64,11 @@ warp)
 warpncu)
   timeout 600 ncu --set full --clock-control none --import-source on -k regex:warp_u8 -s 4 -c 3 -f -o gpurun_out/warp \
       python tools/warp_profile.py > gpurun_out/warp_ncu.log 2>&1; echo "warp ncu rc=$?"; tail -2 gpurun_out/warp_ncu.log;;
+bnab)
+  # forward BatchNorm A/B: finalize kernels (0) against fixed-point accumulators + fused apply (2)
+  for m in 0 2 0 2; do
+    B2SEG_BN_FUSED_FWD=$m timeout 600 python bench.py --no-cpu-baseline --no-extras > gpurun_out/bench_bnfwd$m.json 2> gpurun_out/bench_bnfwd$m.err
+    echo "BN_FUSED_FWD=$m rc=$?"; python -c "import json;d=json.load(open('gpurun_out/bench_bnfwd$m.json'));print(round(d['ms_per_step'],3),'ms', d['launches_per_step'],'launches', d['final_loss'], d.get('parity_check'))"
+  done;;
 esac; done
 ls gpurun_out | wc -l
