@@ -160,9 +160,11 @@ def _peaks():
 
 def _recorded_traffic(a):
     """DRAM bytes per step of the tcgen05 conv kernels from the committed ncu capture of this exact
-    workload (profiles/r01_dram_step_families.json, made by tools/dram_summary.py from
+    workload (profiles/rNN_dram_step_families.json, made by tools/dram_summary.py from
     `ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum`); None for any other workload."""
-    path = os.path.join(ROOT, "profiles", "r01_dram_step_families.json")
+    path = os.path.join(ROOT, "profiles", "r02_dram_step_families.json")  # the newest committed capture
+    if not os.path.exists(path):
+        path = os.path.join(ROOT, "profiles", "r01_dram_step_families.json")
     if not (a.batch == 64 and a.size == 256 and a.backbone == "resnet34" and not a.no_attention
             and os.path.exists(path)):
         return None

@@ -34,7 +34,7 @@ ncu)
   timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none \
       --profile-from-start off --csv --log-file gpurun_out/dram_step.csv \
       python bench.py --steps 1 --warmup 3 --no-kernel-timing --no-cpu-baseline --no-extras > gpurun_out/ncu_dram.log 2>&1; echo "dram list rc=$?"
-  python tools/dram_summary.py gpurun_out/dram_step.csv > gpurun_out/dram_step_summary.txt 2>&1; head -30 gpurun_out/dram_step_summary.txt;;
+  python tools/dram_summary.py gpurun_out/dram_step.csv --json gpurun_out/dram_step_families.json > gpurun_out/dram_step_summary.txt 2>&1; head -30 gpurun_out/dram_step_summary.txt;;
 dp)
   # data parallel over all visible GPUs: consistency over real NCCL, then the bench line (carries dp_c5)
   NG=$(nvidia-smi -L | wc -l)
