@@ -417,33 +417,146 @@ __device__ __forceinline__ void bn_fold_stats(const float* partial, int rows, in
 
 // (sum, sumsq) -> scale / shift in shared memory; block 0 also publishes bnp = scale, shift, mean,
 // invstd and updates the running statistics: the arithmetic of bn_finalize_kernel, verbatim.
+__device__ __forceinline__ void bn_affine_channel(int c, double sum, double sumsq, int C, double count, float eps,
+                                                  float mom, const float* gamma, const float* beta, float* rmean,
+                                                  float* rvar, long long* nbt, float* bnp, float* sm_scale,
+                                                  float* sm_shift) {
+  const double m = sum / count;
+  double var = sumsq / count - m * m;
+  if (var < 0.0) var = 0.0;
+  const float mean = (float)m;
+  const float invstd = (float)(1.0 / sqrt(var + (double)eps));
+  const float g = gamma ? gamma[c] : 1.0f, b = beta ? beta[c] : 0.0f;
+  const float scale = g * invstd;
+  const float shift = b - mean * scale;
+  sm_scale[c] = scale;
+  sm_shift[c] = shift;
+  if (blockIdx.x == 0) {
+    if (rmean) {
+      const double unb = count > 1.0 ? var * count / (count - 1.0) : var;
+      rmean[c] = (1.0f - mom) * rmean[c] + mom * mean;
+      rvar[c] = (1.0f - mom) * rvar[c] + mom * (float)unb;
+    }
+    if (nbt && c == 0) *nbt += 1;
+    bnp[c] = scale;
+    bnp[C + c] = shift;
+    bnp[2 * C + c] = mean;
+    bnp[3 * C + c] = invstd;
+  }
+}
 __device__ __forceinline__ void bn_affine_from_sums(const double* sm_sum, int C, double count, float eps,
                                                     float mom, const float* gamma, const float* beta,
                                                     float* rmean, float* rvar, long long* nbt, float* bnp,
                                                     float* sm_scale, float* sm_shift) {
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    const double m = sm_sum[c] / count;
-    double var = sm_sum[C + c] / count - m * m;
-    if (var < 0.0) var = 0.0;
-    const float mean = (float)m;
-    const float invstd = (float)(1.0 / sqrt(var + (double)eps));
-    const float g = gamma ? gamma[c] : 1.0f, b = beta ? beta[c] : 0.0f;
-    const float scale = g * invstd;
-    const float shift = b - mean * scale;
-    sm_scale[c] = scale;
-    sm_shift[c] = shift;
-    if (blockIdx.x == 0) {
-      if (rmean) {
-        const double unb = count > 1.0 ? var * count / (count - 1.0) : var;
-        rmean[c] = (1.0f - mom) * rmean[c] + mom * mean;
-        rvar[c] = (1.0f - mom) * rvar[c] + mom * (float)unb;
+  for (int c = threadIdx.x; c < C; c += blockDim.x)
+    bn_affine_channel(c, sm_sum[c], sm_sum[C + c], C, count, eps, mom, gamma, beta, rmean, rvar, nbt, bnp,
+                      sm_scale, sm_shift);
+}
+// ... straight from the int64 fixed-point accumulators (no fold, no fp64 staging)
+__device__ __forceinline__ void bn_affine_from_fixed(const long long* acc, int C, double count, float eps,
+                                                     float mom, const float* gamma, const float* beta,
+                                                     float* rmean, float* rvar, long long* nbt, float* bnp,
+                                                     float* sm_scale, float* sm_shift) {
+  for (int c = threadIdx.x; c < C; c += blockDim.x)
+    bn_affine_channel(c, (double)__ldcg(acc + c) * (1.0 / (double)B2SEG_STATS_FIX_SUM),
+                      (double)__ldcg(acc + C + c) * (1.0 / (double)B2SEG_STATS_FIX_SQ), C, count, eps, mom, gamma,
+                      beta, rmean, rvar, nbt, bnp, sm_scale, sm_shift);
+}
+
+// EW_BN_APPLY_FUSED with fixed-point statistics (rows < 0 for every BatchNorm involved): bn_apply_kernel's
+// blocks, grid (one resident wave) and streaming loop; the first pixels of a thread are requested before the
+// statistics are turned into scale / shift, so the accumulators' L2 round trip and the fp64 chain hide behind them.
+// dynamic shared memory: [4C] floats (sc, sf, rs, rf)
+__global__ void __launch_bounds__(kEwThreads, 4) bn_apply_fixed_kernel(const EwArgs a) {
+  pdl_prologue();
+  extern __shared__ __align__(16) float bn_aff_sm[];
+  const bf16* y = (const bf16*)a.p[0];
+  bf16* out = (bf16*)a.p[1];
+  const bf16* res = (const bf16*)a.p[2];
+  const long long P = a.i[0];
+  const int C = (int)a.i[1];
+  const long long ldy = a.i[2], ldo = a.i[3], ldr = a.i[4];
+  const bool relu = a.i[5] != 0;
+  const bool rnorm = a.p[10] != nullptr;
+  const float eps = a.f[0], mom = a.f[1];
+  const int cv = C >> 3;
+  const bool fast = kEwThreads % cv == 0;
+  constexpr int NB = 2;
+  const uint4 zero4 = make_uint4(0, 0, 0, 0);
+  long long p = 0, pstep = 0;
+  int c0 = 0;
+  uint4 yv[NB], rv[NB];
+#pragma unroll
+  for (int b = 0; b < NB; ++b) yv[b] = rv[b] = zero4;
+  if (fast) {
+    const int ppb = kEwThreads / cv;
+    c0 = (threadIdx.x % cv) * 8;
+    pstep = (long long)gridDim.x * ppb;
+    p = (long long)blockIdx.x * ppb + threadIdx.x / cv;
+#pragma unroll
+    for (int b = 0; b < NB; ++b)
+      if (p + b * pstep < P) {
+        yv[b] = bn_ld_raw8(y + (p + b * pstep) * ldy + c0);
+        if (res) rv[b] = bn_ld_raw8(res + (p + b * pstep) * ldr + c0);
       }
-      if (nbt && c == 0) *nbt += 1;
-      bnp[c] = scale;
-      bnp[C + c] = shift;
-      bnp[2 * C + c] = mean;
-      bnp[3 * C + c] = invstd;
+  }
+  bn_affine_from_fixed((const long long*)a.p[3], C, (double)a.i[7], eps, mom, (const float*)a.p[4],
+                       (const float*)a.p[5], (float*)a.p[6], (float*)a.p[7], (long long*)a.p[8], (float*)a.p[9],
+                       bn_aff_sm, bn_aff_sm + C);
+  if (rnorm)
+    bn_affine_from_fixed((const long long*)a.p[10], C, (double)a.i[7], eps, mom, (const float*)a.p[11],
+                         (const float*)a.p[12], (float*)a.p[13], (float*)a.p[14], (long long*)a.p[15],
+                         (float*)a.p[16], bn_aff_sm + 2 * C, bn_aff_sm + 3 * C);
+  __syncthreads();
+  BnApplyCh ch;
+  if (fast) {
+    ch.sc = ld_f8(bn_aff_sm + c0);
+    ch.sf = ld_f8(bn_aff_sm + C + c0);
+    if (rnorm) {
+      ch.rs = ld_f8(bn_aff_sm + 2 * C + c0);
+      ch.rf = ld_f8(bn_aff_sm + 3 * C + c0);
     }
+    // the group requested before the prologue
+#pragma unroll
+    for (int b = 0; b < NB; ++b)
+      if (p + b * pstep < P)
+        st_bf8(out + (p + b * pstep) * ldo + c0, bn_apply_one(yv[b], rv[b], res != nullptr, ch, rnorm, relu));
+    p += NB * pstep;
+    for (; p + (NB - 1) * pstep < P; p += NB * pstep) {
+#pragma unroll
+      for (int b = 0; b < NB; ++b) {
+        yv[b] = bn_ld_raw8(y + (p + b * pstep) * ldy + c0);
+        if (res) rv[b] = bn_ld_raw8(res + (p + b * pstep) * ldr + c0);
+      }
+#pragma unroll
+      for (int b = 0; b < NB; ++b)
+        st_bf8(out + (p + b * pstep) * ldo + c0, bn_apply_one(yv[b], rv[b], res != nullptr, ch, rnorm, relu));
+    }
+    for (; p < P; p += pstep) {
+      const uint4 y0 = bn_ld_raw8(y + p * ldy + c0);
+      uint4 r0 = zero4;
+      if (res) r0 = bn_ld_raw8(res + p * ldr + c0);
+      st_bf8(out + p * ldo + c0, bn_apply_one(y0, r0, res != nullptr, ch, rnorm, relu));
+    }
+    return;
+  }
+  const long long total = P * cv;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const long long q = idx / cv;
+    const int d0 = (int)(idx % cv) * 8;
+    ch.sc = ld_f8(bn_aff_sm + d0);
+    ch.sf = ld_f8(bn_aff_sm + C + d0);
+    const uint4 y0 = bn_ld_raw8(y + q * ldy + d0);
+    uint4 r0 = zero4;
+    if (res) {
+      r0 = bn_ld_raw8(res + q * ldr + d0);
+      if (rnorm) {
+        ch.rs = ld_f8(bn_aff_sm + 2 * C + d0);
+        ch.rf = ld_f8(bn_aff_sm + 3 * C + d0);
+      }
+    }
+    st_bf8(out + q * ldo + d0, bn_apply_one(y0, r0, res != nullptr, ch, rnorm, relu));
   }
 }
 
@@ -904,6 +1017,7 @@ EW_LAUNCHER(launch_colsum_finalize, colsum_finalize_kernel)
 EW_LAUNCHER(launch_pack, pack_kernel)
 EW_LAUNCHER(launch_fill, fill_kernel)
 EW_LAUNCHER(launch_bn_apply_fused, bn_apply_fused_kernel)
+EW_LAUNCHER(launch_bn_apply_fixed, bn_apply_fixed_kernel)
 EW_LAUNCHER(launch_bn_bwd_fused_act, bn_bwd_fused_kernel<true>)
 EW_LAUNCHER(launch_bn_bwd_fused_noact, bn_bwd_fused_kernel<false>)
 
@@ -1025,6 +1139,15 @@ int ew_plan_bn(const b2seg_ew_desc* d, EwPlan* pl) {
       B2_REQUIRE(i[2] % 8 == 0 && i[3] % 8 == 0 && i[4] % 8 == 0 && aligned16(p[0]) &&
                      aligned16(p[1]) && aligned16(p[2]),
                  "bn_apply_fused: leading dimensions / pointers must be 16-byte aligned");
+      if (i[6] < 0 && (!p[10] || i[8] < 0) && !getenv("B2SEG_BN_FIXED_WIDE")) {  // fixed-point statistics only
+        pl->fn = launch_bn_apply_fixed;
+        pl->grid = dim3(ew_resident_blocks(bn_apply_fixed_kernel, i[0] * (i[1] / 8)));
+        pl->block = dim3(kEwThreads);
+        pl->smem = (size_t)4 * i[1] * sizeof(float);
+        pl->smem_limit = 48 * 1024;
+        B2_REQUIRE(pl->smem <= pl->smem_limit, "bn_apply_fused: %lld channels exceed the shared-memory table", i[1]);
+        return B2SEG_OK;
+      }
       pl->fn = launch_bn_apply_fused;
       long long b = (i[0] * (i[1] / 8) + kBnT * 4 - 1) / (kBnT * 4);  // >= 4 vectors per thread
       const long long cap = 2ll * b2_num_sms();
