@@ -538,7 +538,10 @@ enum {
    * p8 num_batches_tracked|NULL  p9 out bnp f32 [4][C]
    * p10 res partial|NULL  p11..p16 = gamma, beta, running_mean, running_var, nbt, bnp of the residual BN
    * i0 P  i1 C  i2 ld_y  i3 ld_out  i4 ld_res  i5 relu  i6 rows  i7 count  i8 res rows
-   * f0 eps  f1 momentum */
+   * f0 eps  f1 momentum
+   * rows < 0 (res rows < 0): p3 (p10) is the int64 [2][C] fixed-point accumulator that the conv epilogues added
+   * to (b2seg_tapgemm_desc::stats_fixed; sum x 2^20, sum of squares x 2^16) -- nothing to fold, the blocks derive
+   * scale / shift straight from it.  The caller zeroes the accumulators before the convolutions of every pass. */
   B2SEG_EW_BN_APPLY_FUSED = 24,
   /* BatchNorm backward in ONE persistent launch (BN_BWD_REDUCE + _FINALIZE + _APPLY): phase 1 block
    * partials of (sum dz, sum dz*y); device-wide barrier (all blocks are co-resident: one per SM);
