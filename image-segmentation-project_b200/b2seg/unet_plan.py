@@ -60,6 +60,7 @@ class BNRef:
 
 
 _BN_FUSED_FWD_DEFAULT = "2"
+_BN_FIXED_BWD_DEFAULT = "0"
 _FX_CAP = 1 << 18  # int64 words of fixed-point BatchNorm accumulators per plan (2 x the BatchNorm channels)
 
 
@@ -72,6 +73,15 @@ def _fused_bn_fwd():
        (exact and order-independent, so still bit-reproducible) and the consumer reads 2C words."""
     import os
     return os.environ.get("B2SEG_BN_FUSED_FWD", _BN_FUSED_FWD_DEFAULT)
+
+
+def _fixed_bn_bwd():
+    """B2SEG_BN_FIXED_BWD=1: the BatchNorm-backward reduce adds its block sums (sum dz, sum dz*y) as fixed-point
+    integers (x 2^40) into one int64 row with atomics and the apply kernel derives its per-channel constants (and
+    block 0 dgamma / dbeta) from it -- no finalize launch.  Exact and order-independent like the forward
+    statistics; range |block sum| < 2^22, resolution 9e-13."""
+    import os
+    return os.environ.get("B2SEG_BN_FIXED_BWD", _BN_FIXED_BWD_DEFAULT) == "1"
 
 
 def _fused_bn_bwd_max_bytes():
@@ -166,6 +176,18 @@ class UNetPlan:
         if self._fx_used > _FX_CAP:
             raise RuntimeError("fixed-point BatchNorm accumulator arena exhausted")
         return self._fx[o:o + n]
+
+    def _fxb_alloc(self, n):
+        """The same for the backward pass (its own arena and fill, so that a second backward after one forward
+        starts from zero too)."""
+        if getattr(self, "_fxb", None) is None:
+            self._fxb = self._alloc((_FX_CAP,), torch.int64, zero=True)
+            self._fxb_used = 0
+        o = self._fxb_used
+        self._fxb_used = o + ((n + 1) & ~1)
+        if self._fxb_used > _FX_CAP:
+            raise RuntimeError("fixed-point BatchNorm accumulator arena exhausted")
+        return self._fxb[o:o + n]
 
     def act(self, n, h, w, c, grad=None):
         """New dense activation (and gradient buffer when a backward pass is planned)."""
@@ -310,6 +332,15 @@ class UNetPlan:
                          i=ii + [dy.sw, dz.sw if dz else 0, 2 if dz_acc else 1, 1 if self_mask else 0,
                                  1 if self.training else 0, 0]))
             return
+        if _fixed_bn_bwd() and C_ % 8 == 0 and 256 % (C_ // 8) == 0:
+            acc = self._fxb_alloc(2 * C_)
+            self.B(eo.ew(L.EW_BN_BWD_REDUCE, p=pp + [acc], i=ii + [1, 0, 0, 1 if self_mask else 0]))  # i6: fixed
+            self.B(eo.ew(L.EW_BN_BWD_APPLY,
+                         p=pp + [acc, dy, dz, self.params[prefix + ".weight"], self.gview(prefix + ".weight"),
+                                 self.gview(prefix + ".bias"), dbias],
+                         i=ii + [dy.sw, dz.sw if dz else 0, 2 if dz_acc else 1, 1 if self_mask else 0,
+                                 1 | (2 if self.training else 0)]))
+            return
         tail = [0, 0, 0, 1 if self_mask else 0]  # i6..i8 unused by REDUCE, i9 = self-mask flag
         self.B(eo.ew(L.EW_BN_BWD_REDUCE, p=pp + [self.part], i=ii + tail))
         coef = self._alloc((3, C_), F32)
@@ -442,6 +473,9 @@ class UNetPlan:
         self.tape += [bwd_up0, bwd_final]
         if ng:
             self.ws = self._alloc((max(self._ws_req, 1024) // 4 + 64,), F32)
+            if _fixed_bn_bwd():  # first backward op: zero the backward accumulators (whole arena: 2 MB, ~1 us)
+                self._fxb_alloc(0)
+                self.B(eo.ew(L.EW_FILL, p=[self._fxb], i=[_FX_CAP * 8, 0]))
             done = {}  # gradient group -> index one past the last backward op that writes into it
             for fn in reversed(self.tape):
                 self._gview_log = []

@@ -231,7 +231,8 @@ __global__ void __launch_bounds__(kEwThreads) bn_bwd_reduce_kernel(const EwArgs 
           acc[0][j] += dz.v[j];
           acc[1][j] = fmaf(dz.v[j], y.v[j], acc[1][j]);
         }
-      });
+      },
+      a.i[6] != 0);  // i6: fixed-point accumulators instead of block-partial rows
 }
 
 __global__ void __launch_bounds__(1024) bn_bwd_finalize_kernel(const EwArgs a) {
@@ -287,6 +288,55 @@ __device__ __forceinline__ BnBwdLin bn_bwd_lin(const BnBwdIn& s, const float* co
   }
   return k;
 }
+// The same constants straight from the fixed-point sums (a.i[10] bit 0): the arithmetic of bn_bwd_finalize_kernel
+// per channel, no finalize launch.  Block 0's first C/8 threads also write dgamma / dbeta / dbias.
+//   p5 int64 [2][C] (sum dz, sum dz*y) x 2^40   p8 gamma|NULL  p9 dgamma|NULL  p10 dbeta|NULL  p11 dbias|NULL
+//   i10: bit 0 fixed, bit 1 training, bit 2 accumulate into dgamma / dbeta / dbias
+__device__ __forceinline__ BnBwdLin bn_bwd_lin_fixed(const BnBwdIn& s, const EwArgs& a, int c0, bool publish) {
+  BnBwdLin k;
+  const int C = s.C;
+  const long long* acc = (const long long*)a.p[5];
+  const float* gamma = (const float*)a.p[8];
+  float* dgamma = (float*)a.p[9];
+  float* dbeta = (float*)a.p[10];
+  float* dbias = (float*)a.p[11];
+  const double count = (double)a.i[0];
+  const bool training = (a.i[10] & 2) != 0, accumulate = (a.i[10] & 4) != 0;
+  long long r0[8], r1[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    r0[j] = __ldcg(acc + c0 + j);
+    r1[j] = __ldcg(acc + C + c0 + j);
+  }
+  const F8 mean = ld_f8(s.bnp + 2 * C + c0), inv = ld_f8(s.bnp + 3 * C + c0);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const double sd = (double)r0[j] * (1.0 / B2SEG_BWD_FIX_SCALE);
+    const double q = (double)inv.v[j] * ((double)r1[j] * (1.0 / B2SEG_BWD_FIX_SCALE) - (double)mean.v[j] * sd);
+    const float g = gamma ? gamma[c0 + j] : 1.0f;
+    const float c1 = g * inv.v[j];
+    const float c2 = training ? (float)(sd / count) : 0.0f;
+    const float c3 = training ? (float)(q / count) : 0.0f;
+    const float t = c3 * inv.v[j];
+    k.A.v[j] = c1;
+    k.B.v[j] = -c1 * t;
+    k.D.v[j] = c1 * (t * mean.v[j] - c2);
+    if (publish) {
+      const int c = c0 + j;
+      if (dgamma) dgamma[c] = accumulate ? dgamma[c] + (float)q : (float)q;
+      if (dbeta) dbeta[c] = accumulate ? dbeta[c] + (float)sd : (float)sd;
+      if (dbias) {
+        const float vb = training ? 0.0f : c1 * (float)sd;
+        dbias[c] = accumulate ? dbias[c] + vb : vb;
+      }
+    }
+  }
+  if (s.self_mask) {
+    k.sc = ld_f8(s.bnp + c0);
+    k.sf = ld_f8(s.bnp + C + c0);
+  }
+  return k;
+}
 __device__ __forceinline__ void bn_bwd_apply_store(const BnBwdIn& s, const BnBwdLin& k, const BnBwdRaw& r,
                                                    bool dz_acc, long long p, int c0, bf16* dy,
                                                    long long lddy, bf16* dzo, long long lddz) {
@@ -318,7 +368,8 @@ __global__ void __launch_bounds__(kEwThreads) bn_bwd_apply_kernel(const EwArgs a
     const int ppb = kEwThreads / cv;
     const int c0 = (threadIdx.x % cv) * 8;
     const long long pstep = (long long)gridDim.x * ppb;
-    const BnBwdLin k = bn_bwd_lin(s, coef, c0);
+    const BnBwdLin k = (a.i[10] & 1) ? bn_bwd_lin_fixed(s, a, c0, blockIdx.x == 0 && threadIdx.x < cv)
+                                     : bn_bwd_lin(s, coef, c0);
     long long p = (long long)blockIdx.x * ppb + threadIdx.x / cv;
     constexpr int U = 3;  // pixels in flight per thread
     for (; p + (U - 1) * pstep < P; p += U * pstep) {
@@ -1093,6 +1144,8 @@ int ew_plan_bn(const b2seg_ew_desc* d, EwPlan* pl) {
         B2_REQUIRE(p[6] && i[6] % 8 == 0 && i[7] % 8 == 0 && aligned16(p[6]) && aligned16(p[7]),
                    "bn_bwd_apply: dy/dz must be 16-byte aligned");
         B2_REQUIRE(!p[7] || i[8] == 1 || i[8] == 2, "bn_bwd_apply: dz mode must be 1 or 2");
+        B2_REQUIRE(!(i[10] & 1) || kEwThreads % (i[1] / 8) == 0,
+                   "bn_bwd_apply: fixed-point sums need C/8 to divide %d (C = %lld)", kEwThreads, i[1]);
         pl->fn = launch_bn_bwd_apply;
         pl->grid = dim3(ew_resident_blocks(bn_bwd_apply_kernel, i[0] * (i[1] / 8)));
         pl->block = dim3(kEwThreads);

@@ -233,10 +233,12 @@ __device__ __forceinline__ void ew_rows_reduce(const float* partial, int rows, l
 // does the arithmetic.  NB pixels are fetched before the first is consumed, so a thread keeps NB x (32-64) bytes
 // in flight: with one pixel per iteration the BatchNorm-backward reduce had ~24 KB in flight per SM and ran at
 // 3.6-4.1 TB/s -- Little's law, not HBM.
+// fixed != 0: `partial` is ONE int64 row [NACC][C] instead; the block adds its sums as fixed-point integers
+// (x 2^40, clamped to +-2^62) with 64-bit atomics -- exact and order-independent (B2SEG_BWD_FIX_SCALE).
 template <int NACC, int NB, class Fetch, class Consume>
 __device__ __forceinline__ void ew_channel_reduce_batched(long long P0, long long P1, int C, float* partial,
                                                           float* red /* smem NACC*pl*C */, Fetch fetch,
-                                                          Consume consume) {
+                                                          Consume consume, bool fixed = false) {
   const int cv = C >> 3;
   const int pl = blockDim.x / cv > 0 ? blockDim.x / cv : 1;
   const int lc = threadIdx.x % cv, lp = threadIdx.x / cv;
@@ -266,7 +268,13 @@ __device__ __forceinline__ void ew_channel_reduce_batched(long long P0, long lon
     const int k = idx / C, c = idx % C;
     float s = 0.0f;
     for (int l = 0; l < pl; ++l) s += red[((size_t)k * pl + l) * C + c];
-    partial[((size_t)blockIdx.x * NACC + k) * C + c] = s;
+    if (fixed) {
+      const double v = fmin(fmax((double)s * B2SEG_BWD_FIX_SCALE, -4.611686018427388e18), 4.611686018427388e18);
+      atomicAdd(reinterpret_cast<unsigned long long*>(partial) + (size_t)k * C + c,
+                (unsigned long long)__double2ll_rn(v));
+    } else {
+      partial[((size_t)blockIdx.x * NACC + k) * C + c] = s;
+    }
   }
 }
 

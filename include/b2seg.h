@@ -351,6 +351,7 @@ typedef struct b2seg_tapgemm_desc {
 } b2seg_tapgemm_desc;
 #define B2SEG_STATS_FIX_SUM 1048576.0f   /* 2^20 */
 #define B2SEG_STATS_FIX_SQ 65536.0f      /* 2^16 */
+#define B2SEG_BWD_FIX_SCALE 1099511627776.0 /* 2^40: BatchNorm-backward sums (sum dz, sum dz*y) as fixed point */
 
 int b2seg_tapgemm_create(const b2seg_tapgemm_desc* desc /*host*/, b2seg_op** out);
 /* number of partial-statistics rows a tapgemm op with this iteration grid writes */
